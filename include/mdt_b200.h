@@ -1,0 +1,202 @@
+/*
+ * mdt_b200.h -- C ABI of the B200-native VAE-HPO trial step.
+ *
+ * The reference (ORNL/MultiDistTorch) has no FFI: its hot path is ~60 lines of
+ * Python (vae-hpo.py:19-92,122-131) that call PyTorch.  This header is the
+ * boundary a maintainer binds instead of those calls (ctypes stub in
+ * INTEGRATION.md).  Every entry point names the reference lines it replaces.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every `float*` is DEVICE memory unless the
+ *     name ends in `_host`; `stream` is a cudaStream_t passed as void*
+ *     (NULL = legacy default stream); `nccl_comm` is an ncclComm_t as void*.
+ *   - every function returns 0 on success or a negative mdt_status; the message
+ *     is available from mdt_last_error() (thread-local).  Nothing throws.
+ *   - work is enqueued on the engine's stream and is asynchronous unless the
+ *     function name ends in `_host` (those synchronise the stream once).
+ *   - one process per GPU, one engine per trial; not re-entrant.
+ *   - there is no CPU path: without a CUDA device every call fails with
+ *     MDT_ERR_CUDA.
+ *
+ * Flat parameter layout (all four bound buffers share it), row-major fp32:
+ *   W1[H,D] b1[H] W2x[2Z,H] b2x[2Z] W3[H,Z] b3[H] W4[D,H] b4[D]
+ * W2x = fc21.weight stacked over fc22.weight (mu rows first), b2x likewise;
+ * every segment starts on a 32-float (128-byte) boundary; gaps stay zero.
+ * mdt_param_layout() returns the offsets.
+ */
+#ifndef MDT_B200_H
+#define MDT_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MDT_VERSION 100 /* 0.1.0 */
+#define MDT_NUM_SEGMENTS 8
+
+typedef enum mdt_status {
+  MDT_OK = 0,
+  MDT_ERR_INVALID = -1,     /* bad argument / shape */
+  MDT_ERR_CUDA = -2,        /* CUDA runtime or driver error (message has the code) */
+  MDT_ERR_NCCL = -3,        /* NCCL error or NCCL symbols not found in the process */
+  MDT_ERR_UNSUPPORTED = -4, /* feature not available in this build / on this device */
+  MDT_ERR_STATE = -5        /* call order (e.g. step before bind_buffers) */
+} mdt_status;
+
+typedef enum mdt_gemm_mode {
+  MDT_GEMM_FP32 = 0,   /* fp32 FFMA tiles: the tight-tolerance parity path */
+  MDT_GEMM_TF32 = 1,   /* tcgen05.mma kind::tf32, TMA-staged, TMEM accumulators */
+  MDT_GEMM_TF32X3 = 2  /* 3-pass split-TF32 on tcgen05 (fp32-grade accuracy) */
+} mdt_gemm_mode;
+
+typedef enum mdt_act { MDT_ACT_NONE = 0, MDT_ACT_RELU = 1, MDT_ACT_SIGMOID = 2 } mdt_act;
+
+/* Model/trial configuration: VAE(in_dim - hidden - latent), ref:vae-hpo.py:20-27. */
+typedef struct mdt_cfg {
+  int32_t in_dim;     /* D, 784 */
+  int32_t hidden;     /* H, 400 (4096 in BASELINE config 5) */
+  int32_t latent;     /* Z, 20 */
+  int32_t max_batch;  /* largest per-rank batch any call will pass */
+  int32_t gemm_mode;  /* mdt_gemm_mode */
+  int32_t use_graph;  /* 1: capture each (batch size) step into a CUDA graph */
+  int32_t reserved[2];
+} mdt_cfg;
+
+/* Adam hyper-parameters as the Python doubles torch.optim.Adam keeps
+ * (ref:vae-hpo.py:131: lr=1e-3, defaults beta=(0.9,0.999), eps=1e-8). */
+typedef struct mdt_adam {
+  double lr, beta1, beta2, eps;
+} mdt_adam;
+
+typedef struct mdt_engine mdt_engine;
+
+int mdt_version(void);
+const char* mdt_last_error(void);
+
+/* Offsets/sizes (in floats) of the 8 segments and the padded total.
+ * Replaces: the implicit model.parameters() order of ref:vae-hpo.py:23-27,131. */
+int mdt_param_layout(const mdt_cfg* cfg, int64_t offsets[MDT_NUM_SEGMENTS], int64_t numels[MDT_NUM_SEGMENTS],
+                     int64_t* total);
+
+/* ---- engine: one trial on one GPU ------------------------------------------------ */
+
+/* Replaces: VAE().to(device) + DistributedDataParallel(model, process_group=group)
+ * construction, ref:vae-hpo.py:129-130.  `nccl_comm` is the communicator of the
+ * trial's subgroup (ref:utils.py:157) or NULL when group_size == 1. */
+int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int group_rank, void* stream,
+                      mdt_engine** out);
+void mdt_engine_destroy(mdt_engine* e);
+
+/* The stream the engine enqueues on (its own blocking stream when created with
+ * stream == NULL): record timing events / order other work against this one. */
+int mdt_engine_stream(mdt_engine* e, void** stream);
+
+/* Caller-owned flat buffers (layout above), 128-byte aligned, `numel` == layout total.
+ * Replaces: model.parameters() / p.grad / Adam state tensors, ref:vae-hpo.py:131. */
+int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                            size_t numel);
+
+/* DDP constructor semantics: broadcast params from group-rank 0 (ref:vae-hpo.py:130). */
+int mdt_engine_broadcast_params(mdt_engine* e);
+
+/* Device-resident per-trial state read by the kernels (so a captured step needs no
+ * host-side scalars): Adam hyper-parameters + completed step count, Philox seed/offset.
+ * Replaces: optim.Adam(..., lr=1e-3) state and the CUDA default generator. */
+int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_steps);
+int mdt_engine_set_rng(mdt_engine* e, uint64_t philox_seed, uint64_t philox_offset);
+int mdt_engine_get_state(mdt_engine* e, int64_t* completed_steps, uint64_t* philox_offset); /* syncs */
+
+/* Stage buffer the step reads x from ([max_batch, D] fp32).  Writing the batch here
+ * (H2D copy, or a device-side sampler) skips the D2D copy mdt_train_step would do. */
+int mdt_engine_input_buffer(mdt_engine* e, float** x_stage);
+
+/* recon, mu, logvar = model(x): ref:vae-hpo.py:42-45 (encode 29-31, reparameterize
+ * 33-36, decode 38-40).  eps_or_null == NULL draws eps from Philox exactly like
+ * torch.randn_like on CUDA and advances the offset.  Outputs may be NULL.  Keeps
+ * the activations for mdt_backward. */
+int mdt_forward(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* recon, float* mu,
+                float* logvar);
+
+/* loss.backward() for upstream gradients produced elsewhere (compat mode, where the
+ * script's own loss_function ran in torch): ref:vae-hpo.py:72.  Fills `grads`. */
+int mdt_backward(mdt_engine* e, const float* d_recon, const float* d_mu, const float* d_logvar);
+
+/* Gradient averaging over the trial group: the DDP reducer inside
+ * loss.backward(), ref:vae-hpo.py:72,130.  SUM only; 1/n is applied by the Adam
+ * kernel (mdt_adam_step grad_scale). */
+int mdt_allreduce_grads(mdt_engine* e);
+
+/* optimizer.step(): ref:vae-hpo.py:74.  Uses/advances the device-resident step count. */
+int mdt_adam_step(mdt_engine* e, float grad_scale);
+
+/* One whole training step, ref:vae-hpo.py:68-74:
+ *   forward -> BCE+KLD loss -> backward -> group all-reduce -> Adam.
+ * `loss_out` (device, may be NULL) receives the summed loss of this rank's batch. */
+int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out);
+
+/* Same, with HOST buffers: copies x (and eps) host->device, runs the step, copies
+ * the loss back and synchronises (the `loss.item()` of ref:vae-hpo.py:73).
+ * Pinned host memory makes the copies asynchronous; pageable memory also works. */
+int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
+                        float* loss_host);
+
+/* Forward + loss only (the eval loop), ref:vae-hpo.py:101-105. */
+int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out,
+                  float* recon);
+
+/* model.module.decode(z): ref:vae-hpo.py:38-40,165. */
+int mdt_decode(mdt_engine* e, const float* z, int batch, float* recon);
+
+/* Debug/test access to an internal activation buffer by name ("h1","ml","z","h3",
+ * "recon","da4","da3","dml","da1","eps"); returns its device pointer and leading
+ * dimension. */
+int mdt_engine_workspace(mdt_engine* e, const char* name, float** ptr, int* ld);
+
+/* Number of kernels this engine has enqueued so far (a CUDA-graph launch counts the
+ * kernels inside the graph).  Measurement aid; no reference counterpart. */
+int mdt_engine_launch_count(mdt_engine* e, int64_t* kernels);
+
+/* Measurement aid: run `iters` un-graphed training steps on x with a CUDA event after
+ * every kernel and write "label avg_ms\n" lines (one per kernel of the step, in launch
+ * order) into `out`.  The steps DO update the parameters.  No reference counterpart
+ * (the reference only prints wall time, ref:vae-hpo.py:159,173-174). */
+int mdt_engine_profile_step(mdt_engine* e, const float* x, int batch, int iters, char* out, size_t out_len);
+
+/* ---- stand-alone kernels (also used by the engine) --------------------------------- */
+
+/* Fused flat Adam: one pass over p,g,m,v (7 x 4 bytes per element).  `step` is the
+ * 1-based step being taken.  Replaces torch's _multi_tensor_adam, ref:vae-hpo.py:74. */
+int mdt_adam_flat(float* p, const float* g, float* m, float* v, size_t n, const mdt_adam* h, int64_t step,
+                  float grad_scale, void* stream);
+
+/* z = mu + eps*exp(0.5*logvar), ref:vae-hpo.py:33-36.  mu/logvar/z have leading
+ * dimensions ld_ml / ld_z.  eps_in NULL -> Philox(seed, offset) as torch CUDA randn;
+ * eps_out (optional) receives the eps used. */
+int mdt_reparam(const float* mu, const float* logvar, int ld_ml, const float* eps_in, uint64_t seed,
+                uint64_t offset, int batch, int latent, float* z, int ld_z, float* eps_out, void* stream);
+
+/* Fused BCE(sum)+KLD loss and its gradients, ref:vae-hpo.py:49-58 and its autograd.
+ * d_* may be NULL.  `loss_out` is one device float.  Uses a small internally
+ * allocated scratch for per-block partial sums (deterministic summation order). */
+int mdt_loss_bce_kl(const float* recon, const float* x, const float* mu, const float* logvar, int batch,
+                    int in_dim, int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar,
+                    void* stream);
+
+/* y[M,N] = act(x[M,K] . W[N,K]^T + b[N]) : nn.Linear (+F.relu / torch.sigmoid),
+ * ref:vae-hpo.py:30-31,39-40.  `gemm_mode` selects the kernel family. */
+int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode,
+               float* y, void* stream);
+
+/* Time `iters` in-place fp32 SUM all-reduces of `bytes` bytes on `comm`; returns the
+ * average seconds per all-reduce measured with CUDA events on `stream`.  Replaces
+ * nothing in the reference (it only all-gathers one int64, ref:example-subgroup.py:25-33);
+ * it backs BASELINE.json's "subgroup allreduce bus GB/s" metric. */
+int mdt_allreduce_bench(void* nccl_comm, void* buf, size_t bytes, int iters, void* stream, double* seconds);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MDT_B200_H */

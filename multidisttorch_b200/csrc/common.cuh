@@ -1,0 +1,119 @@
+// Shared device/host helpers for the B200 VAE-HPO step kernels.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/mdt_b200.h"
+
+namespace mdt {
+
+// ---------------------------------------------------------------- errors
+inline thread_local char g_last_error[1024] = "";
+
+inline int set_error(int code, const char* fmt, ...) __attribute__((format(printf, 2, 3)));
+inline int set_error(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_last_error, sizeof(g_last_error), fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define MDT_CUDA(expr)                                                                                       \
+  do {                                                                                                       \
+    cudaError_t _e = (expr);                                                                                 \
+    if (_e != cudaSuccess)                                                                                   \
+      return ::mdt::set_error(MDT_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(_e), __FILE__, \
+                              __LINE__);                                                                     \
+  } while (0)
+
+#define MDT_CHECK(cond, ...)                                         \
+  do {                                                               \
+    if (!(cond)) return ::mdt::set_error(MDT_ERR_INVALID, __VA_ARGS__); \
+  } while (0)
+
+#define MDT_TRY(expr)          \
+  do {                         \
+    int _r = (expr);           \
+    if (_r != MDT_OK) return _r; \
+  } while (0)
+
+// ---------------------------------------------------------------- layout
+constexpr int kSegAlign = 32;  // floats
+enum Seg { W1 = 0, B1, W2X, B2X, W3, B3, W4, B4, kNumSeg };
+
+struct Layout {
+  int64_t off[kNumSeg];
+  int64_t numel[kNumSeg];
+  int64_t total;
+};
+
+inline int64_t round_up(int64_t n, int64_t a) { return (n + a - 1) / a * a; }
+
+inline Layout make_layout(int D, int H, int Z) {
+  Layout L;
+  const int64_t n[kNumSeg] = {(int64_t)H * D, H, (int64_t)2 * Z * H, 2 * Z, (int64_t)H * Z, H, (int64_t)D * H, D};
+  int64_t o = 0;
+  for (int i = 0; i < kNumSeg; ++i) {
+    L.off[i] = o;
+    L.numel[i] = n[i];
+    o += round_up(n[i], kSegAlign);
+  }
+  L.total = o;
+  return L;
+}
+
+// ---------------------------------------------------------------- device state
+// Per-trial scalars the kernels read from device memory, so a captured CUDA graph
+// of the step never needs host-side arguments refreshed.
+struct StepState {
+  unsigned long long philox_seed;
+  unsigned long long philox_offset;  // advanced by the reparameterisation kernel
+  long long adam_t;                  // completed Adam steps; advanced by the Adam kernel
+  double lr, beta1, beta2, eps;
+  unsigned int ticket_reparam;       // "last block done" counters (self-resetting)
+  unsigned int ticket_adam;
+  unsigned int ticket_loss;
+  unsigned int pad;
+};
+
+// ---------------------------------------------------------------- device helpers
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// Sum over a block of up to 1024 threads; result valid in thread 0.  `red` needs 32 floats.
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  if (lane == 0) red[w] = v;
+  __syncthreads();
+  const int nw = (blockDim.x + 31) >> 5;
+  v = (threadIdx.x < nw) ? red[threadIdx.x] : 0.f;
+  if (w == 0) v = warp_sum(v);
+  __syncthreads();
+  return v;
+}
+
+__device__ __forceinline__ float sigmoidf_ref(float a) { return 1.0f / (1.0f + expf(-a)); }
+
+// Element of F.binary_cross_entropy(reduction='sum'): each log clamped at -100.
+__device__ __forceinline__ float bce_term(float r, float x) {
+  const float l1 = fmaxf(log1pf(-r), -100.0f);
+  const float l0 = fmaxf(logf(r), -100.0f);
+  return (x - 1.0f) * l1 - x * l0;
+}
+// binary_cross_entropy_backward (grad_output == 1).
+__device__ __forceinline__ float bce_grad(float r, float x) { return (r - x) / fmaxf((1.0f - r) * r, 1e-12f); }
+// sigmoid_backward
+__device__ __forceinline__ float sigmoid_bwd(float g, float r) { return g * (1.0f - r) * r; }
+
+}  // namespace mdt

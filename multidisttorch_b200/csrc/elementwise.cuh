@@ -1,0 +1,356 @@
+// HBM-bound kernels of the VAE-HPO step: fused reparameterisation (Philox),
+// fused BCE+KLD loss-and-gradient, bias-gradient column sums, flat fused Adam.
+// All are plain fp32, vectorised (float4) and coalesced; reductions use warp
+// shuffles and a fixed summation order (bit-reproducible run to run).
+#pragma once
+
+#include <curand_kernel.h>
+
+#include "common.cuh"
+
+namespace mdt {
+
+// ============================================================================
+// Reparameterisation: z = mu + eps * exp(0.5*logvar)            ref:vae-hpo.py:33-36
+// eps either supplied or generated exactly like torch.randn_like on CUDA:
+// Philox4x32-10, curand_init(seed, subsequence = thread, offset), lane ii of
+// curand_normal4 for element  thread + S*ii  (S = 256 * torch's grid size).
+// ============================================================================
+__device__ __forceinline__ float torch_cuda_randn_elem(unsigned long long seed, unsigned long long offset,
+                                                       long long i, long long S) {
+  const long long per_round = 4 * S;
+  const long long round = i / per_round;
+  const long long rem = i - round * per_round;
+  const int lane = (int)(rem / S);
+  const long long tid = rem - (long long)lane * S;
+  curandStatePhilox4_32_10_t st;
+  curand_init(seed, (unsigned long long)tid, offset + 4ull * (unsigned long long)round, &st);
+  const float4 r = curand_normal4(&st);
+  return lane == 0 ? r.x : lane == 1 ? r.y : lane == 2 ? r.z : r.w;
+}
+
+// Host: torch's calc_execution_policy (ATen/native/cuda/DistributionTemplates.h:50-62).
+inline void torch_randn_policy(long long numel, int sm_count, int max_threads_per_sm, long long* S,
+                               unsigned long long* offset_inc) {
+  long long grid = (numel + 255) / 256;
+  const long long cap = (long long)sm_count * (max_threads_per_sm / 256);
+  if (grid > cap) grid = cap;
+  if (grid < 1) grid = 1;
+  *S = 256 * grid;
+  *offset_inc = (unsigned long long)(((numel - 1) / (256 * grid * 4) + 1) * 4);
+}
+
+struct ReparamArgs {
+  const float* mu;
+  const float* logvar;
+  int ld_ml;
+  const float* eps_in;  // NULL -> Philox
+  StepState* st;        // non-NULL: seed/offset come from (and the offset is advanced in) device state
+  unsigned long long seed, offset;
+  long long S;
+  unsigned long long offset_inc;
+  int B, Z;
+  float* z;
+  int ld_z;
+  float* eps_out;  // [B,Z] contiguous, optional
+  float* std_out;  // [B,Z] contiguous, optional
+};
+
+__global__ void reparam_kernel(ReparamArgs a) {
+  const long long n = (long long)a.B * a.Z;
+  unsigned long long seed = a.seed, offset = a.offset;
+  if (a.st != nullptr) {
+    seed = a.st->philox_seed;
+    offset = a.st->philox_offset;
+  }
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(i / a.Z), j = (int)(i - (long long)b * a.Z);
+    const float mu = a.mu[(size_t)b * a.ld_ml + j];
+    const float lv = a.logvar[(size_t)b * a.ld_ml + j];
+    const float sd = expf(0.5f * lv);
+    const float e = a.eps_in ? a.eps_in[i] : torch_cuda_randn_elem(seed, offset, i, a.S);
+    a.z[(size_t)b * a.ld_z + j] = mu + e * sd;
+    if (a.eps_out) a.eps_out[i] = e;
+    if (a.std_out) a.std_out[i] = sd;
+  }
+  // advance the device-resident Philox offset once every block has read it
+  if (a.st != nullptr && a.eps_in == nullptr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const unsigned int done = atomicAdd(&a.st->ticket_reparam, 1u);
+      if (done == gridDim.x - 1) {
+        a.st->philox_offset = offset + a.offset_inc;
+        a.st->ticket_reparam = 0;
+        __threadfence();
+      }
+    }
+  }
+}
+
+// dml = [dz + dmu_kl | 0.5*dz*eps*std + dlv_kl]   (autograd of ref:vae-hpo.py:33-36)
+__global__ void reparam_bwd_kernel(const float* dz, int ld_dz, const float* eps, const float* sd, const float* dml_kl,
+                                   int B, int Z, float* dml) {
+  const long long n = (long long)B * Z;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(i / Z), j = (int)(i - (long long)b * Z);
+    const float g = dz[(size_t)b * ld_dz + j];
+    const size_t o = (size_t)b * 2 * Z;
+    dml[o + j] = g + dml_kl[o + j];
+    dml[o + Z + j] = g * eps[i] * sd[i] * 0.5f + dml_kl[o + Z + j];
+  }
+}
+
+// ============================================================================
+// Fused BCE(sum) + KLD loss and gradients                        ref:vae-hpo.py:49-58
+//   loss  = sum bce(r,x) - 0.5*sum(1 + lv - mu^2 - e^lv)
+//   d_rec = (r-x)/max((1-r)r,1e-12)          [kLogitGrad: times r(1-r) -> d/d(logit)]
+//   d_mu  = mu ; d_lv = 0.5*(e^lv - 1)
+// One float4 per thread per iteration; per-thread -> warp shuffle -> block -> one
+// partial per block; the last block to finish adds the partials in index order.
+// ============================================================================
+constexpr int kLossThreads = 256;
+constexpr int kLossMaxBlocks = 1184;  // 148 SMs x 8 resident 256-thread blocks
+
+struct LossArgs {
+  const float* recon;  // [B*D] contiguous
+  const float* x;      // [B*D] contiguous
+  const float* mu;
+  const float* logvar;
+  int ld_ml;
+  int B, D, Z;
+  float* d_recon;   // [B*D] or NULL
+  float* d_mu;      // ld_dml or NULL
+  float* d_logvar;  // ld_dml or NULL
+  int ld_dml;
+  float* partials;        // [gridDim.x] scratch
+  unsigned int* ticket;   // scratch counter, zero before first use, self-resetting
+  float* loss_out;        // one float
+};
+
+template <bool kLogitGrad>
+__global__ void __launch_bounds__(kLossThreads) loss_bce_kl_kernel(LossArgs a) {
+  __shared__ float red[32];
+  __shared__ bool is_last;
+  const long long total = (long long)a.B * a.D;
+  const long long n4 = total >> 2;
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long gstride = (long long)gridDim.x * blockDim.x;
+  float acc = 0.f;
+
+  const float4* r4 = reinterpret_cast<const float4*>(a.recon);
+  const float4* x4 = reinterpret_cast<const float4*>(a.x);
+  float4* d4 = reinterpret_cast<float4*>(a.d_recon);
+  for (long long i = gtid; i < n4; i += gstride) {
+    const float4 r = __ldg(r4 + i);
+    const float4 x = __ldg(x4 + i);
+    acc += bce_term(r.x, x.x) + bce_term(r.y, x.y) + bce_term(r.z, x.z) + bce_term(r.w, x.w);
+    if (a.d_recon) {
+      float4 g = make_float4(bce_grad(r.x, x.x), bce_grad(r.y, x.y), bce_grad(r.z, x.z), bce_grad(r.w, x.w));
+      if (kLogitGrad) {
+        g.x = sigmoid_bwd(g.x, r.x);
+        g.y = sigmoid_bwd(g.y, r.y);
+        g.z = sigmoid_bwd(g.z, r.z);
+        g.w = sigmoid_bwd(g.w, r.w);
+      }
+      d4[i] = g;
+    }
+  }
+  for (long long i = (n4 << 2) + gtid; i < total; i += gstride) {  // ragged tail (B*D % 4)
+    const float r = a.recon[i], x = a.x[i];
+    acc += bce_term(r, x);
+    if (a.d_recon) {
+      float g = bce_grad(r, x);
+      a.d_recon[i] = kLogitGrad ? sigmoid_bwd(g, r) : g;
+    }
+  }
+  // KLD: one element per thread
+  const long long nk = (long long)a.B * a.Z;
+  for (long long i = gtid; i < nk; i += gstride) {
+    const int b = (int)(i / a.Z), j = (int)(i - (long long)b * a.Z);
+    const float mu = a.mu[(size_t)b * a.ld_ml + j];
+    const float lv = a.logvar[(size_t)b * a.ld_ml + j];
+    const float ev = expf(lv);
+    acc += -0.5f * (1.0f + lv - mu * mu - ev);
+    if (a.d_mu) a.d_mu[(size_t)b * a.ld_dml + j] = mu;
+    if (a.d_logvar) a.d_logvar[(size_t)b * a.ld_dml + j] = 0.5f * (ev - 1.0f);
+  }
+
+  const float bsum = block_sum(acc, red);
+  if (threadIdx.x == 0) {
+    a.partials[blockIdx.x] = bsum;
+    __threadfence();
+    const unsigned int done = atomicAdd(a.ticket, 1u);
+    is_last = (done == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    // fixed-order final sum: thread t adds partials t, t+256, ... then the block tree
+    float s = 0.f;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += blockDim.x) s += __ldcg(a.partials + i);
+    const float tot = block_sum(s, red);
+    if (threadIdx.x == 0) {
+      *a.loss_out = tot;
+      *a.ticket = 0;
+    }
+  }
+}
+
+inline int loss_grid(long long total_elems) {
+  long long blocks = (total_elems / 4 + kLossThreads - 1) / kLossThreads;
+  if (blocks < 1) blocks = 1;
+  if (blocks > kLossMaxBlocks) blocks = kLossMaxBlocks;
+  return (int)blocks;
+}
+
+// compat backward entry: da4 = d_recon * (1-r) * r ; dml_kl = [d_mu | d_logvar]
+__global__ void sigmoid_bwd_pack_kernel(const float* d_recon, const float* recon, long long n, float* da4,
+                                        const float* d_mu, const float* d_lv, int B, int Z, float* dml_kl) {
+  const long long gtid = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const long long gstride = (long long)gridDim.x * blockDim.x;
+  for (long long i = gtid; i < n; i += gstride) da4[i] = sigmoid_bwd(d_recon[i], recon[i]);
+  const long long nk = (long long)B * Z;
+  for (long long i = gtid; i < nk; i += gstride) {
+    const int b = (int)(i / Z), j = (int)(i - (long long)b * Z);
+    dml_kl[(size_t)b * 2 * Z + j] = d_mu ? d_mu[i] : 0.f;
+    dml_kl[(size_t)b * 2 * Z + Z + j] = d_lv ? d_lv[i] : 0.f;
+  }
+}
+
+// ============================================================================
+// Bias gradients: db[n] = sum_b dY[b,n] for up to 4 layers in one launch.
+// Block = 32 columns x 8 row-lanes; rows are summed in a fixed order.
+// ============================================================================
+struct ColsumJob {
+  const float* dy;
+  int ld;
+  int N;
+  float* out;
+  int block_begin;  // first blockIdx.x of this job
+};
+struct ColsumArgs {
+  ColsumJob job[4];
+  int njobs;
+  int B;
+};
+
+__global__ void __launch_bounds__(256) colsum_kernel(ColsumArgs a) {
+  __shared__ float s[8][33];
+  int j = 0;
+#pragma unroll
+  for (int q = 1; q < 4; ++q)
+    if (q < a.njobs && (int)blockIdx.x >= a.job[q].block_begin) j = q;
+  const ColsumJob job = a.job[j];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int n = ((int)blockIdx.x - job.block_begin) * 32 + tx;
+  float acc = 0.f;
+  if (n < job.N)
+    for (int b = ty; b < a.B; b += 8) acc += job.dy[(size_t)b * job.ld + n];
+  s[ty][tx] = acc;
+  __syncthreads();
+  if (ty == 0 && n < job.N) {
+    float t = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) t += s[q][tx];
+    job.out[n] = t;
+  }
+}
+
+// ============================================================================
+// Flat fused Adam (torch.optim.Adam semantics)   ref:vae-hpo.py:74
+//   g  = grad_scale * g_sum                (grad_scale = 1/group_size)
+//   m += (g - m)*(1-b1) ; v = v*b2 + (1-b2)*g*g
+//   p -= (lr/bc1) * m / (sqrt(v)/sqrt(bc2) + eps)
+// 4 reads + 3 writes of 4 bytes per element -> 28 B/element, HBM-bound.
+// Scalars come either from device state (t = adam_t + 1, advanced by the last
+// block) or from the host (stand-alone entry).
+// ============================================================================
+constexpr int kAdamThreads = 256;
+
+struct AdamArgs {
+  float* p;
+  const float* g;
+  float* m;
+  float* v;
+  long long n;  // multiple of 4 (flat buffers are padded)
+  StepState* st;  // NULL -> host scalars below
+  float step_size, bc2_sqrt, one_minus_b1, b2, one_minus_b2, eps;
+  float grad_scale;
+};
+
+__device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, float step_size, float bc2_sqrt,
+                                          float omb1, float b2, float omb2, float eps) {
+  m = m + (g - m) * omb1;
+  v = v * b2 + omb2 * g * g;
+  const float denom = __fdiv_rn(__fsqrt_rn(v), bc2_sqrt) + eps;
+  p = p - step_size * __fdiv_rn(m, denom);
+}
+
+__global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
+  __shared__ float sc[6];
+  if (a.st != nullptr) {
+    if (threadIdx.x == 0) {
+      const double t = (double)(a.st->adam_t + 1);
+      const double bc1 = 1.0 - pow(a.st->beta1, t);
+      const double bc2 = 1.0 - pow(a.st->beta2, t);
+      sc[0] = (float)(a.st->lr / bc1);
+      sc[1] = (float)sqrt(bc2);
+      sc[2] = (float)(1.0 - a.st->beta1);
+      sc[3] = (float)a.st->beta2;
+      sc[4] = (float)(1.0 - a.st->beta2);
+      sc[5] = (float)a.st->eps;
+    }
+    __syncthreads();
+  } else if (threadIdx.x == 0) {
+    sc[0] = a.step_size; sc[1] = a.bc2_sqrt; sc[2] = a.one_minus_b1;
+    sc[3] = a.b2; sc[4] = a.one_minus_b2; sc[5] = a.eps;
+  }
+  __syncthreads();
+  const float step_size = sc[0], bc2_sqrt = sc[1], omb1 = sc[2], b2 = sc[3], omb2 = sc[4], eps = sc[5];
+  const float gs = a.grad_scale;
+
+  const long long n4 = a.n >> 2;
+  float4* p4 = reinterpret_cast<float4*>(a.p);
+  const float4* g4 = reinterpret_cast<const float4*>(a.g);
+  float4* m4 = reinterpret_cast<float4*>(a.m);
+  float4* v4 = reinterpret_cast<float4*>(a.v);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 p = p4[i], m = m4[i], v = v4[i];
+    float4 g = __ldg(g4 + i);
+    g.x *= gs; g.y *= gs; g.z *= gs; g.w *= gs;
+    adam_elem(p.x, g.x, m.x, v.x, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.y, g.y, m.y, v.y, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.z, g.z, m.z, v.z, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.w, g.w, m.w, v.w, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    p4[i] = p; m4[i] = m; v4[i] = v;
+  }
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < a.n;
+       i += (long long)gridDim.x * blockDim.x) {
+    float p = a.p[i], m = a.m[i], v = a.v[i];
+    adam_elem(p, a.g[i] * gs, m, v, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    a.p[i] = p; a.m[i] = m; a.v[i] = v;
+  }
+  if (a.st != nullptr) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence();
+      const unsigned int done = atomicAdd(&a.st->ticket_adam, 1u);
+      if (done == gridDim.x - 1) {
+        a.st->adam_t += 1;
+        a.st->ticket_adam = 0;
+        __threadfence();
+      }
+    }
+  }
+}
+
+inline int adam_grid(long long n, int sm_count) {
+  long long blocks = ((n >> 2) + kAdamThreads - 1) / kAdamThreads;
+  const long long cap = (long long)sm_count * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  return (int)blocks;
+}
+
+}  // namespace mdt

@@ -1,0 +1,768 @@
+// C-ABI of the B200-native VAE-HPO trial step (see include/mdt_b200.h).
+// Host side: the per-trial engine (workspaces, device-resident step state, CUDA
+// graph cache, NCCL subgroup all-reduce) and the stand-alone kernel entry points.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+#include <nccl.h>
+
+#include <cstdarg>
+#include <map>
+#include <tuple>
+#include <vector>
+
+#include "common.cuh"
+#include "elementwise.cuh"
+#include "gemm_simt.cuh"
+#include "gemm_tcgen05.cuh"
+
+using namespace mdt;
+
+// ------------------------------------------------------------------ NCCL (resolved at run time)
+// The library never links libnccl: it binds the instance torch already mapped
+// (nvidia/nccl/lib/libnccl.so.2) so the communicator handed over by
+// ProcessGroupNCCL and the functions called on it come from the same build.
+namespace {
+struct NcclApi {
+  ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*Broadcast)(const void*, void*, size_t, ncclDataType_t, int, ncclComm_t, cudaStream_t) = nullptr;
+  const char* (*GetErrorString)(ncclResult_t) = nullptr;
+  bool tried = false, ok = false;
+};
+NcclApi g_nccl;
+
+int load_nccl() {
+  if (g_nccl.ok) return MDT_OK;
+  if (!g_nccl.tried) {
+    g_nccl.tried = true;
+    void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) {
+      const char* p = getenv("MDT_NCCL_LIB");
+      if (p) h = dlopen(p, RTLD_NOW | RTLD_GLOBAL);
+    }
+    if (!h) h = RTLD_DEFAULT;
+    g_nccl.AllReduce = reinterpret_cast<decltype(g_nccl.AllReduce)>(dlsym(h, "ncclAllReduce"));
+    g_nccl.Broadcast = reinterpret_cast<decltype(g_nccl.Broadcast)>(dlsym(h, "ncclBroadcast"));
+    g_nccl.GetErrorString = reinterpret_cast<decltype(g_nccl.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+    g_nccl.ok = g_nccl.AllReduce && g_nccl.Broadcast && g_nccl.GetErrorString;
+  }
+  if (!g_nccl.ok)
+    return set_error(MDT_ERR_NCCL,
+                     "NCCL symbols not found in this process: import torch (CUDA build) first, or set MDT_NCCL_LIB");
+  return MDT_OK;
+}
+
+#define MDT_NCCL(expr)                                                                                   \
+  do {                                                                                                   \
+    ncclResult_t _r = (expr);                                                                            \
+    if (_r != ncclSuccess)                                                                               \
+      return set_error(MDT_ERR_NCCL, "%s failed: %s (%s:%d)", #expr, g_nccl.GetErrorString(_r), __FILE__, \
+                       __LINE__);                                                                        \
+  } while (0)
+
+// ------------------------------------------------------------------ per-device info + lazy scratch
+struct DeviceInfo {
+  bool init = false;
+  int sm_count = 0, max_threads_sm = 0, cc_major = 0, cc_minor = 0;
+  float* loss_partials = nullptr;  // scratch of the stand-alone loss entry
+  unsigned int* loss_ticket = nullptr;
+};
+DeviceInfo g_dev[64];
+
+int device_info(DeviceInfo** out) {
+  int dev = 0;
+  MDT_CUDA(cudaGetDevice(&dev));
+  MDT_CHECK(dev >= 0 && dev < 64, "device index %d out of range", dev);
+  DeviceInfo& d = g_dev[dev];
+  if (!d.init) {
+    MDT_CUDA(cudaDeviceGetAttribute(&d.sm_count, cudaDevAttrMultiProcessorCount, dev));
+    MDT_CUDA(cudaDeviceGetAttribute(&d.max_threads_sm, cudaDevAttrMaxThreadsPerMultiProcessor, dev));
+    MDT_CUDA(cudaDeviceGetAttribute(&d.cc_major, cudaDevAttrComputeCapabilityMajor, dev));
+    MDT_CUDA(cudaDeviceGetAttribute(&d.cc_minor, cudaDevAttrComputeCapabilityMinor, dev));
+    d.init = true;
+  }
+  *out = &d;
+  return MDT_OK;
+}
+
+size_t align_up(size_t n, size_t a) { return (n + a - 1) / a * a; }
+}  // namespace
+
+// ------------------------------------------------------------------ engine
+struct mdt_engine {
+  mdt_cfg cfg;
+  int D, H, Z, Bmax;
+  Layout L;
+  DeviceInfo* dev = nullptr;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bool own_stream = false;
+  ncclComm_t comm = nullptr;
+  int gsize = 1, grank = 0;
+
+  float *params = nullptr, *grads = nullptr, *m = nullptr, *v = nullptr;
+  bool bound = false;
+
+  char* slab = nullptr;
+  float *x_stage, *eps_stage, *h1, *ml, *eps, *sd, *z, *h3, *recon, *da4, *da3, *dz, *dml_kl, *dml, *da1;
+  float *loss_partials, *loss_dev;
+  unsigned int* loss_ticket;
+  StepState* st;
+  float* loss_pinned = nullptr;
+  int last_B = 0;  // batch of the activations currently held
+
+  Tc05Plan* tc = nullptr;  // tcgen05 path state (tensor maps, transposed shadows); NULL in fp32 mode
+
+  struct Graph { cudaGraphExec_t exec; long long kernels; };
+  std::map<std::tuple<int, int, int>, Graph> graphs;
+
+  long long launch_count = 0;  // kernels enqueued (a graph launch adds the kernels it holds)
+  bool prof_on = false;        // per-kernel event timing (mdt_engine_profile_step)
+  std::vector<std::pair<const char*, cudaEvent_t>> prof_marks;
+
+  float* seg(float* base, int s) const { return base + L.off[s]; }
+};
+
+namespace {
+
+// Book-keeping after every kernel launch: count it and, in profiling mode, drop a timing event.
+int note_launch(mdt_engine* e, const char* label) {
+  MDT_CUDA(cudaGetLastError());
+  e->launch_count += 1;
+  if (e->prof_on) {
+    cudaEvent_t ev;
+    MDT_CUDA(cudaEventCreate(&ev));
+    MDT_CUDA(cudaEventRecord(ev, e->stream));
+    e->prof_marks.emplace_back(label, ev);
+  }
+  return MDT_OK;
+}
+
+__global__ void spin_kernel(long long ns) {
+  unsigned long long t0, t1;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+  do {
+    __nanosleep(1000);
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+  } while ((long long)(t1 - t0) < ns);
+}
+
+int carve_workspace(mdt_engine* e) {
+  const size_t B = e->Bmax, D = e->D, H = e->H, Z = e->Z;
+  struct Item { float** p; size_t n; };
+  std::vector<Item> items = {
+      {&e->x_stage, B * D}, {&e->eps_stage, B * Z}, {&e->h1, B * H}, {&e->ml, B * 2 * Z}, {&e->eps, B * Z},
+      {&e->sd, B * Z}, {&e->z, B * Z}, {&e->h3, B * H}, {&e->recon, B * D}, {&e->da4, B * D}, {&e->da3, B * H},
+      {&e->dz, B * Z}, {&e->dml_kl, B * 2 * Z}, {&e->dml, B * 2 * Z}, {&e->da1, B * H},
+      {&e->loss_partials, (size_t)kLossMaxBlocks}, {&e->loss_dev, 64},
+  };
+  size_t bytes = 0;
+  for (auto& it : items) bytes += align_up(it.n * sizeof(float), 256);
+  bytes += 256 /*ticket*/ + align_up(sizeof(StepState), 256);
+  MDT_CUDA(cudaMalloc(&e->slab, bytes));
+  MDT_CUDA(cudaMemsetAsync(e->slab, 0, bytes, e->stream));
+  char* p = e->slab;
+  for (auto& it : items) {
+    *it.p = reinterpret_cast<float*>(p);
+    p += align_up(it.n * sizeof(float), 256);
+  }
+  e->loss_ticket = reinterpret_cast<unsigned int*>(p);
+  p += 256;
+  e->st = reinterpret_cast<StepState*>(p);
+  return MDT_OK;
+}
+
+// ---- enqueue helpers (no synchronisation; safe under stream capture) --------------------------
+// GEMM launch + book-keeping in one statement.
+#define MDT_GEMM_SIMT(label, AK, BK, ...)                      \
+  do {                                                         \
+    MDT_CUDA((launch_gemm_simt<AK, BK>(__VA_ARGS__, s)));      \
+    MDT_TRY(note_launch(e, label));                            \
+  } while (0)
+
+int enqueue_forward_fp32(mdt_engine* e, const float* x, int B, const float* eps_in, bool decode_only) {
+  cudaStream_t s = e->stream;
+  const int D = e->D, H = e->H, Z = e->Z;
+  const float* P = e->params;
+  if (!decode_only) {
+    MDT_GEMM_SIMT("fc1_fwd", true, true, x, P + e->L.off[W1], B, H, D, D, D,
+                  EpiBiasAct{e->h1, H, P + e->L.off[B1], MDT_ACT_RELU});
+    MDT_GEMM_SIMT("fc2x_fwd", true, true, e->h1, P + e->L.off[W2X], B, 2 * Z, H, H, H,
+                  EpiBiasAct{e->ml, 2 * Z, P + e->L.off[B2X], MDT_ACT_NONE});
+    ReparamArgs a{};
+    a.mu = e->ml; a.logvar = e->ml + Z; a.ld_ml = 2 * Z; a.eps_in = eps_in; a.st = e->st;
+    torch_randn_policy((long long)B * Z, e->dev->sm_count, e->dev->max_threads_sm, &a.S, &a.offset_inc);
+    a.B = B; a.Z = Z; a.z = e->z; a.ld_z = Z; a.eps_out = e->eps; a.std_out = e->sd;
+    const int blocks = (int)(((long long)B * Z + 255) / 256);
+    reparam_kernel<<<blocks < 1 ? 1 : blocks, 256, 0, s>>>(a);
+    MDT_TRY(note_launch(e, "reparam"));
+  }
+  MDT_GEMM_SIMT("fc3_fwd", true, true, e->z, P + e->L.off[W3], B, H, Z, Z, Z,
+                EpiBiasAct{e->h3, H, P + e->L.off[B3], MDT_ACT_RELU});
+  MDT_GEMM_SIMT("fc4_fwd", true, true, e->h3, P + e->L.off[W4], B, D, H, H, H,
+                EpiBiasAct{e->recon, D, P + e->L.off[B4], MDT_ACT_SIGMOID});
+  return MDT_OK;
+}
+
+int enqueue_loss(mdt_engine* e, const float* x, int B, bool with_grads) {
+  LossArgs a{};
+  a.recon = e->recon; a.x = x; a.mu = e->ml; a.logvar = e->ml + e->Z; a.ld_ml = 2 * e->Z;
+  a.B = B; a.D = e->D; a.Z = e->Z;
+  if (with_grads) { a.d_recon = e->da4; a.d_mu = e->dml_kl; a.d_logvar = e->dml_kl + e->Z; a.ld_dml = 2 * e->Z; }
+  a.partials = e->loss_partials; a.ticket = e->loss_ticket; a.loss_out = e->loss_dev;
+  loss_bce_kl_kernel<true><<<loss_grid((long long)B * e->D), kLossThreads, 0, e->stream>>>(a);
+  return note_launch(e, "loss_bce_kl");
+}
+
+// Backward from da4 (= dL/d logits of fc4) and dml_kl (= direct dL/d[mu|logvar]).
+int enqueue_backward_fp32(mdt_engine* e, const float* x, int B) {
+  cudaStream_t s = e->stream;
+  const int D = e->D, H = e->H, Z = e->Z;
+  const float* P = e->params;
+  float* G = e->grads;
+  // fc4
+  MDT_GEMM_SIMT("fc4_dW", false, false, e->da4, e->h3, D, H, B, D, H, EpiStore{G + e->L.off[W4], H});
+  MDT_GEMM_SIMT("fc4_dX", true, false, e->da4, P + e->L.off[W4], B, H, D, D, H, EpiReluMask{e->da3, H, e->h3, H});
+  // fc3
+  MDT_GEMM_SIMT("fc3_dW", false, false, e->da3, e->z, H, Z, B, H, Z, EpiStore{G + e->L.off[W3], Z});
+  MDT_GEMM_SIMT("fc3_dX", true, false, e->da3, P + e->L.off[W3], B, Z, H, H, Z, EpiStore{e->dz, Z});
+  {
+    const int blocks = (int)(((long long)B * Z + 255) / 256);
+    reparam_bwd_kernel<<<blocks < 1 ? 1 : blocks, 256, 0, s>>>(e->dz, Z, e->eps, e->sd, e->dml_kl, B, Z, e->dml);
+    MDT_TRY(note_launch(e, "reparam_bwd"));
+  }
+  // fc21 | fc22
+  MDT_GEMM_SIMT("fc2x_dW", false, false, e->dml, e->h1, 2 * Z, H, B, 2 * Z, H, EpiStore{G + e->L.off[W2X], H});
+  MDT_GEMM_SIMT("fc2x_dX", true, false, e->dml, P + e->L.off[W2X], B, H, 2 * Z, 2 * Z, H,
+                EpiReluMask{e->da1, H, e->h1, H});
+  // fc1 (no dX)
+  MDT_GEMM_SIMT("fc1_dW", false, false, e->da1, x, H, D, B, H, D, EpiStore{G + e->L.off[W1], D});
+  // bias gradients, one launch
+  ColsumArgs c{};
+  c.B = B; c.njobs = 4;
+  const float* dy[4] = {e->da4, e->da3, e->dml, e->da1};
+  const int nn[4] = {D, H, 2 * Z, H};
+  const int sg[4] = {B4, B3, B2X, B1};
+  int blk = 0;
+  for (int i = 0; i < 4; ++i) {
+    c.job[i] = ColsumJob{dy[i], nn[i], nn[i], G + e->L.off[sg[i]], blk};
+    blk += (nn[i] + 31) / 32;
+  }
+  colsum_kernel<<<blk, 256, 0, s>>>(c);
+  return note_launch(e, "bias_grads");
+}
+
+int enqueue_adam(mdt_engine* e, float grad_scale) {
+  AdamArgs a{};
+  a.p = e->params; a.g = e->grads; a.m = e->m; a.v = e->v; a.n = e->L.total; a.st = e->st; a.grad_scale = grad_scale;
+  adam_flat_kernel<<<adam_grid(a.n, e->dev->sm_count), kAdamThreads, 0, e->stream>>>(a);
+  return note_launch(e, "adam_flat");
+}
+
+int enqueue_forward(mdt_engine* e, const float* x, int B, const float* eps_in, bool decode_only) {
+  if (e->tc) return tc05_forward(e->tc, e->stream, x, B, eps_in, decode_only);
+  return enqueue_forward_fp32(e, x, B, eps_in, decode_only);
+}
+int enqueue_backward(mdt_engine* e, const float* x, int B) {
+  if (e->tc) return tc05_backward(e->tc, e->stream, x, B);
+  return enqueue_backward_fp32(e, x, B);
+}
+
+int check_batch(mdt_engine* e, int B) {
+  MDT_CHECK(e != nullptr, "engine is NULL");
+  if (!e->bound) return set_error(MDT_ERR_STATE, "mdt_engine_bind_buffers has not been called");
+  MDT_CHECK(B >= 0 && B <= e->Bmax, "batch %d outside [0, max_batch=%d]", B, e->Bmax);
+  return MDT_OK;
+}
+
+// Run `fn` through the CUDA-graph cache when enabled.
+template <class F>
+int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
+  if (!e->cfg.use_graph || e->prof_on) return fn();
+  auto key = std::make_tuple(kind, B, flag);
+  auto it = e->graphs.find(key);
+  if (it == e->graphs.end()) {
+    cudaGraph_t g = nullptr;
+    const long long before = e->launch_count;
+    MDT_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeRelaxed));
+    int r = fn();
+    cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
+    const long long kernels = e->launch_count - before;
+    e->launch_count = before;
+    if (r != MDT_OK) {
+      if (g) cudaGraphDestroy(g);
+      return r;
+    }
+    if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    cudaGraphExec_t ex = nullptr;
+    ce = cudaGraphInstantiate(&ex, g, 0);
+    cudaGraphDestroy(g);
+    if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
+    it = e->graphs.emplace(key, mdt_engine::Graph{ex, kernels}).first;
+  }
+  MDT_CUDA(cudaGraphLaunch(it->second.exec, e->stream));
+  e->launch_count += it->second.kernels;
+  return MDT_OK;
+}
+
+int stage_inputs(mdt_engine* e, const float** x, int B, const float** eps, cudaMemcpyKind kind) {
+  if (*x != e->x_stage && B > 0)
+    MDT_CUDA(cudaMemcpyAsync(e->x_stage, *x, (size_t)B * e->D * sizeof(float), kind, e->stream));
+  *x = e->x_stage;
+  if (*eps != nullptr) {
+    if (*eps != e->eps_stage && B > 0)
+      MDT_CUDA(cudaMemcpyAsync(e->eps_stage, *eps, (size_t)B * e->Z * sizeof(float), kind, e->stream));
+    *eps = e->eps_stage;
+  }
+  return MDT_OK;
+}
+
+int allreduce_grads(mdt_engine* e) {
+  if (e->gsize <= 1) return MDT_OK;
+  if (e->comm == nullptr)
+    return set_error(MDT_ERR_STATE, "group_size %d but no NCCL communicator was given to mdt_engine_create", e->gsize);
+  MDT_TRY(load_nccl());
+  // two buckets in DDP's order (fc4 first, then the rest): both are contiguous ranges of the flat buffer
+  const int64_t split = e->L.off[W4];
+  MDT_NCCL(g_nccl.AllReduce(e->grads + split, e->grads + split, (size_t)(e->L.total - split), ncclFloat, ncclSum, e->comm, e->stream));
+  MDT_NCCL(g_nccl.AllReduce(e->grads, e->grads, (size_t)split, ncclFloat, ncclSum, e->comm, e->stream));
+  return MDT_OK;
+}
+
+int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
+  e->last_B = B;
+  if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
+  const float gscale = 1.0f / (float)e->gsize;
+  if (e->gsize == 1) {
+    return run_cached(e, /*kind=*/0, B, eps != nullptr, [&]() -> int {
+      MDT_TRY(enqueue_forward(e, x, B, eps, false));
+      MDT_TRY(enqueue_loss(e, x, B, true));
+      MDT_TRY(enqueue_backward(e, x, B));
+      return enqueue_adam(e, gscale);
+    });
+  }
+  MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int {
+    MDT_TRY(enqueue_forward(e, x, B, eps, false));
+    MDT_TRY(enqueue_loss(e, x, B, true));
+    return enqueue_backward(e, x, B);
+  }));
+  MDT_TRY(allreduce_grads(e));
+  return run_cached(e, /*kind=*/2, 0, 0, [&]() -> int { return enqueue_adam(e, gscale); });
+}
+
+}  // namespace
+
+// =================================================================== C ABI
+extern "C" {
+
+int mdt_version(void) { return MDT_VERSION; }
+const char* mdt_last_error(void) { return g_last_error; }
+
+int mdt_param_layout(const mdt_cfg* cfg, int64_t offsets[MDT_NUM_SEGMENTS], int64_t numels[MDT_NUM_SEGMENTS],
+                     int64_t* total) {
+  MDT_CHECK(cfg && cfg->in_dim > 0 && cfg->hidden > 0 && cfg->latent > 0, "bad cfg");
+  const Layout L = make_layout(cfg->in_dim, cfg->hidden, cfg->latent);
+  for (int i = 0; i < kNumSeg; ++i) {
+    if (offsets) offsets[i] = L.off[i];
+    if (numels) numels[i] = L.numel[i];
+  }
+  if (total) *total = L.total;
+  return MDT_OK;
+}
+
+int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int group_rank, void* stream,
+                      mdt_engine** out) {
+  MDT_CHECK(cfg && out, "cfg/out is NULL");
+  MDT_CHECK(cfg->in_dim > 0 && cfg->hidden > 0 && cfg->latent > 0 && cfg->max_batch > 0, "bad dims in cfg");
+  MDT_CHECK(cfg->in_dim % 4 == 0 && cfg->hidden % 4 == 0 && cfg->latent % 4 == 0,
+            "in_dim, hidden and latent must be multiples of 4 (16-byte rows)");
+  MDT_CHECK(group_size >= 1 && group_rank >= 0 && group_rank < group_size, "bad group size/rank");
+  MDT_CHECK(cfg->gemm_mode >= MDT_GEMM_FP32 && cfg->gemm_mode <= MDT_GEMM_TF32X3, "unknown gemm_mode %d", cfg->gemm_mode);
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  if (cfg->gemm_mode != MDT_GEMM_FP32 && di->cc_major != 10)
+    return set_error(MDT_ERR_UNSUPPORTED, "tcgen05 GEMM modes need an sm_100 device (found sm_%d%d)", di->cc_major, di->cc_minor);
+  mdt_engine* e = new mdt_engine();
+  e->cfg = *cfg;
+  e->D = cfg->in_dim; e->H = cfg->hidden; e->Z = cfg->latent; e->Bmax = cfg->max_batch;
+  e->L = make_layout(e->D, e->H, e->Z);
+  e->dev = di;
+  cudaGetDevice(&e->device);
+  e->comm = reinterpret_cast<ncclComm_t>(nccl_comm);
+  e->gsize = group_size; e->grank = group_rank;
+  if (stream) {
+    e->stream = reinterpret_cast<cudaStream_t>(stream);
+  } else {
+    // a *blocking* stream: implicitly ordered with the legacy default stream torch uses by default,
+    // yet capturable into a CUDA graph (the legacy stream is not)
+    cudaError_t ce = cudaStreamCreate(&e->stream);
+    if (ce != cudaSuccess) { delete e; return set_error(MDT_ERR_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce)); }
+    e->own_stream = true;
+  }
+  int r = carve_workspace(e);
+  if (r == MDT_OK) {
+    cudaError_t ce = cudaMallocHost(&e->loss_pinned, 256);
+    if (ce != cudaSuccess) r = set_error(MDT_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(ce));
+  }
+  if (r == MDT_OK) {
+    mdt_adam h{1e-3, 0.9, 0.999, 1e-8};
+    r = mdt_engine_set_adam(e, &h, 0);
+  }
+  if (r != MDT_OK) { mdt_engine_destroy(e); return r; }
+  *out = e;
+  return MDT_OK;
+}
+
+void mdt_engine_destroy(mdt_engine* e) {
+  if (!e) return;
+  cudaStreamSynchronize(e->stream);
+  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
+  if (e->tc) tc05_destroy(e->tc);
+  if (e->slab) cudaFree(e->slab);
+  if (e->loss_pinned) cudaFreeHost(e->loss_pinned);
+  if (e->own_stream) cudaStreamDestroy(e->stream);
+  delete e;
+}
+
+int mdt_engine_stream(mdt_engine* e, void** stream) {
+  MDT_CHECK(e && stream, "NULL argument");
+  *stream = e->stream;
+  return MDT_OK;
+}
+
+int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* exp_avg, float* exp_avg_sq,
+                            size_t numel) {
+  MDT_CHECK(e && params && grads && exp_avg && exp_avg_sq, "NULL buffer");
+  MDT_CHECK((int64_t)numel == e->L.total, "numel %zu != layout total %lld", numel, (long long)e->L.total);
+  for (const void* p : {(const void*)params, (const void*)grads, (const void*)exp_avg, (const void*)exp_avg_sq})
+    MDT_CHECK(reinterpret_cast<uintptr_t>(p) % 128 == 0, "flat buffers must be 128-byte aligned");
+  e->params = params; e->grads = grads; e->m = exp_avg; e->v = exp_avg_sq;
+  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
+  e->graphs.clear();
+  if (e->cfg.gemm_mode != MDT_GEMM_FP32) {
+    if (e->tc) { tc05_destroy(e->tc); e->tc = nullptr; }
+    Tc05Buffers b{};
+    b.params = params; b.grads = grads; b.L = e->L; b.D = e->D; b.H = e->H; b.Z = e->Z; b.Bmax = e->Bmax;
+    b.x_stage = e->x_stage; b.h1 = e->h1; b.ml = e->ml; b.eps = e->eps; b.sd = e->sd; b.z = e->z; b.h3 = e->h3;
+    b.recon = e->recon; b.da4 = e->da4; b.da3 = e->da3; b.dz = e->dz; b.dml_kl = e->dml_kl; b.dml = e->dml; b.da1 = e->da1;
+    b.st = e->st; b.sm_count = e->dev->sm_count; b.max_threads_sm = e->dev->max_threads_sm;
+    b.split3 = (e->cfg.gemm_mode == MDT_GEMM_TF32X3);
+    MDT_TRY(tc05_create(&b, e->stream, &e->tc));
+  }
+  e->bound = true;
+  return MDT_OK;
+}
+
+int mdt_engine_broadcast_params(mdt_engine* e) {
+  MDT_TRY(check_batch(e, 0));
+  if (e->gsize <= 1) return MDT_OK;
+  if (!e->comm) return set_error(MDT_ERR_STATE, "no NCCL communicator");
+  MDT_TRY(load_nccl());
+  MDT_NCCL(g_nccl.Broadcast(e->params, e->params, (size_t)e->L.total, ncclFloat, 0, e->comm, e->stream));
+  if (e->tc) MDT_TRY(tc05_params_changed(e->tc, e->stream));
+  return MDT_OK;
+}
+
+int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_steps) {
+  MDT_CHECK(e && h, "NULL argument");
+  struct { long long t; double lr, b1, b2, eps; } host{completed_steps, h->lr, h->beta1, h->beta2, h->eps};
+  MDT_CUDA(cudaMemcpyAsync(&e->st->adam_t, &host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
+  MDT_CUDA(cudaStreamSynchronize(e->stream));  // `host` lives on this stack frame
+  return MDT_OK;
+}
+
+int mdt_engine_set_rng(mdt_engine* e, uint64_t philox_seed, uint64_t philox_offset) {
+  MDT_CHECK(e, "NULL engine");
+  MDT_CHECK(philox_offset % 4 == 0, "philox offset must be a multiple of 4 (torch keeps it so)");
+  unsigned long long host[2] = {philox_seed, philox_offset};
+  MDT_CUDA(cudaMemcpyAsync(&e->st->philox_seed, host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  return MDT_OK;
+}
+
+int mdt_engine_get_state(mdt_engine* e, int64_t* completed_steps, uint64_t* philox_offset) {
+  MDT_CHECK(e, "NULL engine");
+  StepState h;
+  MDT_CUDA(cudaMemcpyAsync(&h, e->st, sizeof(h), cudaMemcpyDeviceToHost, e->stream));
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  if (completed_steps) *completed_steps = h.adam_t;
+  if (philox_offset) *philox_offset = h.philox_offset;
+  return MDT_OK;
+}
+
+int mdt_engine_input_buffer(mdt_engine* e, float** x_stage) {
+  MDT_CHECK(e && x_stage, "NULL argument");
+  *x_stage = e->x_stage;
+  return MDT_OK;
+}
+
+int mdt_forward(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* recon, float* mu,
+                float* logvar) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x, "x is NULL");
+  e->last_B = batch;
+  if (batch == 0) return MDT_OK;
+  const float* eps = eps_or_null;
+  MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyDeviceToDevice));
+  MDT_TRY(run_cached(e, 3, batch, eps != nullptr, [&]() -> int { return enqueue_forward(e, x, batch, eps, false); }));
+  const size_t zb = e->Z * sizeof(float);
+  if (recon) MDT_CUDA(cudaMemcpyAsync(recon, e->recon, (size_t)batch * e->D * sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  if (mu) MDT_CUDA(cudaMemcpy2DAsync(mu, zb, e->ml, 2 * zb, zb, batch, cudaMemcpyDeviceToDevice, e->stream));
+  if (logvar) MDT_CUDA(cudaMemcpy2DAsync(logvar, zb, e->ml + e->Z, 2 * zb, zb, batch, cudaMemcpyDeviceToDevice, e->stream));
+  return MDT_OK;
+}
+
+int mdt_backward(mdt_engine* e, const float* d_recon, const float* d_mu, const float* d_logvar) {
+  MDT_TRY(check_batch(e, 0));
+  const int B = e->last_B;
+  if (B == 0) return MDT_OK;
+  MDT_CHECK(d_recon, "d_recon is NULL");
+  const long long n = (long long)B * e->D;
+  int blocks = (int)((n + 255) / 256);
+  if (blocks > e->dev->sm_count * 8) blocks = e->dev->sm_count * 8;
+  sigmoid_bwd_pack_kernel<<<blocks, 256, 0, e->stream>>>(d_recon, e->recon, n, e->da4, d_mu, d_logvar, B, e->Z, e->dml_kl);
+  MDT_TRY(note_launch(e, "sigmoid_bwd"));
+  if (e->tc) MDT_TRY(tc05_after_external_da4(e->tc, e->stream, B));
+  return run_cached(e, 4, B, 0, [&]() -> int { return enqueue_backward(e, e->x_stage, B); });
+}
+
+int mdt_allreduce_grads(mdt_engine* e) {
+  MDT_TRY(check_batch(e, 0));
+  return allreduce_grads(e);
+}
+
+int mdt_adam_step(mdt_engine* e, float grad_scale) {
+  MDT_TRY(check_batch(e, 0));
+  return enqueue_adam(e, grad_scale);
+}
+
+int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x || batch == 0, "x is NULL");
+  const float* eps = eps_or_null;
+  MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyDeviceToDevice));
+  if (batch == 0) MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));
+  MDT_TRY(train_step_device(e, x, batch, eps));
+  if (loss_out) MDT_CUDA(cudaMemcpyAsync(loss_out, e->loss_dev, sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  return MDT_OK;
+}
+
+int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
+                        float* loss_host) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x_host || batch == 0, "x_host is NULL");
+  const float* x = x_host;
+  const float* eps = eps_host_or_null;
+  // host buffers never alias the stage, so both copies are issued (H2D, async when pinned)
+  MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice));
+  if (batch == 0) MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));
+  MDT_TRY(train_step_device(e, x, batch, eps));
+  MDT_CUDA(cudaMemcpyAsync(e->loss_pinned, e->loss_dev, sizeof(float), cudaMemcpyDeviceToHost, e->stream));
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  if (loss_host) *loss_host = *e->loss_pinned;
+  return MDT_OK;
+}
+
+int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out, float* recon) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x || batch == 0, "x is NULL");
+  e->last_B = batch;
+  const float* eps = eps_or_null;
+  MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyDeviceToDevice));
+  if (batch == 0) {
+    MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));
+  } else {
+    MDT_TRY(run_cached(e, 5, batch, eps != nullptr, [&]() -> int {
+      MDT_TRY(enqueue_forward(e, x, batch, eps, false));
+      return enqueue_loss(e, x, batch, false);
+    }));
+  }
+  if (loss_out) MDT_CUDA(cudaMemcpyAsync(loss_out, e->loss_dev, sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  if (recon && batch > 0)
+    MDT_CUDA(cudaMemcpyAsync(recon, e->recon, (size_t)batch * e->D * sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  return MDT_OK;
+}
+
+int mdt_decode(mdt_engine* e, const float* z, int batch, float* recon) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(z && recon, "NULL argument");
+  if (batch == 0) return MDT_OK;
+  e->last_B = 0;  // activations no longer describe a full forward
+  MDT_CUDA(cudaMemcpyAsync(e->z, z, (size_t)batch * e->Z * sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  MDT_TRY(enqueue_forward(e, nullptr, batch, nullptr, true));
+  MDT_CUDA(cudaMemcpyAsync(recon, e->recon, (size_t)batch * e->D * sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+  return MDT_OK;
+}
+
+int mdt_engine_workspace(mdt_engine* e, const char* name, float** ptr, int* ld) {
+  MDT_CHECK(e && name && ptr, "NULL argument");
+  struct { const char* n; float* p; int ld; } tab[] = {
+      {"x", e->x_stage, e->D}, {"h1", e->h1, e->H}, {"ml", e->ml, 2 * e->Z}, {"eps", e->eps, e->Z}, {"std", e->sd, e->Z},
+      {"z", e->z, e->Z}, {"h3", e->h3, e->H}, {"recon", e->recon, e->D}, {"da4", e->da4, e->D}, {"da3", e->da3, e->H},
+      {"dz", e->dz, e->Z}, {"dml_kl", e->dml_kl, 2 * e->Z}, {"dml", e->dml, 2 * e->Z}, {"da1", e->da1, e->H},
+      {"loss", e->loss_dev, 1},
+  };
+  for (auto& t : tab)
+    if (strcmp(t.n, name) == 0) {
+      *ptr = t.p;
+      if (ld) *ld = t.ld;
+      return MDT_OK;
+    }
+  return set_error(MDT_ERR_INVALID, "unknown workspace '%s'", name);
+}
+
+int mdt_engine_launch_count(mdt_engine* e, int64_t* kernels) {
+  MDT_CHECK(e && kernels, "NULL argument");
+  *kernels = e->launch_count;
+  return MDT_OK;
+}
+
+int mdt_engine_profile_step(mdt_engine* e, const float* x, int batch, int iters, char* out, size_t out_len) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x && out && out_len > 0 && iters > 0 && batch > 0, "bad argument");
+  MDT_CHECK(e->gsize == 1, "profile_step times the single-GPU step only");
+  const float* eps = nullptr;
+  MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyDeviceToDevice));
+  std::vector<const char*> names;
+  std::vector<double> ms;
+  e->prof_on = true;
+  int rc = MDT_OK;
+  for (int it = 0; it < iters && rc == MDT_OK; ++it) {
+    e->prof_marks.clear();
+    // keep the GPU busy while the host enqueues the whole step, so intervals are device time, not launch time
+    spin_kernel<<<1, 1, 0, e->stream>>>(300000);
+    rc = note_launch(e, "_start");
+    if (rc == MDT_OK) rc = train_step_device(e, x, batch, nullptr);
+    if (rc == MDT_OK && cudaStreamSynchronize(e->stream) != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "sync failed in profile_step");
+    if (rc == MDT_OK) {
+      if (names.empty()) {
+        for (size_t i = 1; i < e->prof_marks.size(); ++i) names.push_back(e->prof_marks[i].first);
+        ms.assign(names.size(), 0.0);
+      }
+      for (size_t i = 1; i < e->prof_marks.size() && i - 1 < ms.size(); ++i) {
+        float t = 0.f;
+        cudaEventElapsedTime(&t, e->prof_marks[i - 1].second, e->prof_marks[i].second);
+        ms[i - 1] += t;
+      }
+    }
+    for (auto& m : e->prof_marks) cudaEventDestroy(m.second);
+    e->prof_marks.clear();
+  }
+  e->prof_on = false;
+  MDT_TRY(rc);
+  size_t pos = 0;
+  out[0] = 0;
+  for (size_t i = 0; i < names.size(); ++i) {
+    int w = snprintf(out + pos, out_len - pos, "%s %.6f\n", names[i], ms[i] / iters);
+    if (w < 0 || (size_t)w >= out_len - pos) return set_error(MDT_ERR_INVALID, "profile buffer too small");
+    pos += (size_t)w;
+  }
+  return MDT_OK;
+}
+
+// ------------------------------------------------------------------ stand-alone kernels
+
+int mdt_adam_flat(float* p, const float* g, float* m, float* v, size_t n, const mdt_adam* h, int64_t step,
+                  float grad_scale, void* stream) {
+  MDT_CHECK(p && g && m && v && h, "NULL argument");
+  MDT_CHECK(step >= 1, "step is 1-based");
+  for (const void* q : {(const void*)p, (const void*)g, (const void*)m, (const void*)v})
+    MDT_CHECK(reinterpret_cast<uintptr_t>(q) % 16 == 0, "buffers must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  if (n == 0) return MDT_OK;
+  AdamArgs a{};
+  a.p = p; a.g = g; a.m = m; a.v = v; a.n = (long long)n; a.st = nullptr; a.grad_scale = grad_scale;
+  const double bc1 = 1.0 - pow(h->beta1, (double)step), bc2 = 1.0 - pow(h->beta2, (double)step);
+  a.step_size = (float)(h->lr / bc1);
+  a.bc2_sqrt = (float)sqrt(bc2);
+  a.one_minus_b1 = (float)(1.0 - h->beta1);
+  a.b2 = (float)h->beta2;
+  a.one_minus_b2 = (float)(1.0 - h->beta2);
+  a.eps = (float)h->eps;
+  adam_flat_kernel<<<adam_grid(a.n, di->sm_count), kAdamThreads, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
+int mdt_reparam(const float* mu, const float* logvar, int ld_ml, const float* eps_in, uint64_t seed, uint64_t offset,
+                int batch, int latent, float* z, int ld_z, float* eps_out, void* stream) {
+  MDT_CHECK(mu && logvar && z, "NULL argument");
+  MDT_CHECK(batch >= 0 && latent > 0 && ld_ml >= latent && ld_z >= latent, "bad shape");
+  MDT_CHECK(offset % 4 == 0, "philox offset must be a multiple of 4");
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  if (batch == 0) return MDT_OK;
+  ReparamArgs a{};
+  a.mu = mu; a.logvar = logvar; a.ld_ml = ld_ml; a.eps_in = eps_in; a.st = nullptr; a.seed = seed; a.offset = offset;
+  torch_randn_policy((long long)batch * latent, di->sm_count, di->max_threads_sm, &a.S, &a.offset_inc);
+  a.B = batch; a.Z = latent; a.z = z; a.ld_z = ld_z; a.eps_out = eps_out; a.std_out = nullptr;
+  long long blocks = ((long long)batch * latent + 255) / 256;
+  if (blocks > di->sm_count * 8) blocks = di->sm_count * 8;
+  reparam_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
+int mdt_loss_bce_kl(const float* recon, const float* x, const float* mu, const float* logvar, int batch, int in_dim,
+                    int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar, void* stream) {
+  MDT_CHECK(recon && x && mu && logvar && loss_out, "NULL argument");
+  MDT_CHECK(batch >= 0 && in_dim > 0 && latent > 0, "bad shape");
+  for (const void* q : {(const void*)recon, (const void*)x, (const void*)d_recon})
+    MDT_CHECK(reinterpret_cast<uintptr_t>(q) % 16 == 0, "recon/x/d_recon must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (di->loss_partials == nullptr) {
+    MDT_CUDA(cudaMalloc(&di->loss_partials, kLossMaxBlocks * sizeof(float)));
+    MDT_CUDA(cudaMalloc(&di->loss_ticket, 256));
+    MDT_CUDA(cudaMemset(di->loss_ticket, 0, 256));
+  }
+  LossArgs a{};
+  a.recon = recon; a.x = x; a.mu = mu; a.logvar = logvar; a.ld_ml = latent; a.B = batch; a.D = in_dim; a.Z = latent;
+  a.d_recon = d_recon; a.d_mu = d_mu; a.d_logvar = d_logvar; a.ld_dml = latent;
+  a.partials = di->loss_partials; a.ticket = di->loss_ticket; a.loss_out = loss_out;
+  loss_bce_kl_kernel<false><<<loss_grid((long long)batch * in_dim), kLossThreads, 0, s>>>(a);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
+int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode, float* y,
+               void* stream) {
+  MDT_CHECK(x && w && y, "NULL argument");
+  MDT_CHECK(M >= 0 && N > 0 && K > 0, "bad shape");
+  MDT_CHECK(act >= MDT_ACT_NONE && act <= MDT_ACT_SIGMOID, "bad act");
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (M == 0) return MDT_OK;
+  if (gemm_mode == MDT_GEMM_FP32) {
+    MDT_CUDA((launch_gemm_simt<true, true>(x, w, M, N, K, K, K, EpiBiasAct{y, N, b, act}, s)));
+    return MDT_OK;
+  }
+  MDT_CHECK(gemm_mode == MDT_GEMM_TF32 || gemm_mode == MDT_GEMM_TF32X3, "unknown gemm_mode %d", gemm_mode);
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  if (di->cc_major != 10) return set_error(MDT_ERR_UNSUPPORTED, "tcgen05 GEMM needs an sm_100 device");
+  return tc05_linear(x, w, b, M, N, K, act, gemm_mode == MDT_GEMM_TF32X3, y, s);
+}
+
+int mdt_allreduce_bench(void* nccl_comm, void* buf, size_t bytes, int iters, void* stream, double* seconds) {
+  MDT_CHECK(nccl_comm && buf && seconds && iters > 0 && bytes % 4 == 0, "bad argument");
+  MDT_TRY(load_nccl());
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  ncclComm_t comm = reinterpret_cast<ncclComm_t>(nccl_comm);
+  cudaEvent_t e0, e1;
+  MDT_CUDA(cudaEventCreate(&e0));
+  MDT_CUDA(cudaEventCreate(&e1));
+  MDT_NCCL(g_nccl.AllReduce(buf, buf, bytes / 4, ncclFloat, ncclSum, comm, s));  // warm-up
+  MDT_CUDA(cudaEventRecord(e0, s));
+  for (int i = 0; i < iters; ++i) MDT_NCCL(g_nccl.AllReduce(buf, buf, bytes / 4, ncclFloat, ncclSum, comm, s));
+  MDT_CUDA(cudaEventRecord(e1, s));
+  MDT_CUDA(cudaEventSynchronize(e1));
+  float ms = 0.f;
+  MDT_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  *seconds = (double)ms * 1e-3 / iters;
+  return MDT_OK;
+}
+
+}  // extern "C"

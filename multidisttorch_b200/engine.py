@@ -1,0 +1,288 @@
+"""Python handle on one trial's B200 engine (host side of the C-ABI).
+
+Mirrors what ref:vae-hpo.py:129-131 builds -- ``VAE().to(device)`` wrapped in
+``DistributedDataParallel(process_group=group)`` plus ``optim.Adam(lr=1e-3)`` --
+as ONE object that owns four flat fp32 device buffers (params, grads, exp_avg,
+exp_avg_sq) and drives the hand-written sm_100a kernels through ctypes.  torch
+is used for device memory, streams and torch.distributed only."""
+import ctypes as C
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import MDT_GEMM, SEGMENTS, check, mdt_adam, mdt_cfg
+
+# reference parameter names, ref:vae-hpo.py:23-27
+REF_NAMES = ("fc1.weight", "fc1.bias", "fc21.weight", "fc21.bias", "fc22.weight", "fc22.bias",
+             "fc3.weight", "fc3.bias", "fc4.weight", "fc4.bias")
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    return C.c_void_p(t.data_ptr())
+
+
+def nccl_comm_ptr(group, device):
+    """ncclComm_t of ``group`` as an integer (torch owns it; never free it)."""
+    backend = group._get_backend(torch.device("cuda", device.index))
+    if not hasattr(backend, "_comm_ptr"):
+        raise RuntimeError("this torch build does not expose ProcessGroupNCCL._comm_ptr()")
+    try:
+        return int(backend._comm_ptr())
+    except Exception:
+        # communicator not created yet (process group made without device_id): one tiny collective creates it
+        t = torch.zeros(1, device=device)
+        dist.all_reduce(t, group=group)
+        torch.cuda.synchronize(device)
+        return int(backend._comm_ptr())
+
+
+class VAEEngine:
+    def __init__(self, in_dim=784, hidden=400, latent=20, max_batch=128, gemm_mode="fp32", use_graph=True,
+                 group=None, device=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+        if not torch.cuda.is_available():
+            raise RuntimeError("multidisttorch_b200.VAEEngine needs a CUDA device; there is no CPU path")
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.D, self.H, self.Z, self.max_batch = in_dim, hidden, latent, max_batch
+        self.gemm_mode = gemm_mode
+        self.group = group
+        self.group_size = dist.get_world_size(group) if (group is not None and dist.is_initialized()) else 1
+        self.group_rank = dist.get_rank(group) if self.group_size > 1 else 0
+        self.cfg = mdt_cfg(in_dim, hidden, latent, max_batch, MDT_GEMM[gemm_mode], int(bool(use_graph)))
+        off = (C.c_int64 * 8)()
+        num = (C.c_int64 * 8)()
+        tot = C.c_int64()
+        check(self.lib.mdt_param_layout(C.byref(self.cfg), off, num, C.byref(tot)))
+        self.offsets = dict(zip(SEGMENTS, (int(o) for o in off)))
+        self.numels = dict(zip(SEGMENTS, (int(n) for n in num)))
+        self.total = int(tot.value)
+        self.shapes = {"W1": (hidden, in_dim), "b1": (hidden,), "W2x": (2 * latent, hidden), "b2x": (2 * latent,),
+                       "W3": (hidden, latent), "b3": (hidden,), "W4": (in_dim, hidden), "b4": (in_dim,)}
+        self._h = None
+        with torch.cuda.device(self.device):
+            z = lambda: torch.zeros(self.total, dtype=torch.float32, device=self.device)
+            self.params, self.grads, self.exp_avg, self.exp_avg_sq = z(), z(), z(), z()
+            self._loss = torch.zeros(1, dtype=torch.float32, device=self.device)
+            comm = None
+            if self.group_size > 1:
+                comm = C.c_void_p(nccl_comm_ptr(group, self.device))
+            h = C.c_void_p()
+            torch.cuda.synchronize(self.device)
+            check(self.lib.mdt_engine_create(C.byref(self.cfg), comm, self.group_size, self.group_rank, None, C.byref(h)))
+            self._h = h
+            check(self.lib.mdt_engine_bind_buffers(h, _ptr(self.params), _ptr(self.grads), _ptr(self.exp_avg),
+                                                   _ptr(self.exp_avg_sq), self.total))
+            s = C.c_void_p()
+            check(self.lib.mdt_engine_stream(h, C.byref(s)))
+            self.stream = torch.cuda.ExternalStream(s.value, device=self.device)
+        self.set_adam(lr, betas, eps, 0)
+
+    # ------------------------------------------------------------------ buffers
+    def segment(self, buf, name):
+        o, n = self.offsets[name], self.numels[name]
+        return buf[o:o + n].view(self.shapes[name])
+
+    def named_parameter_views(self, buf=None):
+        """Reference-named views (fc1.weight ... fc4.bias) into a flat buffer."""
+        buf = self.params if buf is None else buf
+        Z = self.Z
+        seg = lambda n: self.segment(buf, n)
+        return {
+            "fc1.weight": seg("W1"), "fc1.bias": seg("b1"),
+            "fc21.weight": seg("W2x")[:Z], "fc21.bias": seg("b2x")[:Z],
+            "fc22.weight": seg("W2x")[Z:], "fc22.bias": seg("b2x")[Z:],
+            "fc3.weight": seg("W3"), "fc3.bias": seg("b3"),
+            "fc4.weight": seg("W4"), "fc4.bias": seg("b4"),
+        }
+
+    def load_segments(self, seg_dict):
+        """seg_dict: segment name -> array/tensor (flat-layout naming)."""
+        with torch.no_grad():
+            for k in SEGMENTS:
+                v = seg_dict[k]
+                src = v if torch.is_tensor(v) else torch.from_numpy(np.ascontiguousarray(v))
+                self.segment(self.params, k).copy_(src.to(self.device, torch.float32))
+        self.params_changed()
+
+    def load_reference_state_dict(self, sd):
+        with torch.no_grad():
+            views = self.named_parameter_views()
+            for k in REF_NAMES:
+                views[k].copy_(sd[k].to(self.device, torch.float32))
+        self.params_changed()
+
+    def segments_to_numpy(self, buf=None):
+        buf = self.params if buf is None else buf
+        self.synchronize()
+        torch.cuda.synchronize(self.device)
+        return {k: self.segment(buf, k).detach().cpu().numpy().copy() for k in SEGMENTS}
+
+    def params_changed(self):
+        """Call after writing ``params`` from outside the engine: re-binds so derived
+        copies (transposed weight shadows of the tcgen05 path) are rebuilt."""
+        torch.cuda.synchronize(self.device)
+        check(self.lib.mdt_engine_bind_buffers(self._h, _ptr(self.params), _ptr(self.grads), _ptr(self.exp_avg),
+                                               _ptr(self.exp_avg_sq), self.total))
+
+    def broadcast_params(self):
+        check(self.lib.mdt_engine_broadcast_params(self._h))
+
+    # ------------------------------------------------------------------ state
+    def set_adam(self, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, completed_steps=0):
+        h = mdt_adam(lr, betas[0], betas[1], eps)
+        check(self.lib.mdt_engine_set_adam(self._h, C.byref(h), completed_steps))
+
+    def set_rng(self, seed, offset=0):
+        check(self.lib.mdt_engine_set_rng(self._h, seed, offset))
+
+    def state(self):
+        t, o = C.c_int64(), C.c_uint64()
+        check(self.lib.mdt_engine_get_state(self._h, C.byref(t), C.byref(o)))
+        return int(t.value), int(o.value)
+
+    def synchronize(self):
+        self.stream.synchronize()
+
+    def input_buffer_ptr(self):
+        p = C.c_void_p()
+        check(self.lib.mdt_engine_input_buffer(self._h, C.byref(p)))
+        return p.value
+
+    def workspace(self, name, rows):
+        """Copy of an internal activation buffer (tests/debugging)."""
+        p, ld = C.c_void_p(), C.c_int()
+        check(self.lib.mdt_engine_workspace(self._h, name.encode(), C.byref(p), C.byref(ld)))
+        self.synchronize()
+        view = _DevView(p.value, (rows, ld.value), self.device)
+        return torch.as_tensor(view, device=self.device).clone()
+
+    # ------------------------------------------------------------------ the step
+    def _x2d(self, x):
+        x = x.reshape(-1, self.D)
+        assert x.dtype == torch.float32 and x.is_contiguous()
+        return x
+
+    def train_step(self, x, eps=None, want_loss=True):
+        """One ref:vae-hpo.py:68-74 step on device-resident x.  Returns the loss as a
+        1-element device tensor (no host sync) or None."""
+        x = self._x2d(x)
+        check(self.lib.mdt_train_step(self._h, _ptr(x), x.shape[0], _ptr(eps), _ptr(self._loss) if want_loss else None))
+        return self._loss if want_loss else None
+
+    def train_step_host(self, x_host, eps_host=None):
+        """Same step with HOST tensors (pinned for async copies); returns float loss."""
+        x = self._x2d(x_host)
+        out = C.c_float()
+        check(self.lib.mdt_train_step_host(self._h, _ptr(x), x.shape[0], _ptr(eps_host), C.byref(out)))
+        return float(out.value)
+
+    def forward(self, x, eps=None):
+        x = self._x2d(x)
+        B = x.shape[0]
+        recon = torch.empty(B, self.D, dtype=torch.float32, device=self.device)
+        mu = torch.empty(B, self.Z, dtype=torch.float32, device=self.device)
+        lv = torch.empty(B, self.Z, dtype=torch.float32, device=self.device)
+        check(self.lib.mdt_forward(self._h, _ptr(x), B, _ptr(eps), _ptr(recon), _ptr(mu), _ptr(lv)))
+        return recon, mu, lv
+
+    def backward(self, d_recon, d_mu, d_logvar):
+        check(self.lib.mdt_backward(self._h, _ptr(d_recon.contiguous()), _ptr(d_mu.contiguous()),
+                                    _ptr(d_logvar.contiguous())))
+
+    def allreduce_grads(self):
+        check(self.lib.mdt_allreduce_grads(self._h))
+
+    def adam_step(self, grad_scale=None):
+        gs = 1.0 / self.group_size if grad_scale is None else grad_scale
+        check(self.lib.mdt_adam_step(self._h, gs))
+
+    def eval_step(self, x, eps=None, want_recon=False):
+        x = self._x2d(x)
+        recon = torch.empty(x.shape[0], self.D, dtype=torch.float32, device=self.device) if want_recon else None
+        check(self.lib.mdt_eval_step(self._h, _ptr(x), x.shape[0], _ptr(eps), _ptr(self._loss), _ptr(recon)))
+        return self._loss, recon
+
+    def decode(self, z):
+        z = z.reshape(-1, self.Z).contiguous()
+        recon = torch.empty(z.shape[0], self.D, dtype=torch.float32, device=self.device)
+        check(self.lib.mdt_decode(self._h, _ptr(z), z.shape[0], _ptr(recon)))
+        return recon
+
+    def launch_count(self):
+        n = C.c_int64()
+        check(self.lib.mdt_engine_launch_count(self._h, C.byref(n)))
+        return int(n.value)
+
+    def profile_step(self, x, iters=20):
+        """Per-kernel device time of the (un-graphed) step: list of (label, avg_ms)."""
+        x = self._x2d(x)
+        buf = C.create_string_buffer(8192)
+        check(self.lib.mdt_engine_profile_step(self._h, _ptr(x), x.shape[0], iters, buf, len(buf)))
+        rows = [l.split() for l in buf.value.decode().splitlines() if l.strip()]
+        return [(n, float(ms)) for n, ms in rows]
+
+    def close(self):
+        if getattr(self, "_h", None) is not None:
+            self.lib.mdt_engine_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class _DevView:
+    """Expose a raw device pointer to torch through __cuda_array_interface__."""
+
+    def __init__(self, ptr, shape, device):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<f4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+        self.device = device
+
+
+# ---------------------------------------------------------------------- stand-alone ops
+def _cur_stream(dev):
+    return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+
+
+def adam_flat(p, g, m, v, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
+    h = mdt_adam(lr, betas[0], betas[1], eps)
+    check(_lib.load().mdt_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), C.byref(h), step, grad_scale,
+                                    _cur_stream(p.device)))
+
+
+def reparam(mu, logvar, eps=None, seed=0, offset=0):
+    B, Z = mu.shape
+    z = torch.empty(B, Z, dtype=torch.float32, device=mu.device)
+    eps_out = torch.empty(B, Z, dtype=torch.float32, device=mu.device)
+    assert mu.stride(0) == logvar.stride(0) and mu.stride(1) == 1 and logvar.stride(1) == 1
+    check(_lib.load().mdt_reparam(_ptr(mu), _ptr(logvar), mu.stride(0), _ptr(eps), seed, offset, B, Z, _ptr(z), Z,
+                                  _ptr(eps_out), _cur_stream(mu.device)))
+    return z, eps_out
+
+
+def loss_bce_kl(recon, x, mu, logvar, want_grads=True):
+    B, D = recon.shape
+    Z = mu.shape[1]
+    loss = torch.empty(1, dtype=torch.float32, device=recon.device)
+    dr = torch.empty_like(recon) if want_grads else None
+    dm = torch.empty_like(mu) if want_grads else None
+    dl = torch.empty_like(logvar) if want_grads else None
+    check(_lib.load().mdt_loss_bce_kl(_ptr(recon), _ptr(x), _ptr(mu), _ptr(logvar), B, D, Z, _ptr(loss), _ptr(dr),
+                                      _ptr(dm), _ptr(dl), _cur_stream(recon.device)))
+    return loss, dr, dm, dl
+
+
+def linear(x, w, b=None, act="none", gemm_mode="fp32"):
+    M, K = x.shape
+    N = w.shape[0]
+    y = torch.empty(M, N, dtype=torch.float32, device=x.device)
+    check(_lib.load().mdt_linear(_ptr(x), _ptr(w), _ptr(b), M, N, K, _lib.MDT_ACT[act], MDT_GEMM[gemm_mode], _ptr(y),
+                                 _cur_stream(x.device)))
+    return y

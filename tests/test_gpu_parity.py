@@ -1,0 +1,305 @@
+"""GPU parity tests: every call goes through the C-ABI (ctypes) into the sm_100a
+kernels and is compared with the CPU oracle and with the golden vectors the real
+reference produced.  Run with `pytest -m gpu` on the B200 box."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import vae_numpy as O
+from tests.golden_cases import PARAM_SEED, batch_seed, check_fp, load, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+# Stated tolerances.  fp32 mode = true fp32 FFMA GEMMs: differs from the reference (torch fp32 on CPU) only by
+# summation order and FMA contraction.  tf32x3 = 3-pass split TF32 on tcgen05 (fp32-grade).  tf32 = single pass
+# (10-bit mantissa operands): loss-level and single-step-gradient-level agreement only (SURVEY §7 "Precision").
+TOL = {
+    "fp32":   dict(loss=1e-5, act=2e-5, grad=1e-4, param=1e-4, mom=1e-4),
+    "tf32x3": dict(loss=1e-5, act=5e-5, grad=2e-4, param=2e-4, mom=2e-4),
+    "tf32":   dict(loss=1e-3, act=5e-3, grad=2e-2, param=5e-2, mom=5e-2),
+}
+MODES = [m for m in os.environ.get("MDT_TEST_MODES", "fp32").split(",") if m]
+
+
+def dev(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).cuda()
+
+
+@pytest.fixture(scope="module")
+def E():
+    from multidisttorch_b200 import engine
+    assert torch.cuda.is_available()
+    return engine
+
+
+def make_engine(E, mode, B, **kw):
+    eng = E.VAEEngine(max_batch=max(B, 1), gemm_mode=mode, **kw)
+    eng.load_segments(O.init_params(PARAM_SEED))
+    return eng
+
+
+# ------------------------------------------------------------------ stand-alone kernels
+
+def test_adam_flat_matches_oracle(E):
+    rs = np.random.RandomState(0)
+    n = 652896
+    p = rs.standard_normal(n).astype(np.float32) * 0.05
+    m = np.zeros(n, np.float32)
+    v = np.zeros(n, np.float32)
+    dp, dm, dv = dev(p), dev(m), dev(v)
+    for t in range(1, 6):
+        g = (rs.standard_normal(n) * 10.0 ** rs.uniform(-6, 1, n)).astype(np.float32)
+        O.adam_update(p, g * np.float32(0.5), m, v, t)
+        E.adam_flat(dp, dev(g), dm, dv, t, grad_scale=0.5)
+    torch.cuda.synchronize()
+    assert rel_l2(dm.cpu().numpy(), m) < 1e-6
+    assert rel_l2(dv.cpu().numpy(), v) < 1e-6
+    assert rel_l2(dp.cpu().numpy(), p) < 1e-6
+    assert np.abs(dp.cpu().numpy() - p).max() < 1e-6
+
+
+def test_adam_flat_odd_sizes_and_errors(E):
+    for n in (4, 8, 1028):
+        p, g, m, v = (torch.zeros(n, device="cuda") for _ in range(4))
+        g.fill_(1.0)
+        E.adam_flat(p, g, m, v, 1)
+        torch.cuda.synchronize()
+        np.testing.assert_allclose(p.cpu().numpy(), -1e-3, rtol=1e-5)
+    with pytest.raises(RuntimeError, match="1-based"):
+        E.adam_flat(p, g, m, v, 0)
+
+
+def test_loss_kernel_golden_corners(E):
+    g = load("loss_edge")
+    loss, dr, dm, dl = E.loss_bce_kl(dev(g["recon"]), dev(g["x"]), dev(g["mu"]), dev(g["logvar"]))
+    torch.cuda.synchronize()
+    assert abs(float(loss.item()) - float(g["loss"])) <= 2e-6 * abs(float(g["loss"]))
+    np.testing.assert_allclose(dr.cpu().numpy(), g["d_recon"], rtol=3e-6, atol=0)
+    np.testing.assert_array_equal(dm.cpu().numpy(), g["d_mu"])
+    np.testing.assert_allclose(dl.cpu().numpy(), g["d_logvar"], rtol=3e-6, atol=1.2e-7)
+
+
+@pytest.mark.parametrize("B", [1, 3, 128, 1000])
+def test_loss_kernel_random_vs_oracle(E, B):
+    rs = np.random.RandomState(B)
+    recon = rs.random_sample((B, 784)).astype(np.float32)
+    x = rs.random_sample((B, 784)).astype(np.float32)
+    mu = rs.standard_normal((B, 20)).astype(np.float32)
+    lv = rs.standard_normal((B, 20)).astype(np.float32)
+    loss, dr, dm, dl = E.loss_bce_kl(dev(recon), dev(x), dev(mu), dev(lv))
+    loss2, _, _, _ = E.loss_bce_kl(dev(recon), dev(x), dev(mu), dev(lv), want_grads=False)
+    ref = O.loss_function(recon, x, mu, lv)
+    rdr, rdm, rdl = O.loss_grads(recon, x, mu, lv)
+    assert abs(float(loss.item()) - ref) <= 2e-6 * abs(ref)
+    assert float(loss.item()) == float(loss2.item())          # fixed summation order: bit-reproducible
+    assert rel_l2(dr.cpu().numpy(), rdr) < 1e-6 and rel_l2(dl.cpu().numpy(), rdl) < 1e-6
+    np.testing.assert_array_equal(dm.cpu().numpy(), rdm)
+
+
+def test_reparam_supplied_eps(E):
+    rs = np.random.RandomState(1)
+    ml = rs.standard_normal((128, 40)).astype(np.float32)
+    eps = rs.standard_normal((128, 20)).astype(np.float32)
+    dml = dev(ml)
+    z, eo = E.reparam(dml[:, :20], dml[:, 20:], dev(eps))
+    ref = ml[:, :20] + eps * np.exp(np.float32(0.5) * ml[:, 20:], dtype=np.float32)
+    np.testing.assert_allclose(z.cpu().numpy(), ref, rtol=2e-6, atol=1e-7)
+    np.testing.assert_array_equal(eo.cpu().numpy(), eps)
+
+
+@pytest.mark.parametrize("B,offset", [(128, 0), (128, 4 * 37), (1, 8), (20000, 0)])
+def test_reparam_philox_is_torch_cuda_randn(E, B, offset):
+    """eps drawn inside the kernel must be bit-identical to what the reference's
+    torch.randn_like(std) yields on CUDA for the same generator state (ref:vae-hpo.py:35)."""
+    seed = 1234
+    gen = torch.Generator(device="cuda")
+    gen.manual_seed(seed)
+    gen.set_offset(offset)
+    want = torch.randn(B, 20, device="cuda", generator=gen)
+    mu = torch.zeros(B, 20, device="cuda")
+    lv = torch.zeros(B, 20, device="cuda")
+    z, eps = E.reparam(mu, lv, None, seed=seed, offset=offset)
+    torch.cuda.synchronize()
+    assert torch.equal(eps, want)
+    assert torch.equal(z, want)           # mu=0, std=1
+    if B <= 128:                          # and the numpy restatement of Philox/Box-Muller agrees (libm sin vs __sincosf)
+        np.testing.assert_allclose(O.cuda_randn(seed, offset, B * 20), want.cpu().numpy().ravel(), rtol=0, atol=2e-5)
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("M,N,K,act", [(128, 400, 784, "relu"), (128, 40, 400, "none"), (128, 400, 20, "relu"),
+                                       (128, 784, 400, "sigmoid"), (48, 400, 784, "relu"), (1, 784, 400, "none"),
+                                       (300, 400, 784, "none")])
+def test_linear_vs_oracle(E, mode, M, N, K, act):
+    rs = np.random.RandomState(M + N + K)
+    x = rs.random_sample((M, K)).astype(np.float32)
+    w = (rs.standard_normal((N, K)) / np.sqrt(K)).astype(np.float32)
+    b = rs.standard_normal(N).astype(np.float32)
+    y = E.linear(dev(x), dev(w), dev(b), act=act, gemm_mode=mode).cpu().numpy()
+    ref = x.astype(np.float64) @ w.astype(np.float64).T + b
+    ref = {"none": ref, "relu": np.maximum(ref, 0), "sigmoid": 1 / (1 + np.exp(-ref))}[act]
+    assert rel_l2(y, ref) < TOL[mode]["act"], rel_l2(y, ref)
+
+
+# ------------------------------------------------------------------ engine vs golden
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("tag", ["step_b128", "step_b48", "step_b1"])
+@pytest.mark.parametrize("graph", [True, False])
+def test_train_steps_match_reference_golden(E, mode, tag, graph):
+    g = load(tag)
+    tol = TOL[mode]
+    B, n = int(g["B"]), int(g["n_steps"])
+    eng = make_engine(E, mode, B, use_graph=graph)
+    for t in range(n):
+        x, eps = O.make_batch(batch_seed(t), B)
+        loss = eng.train_step(dev(x), dev(eps))
+        got = float(loss.item())
+        assert abs(got - g["losses"][t]) <= tol["loss"] * abs(g["losses"][t]), (tag, t, got, g["losses"][t])
+        if t == 0:
+            gr = eng.segments_to_numpy(eng.grads)
+            for k in O.SEGMENTS:
+                check_fp(g, "grad0", k, gr[k], tol["grad"], f"{tag}/{mode}")
+    pN = eng.segments_to_numpy()
+    mN = eng.segments_to_numpy(eng.exp_avg)
+    vN = eng.segments_to_numpy(eng.exp_avg_sq)
+    for k in O.SEGMENTS:
+        check_fp(g, "paramN", k, pN[k], tol["param"], f"{tag}/{mode}")
+        check_fp(g, "mN", k, mN[k], tol["mom"], f"{tag}/{mode}")
+        check_fp(g, "vN", k, vN[k], 2 * tol["mom"], f"{tag}/{mode}")
+    assert eng.state()[0] == n
+    eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_forward_eval_decode_golden(E, mode):
+    g = load("eval_b64")
+    tol = TOL[mode]
+    B = int(g["B"])
+    eng = make_engine(E, mode, B)
+    x, eps = O.make_batch(batch_seed(77), B)
+    recon, mu, lv = eng.forward(dev(x), dev(eps))
+    check_fp(g, "eval", "recon", recon.cpu().numpy(), tol["act"])
+    check_fp(g, "eval", "mu", mu.cpu().numpy(), tol["act"])
+    check_fp(g, "eval", "logvar", lv.cpu().numpy(), tol["act"])
+    loss, rec2 = eng.eval_step(dev(x), dev(eps), want_recon=True)
+    assert abs(float(loss.item()) - float(g["loss"])) <= tol["loss"] * abs(float(g["loss"]))
+    assert torch.equal(rec2, recon)
+    zs = np.random.RandomState(99).standard_normal((64, 20)).astype(np.float32)
+    check_fp(g, "eval", "decode64", eng.decode(dev(zs)).cpu().numpy(), tol["act"])
+    eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_compat_mode_backward_from_torch_loss(E, mode):
+    """Compat mode: the script's own loss_function runs in torch on the
+    engine's outputs; mdt_backward consumes dL/d(recon, mu, logvar)."""
+    tol = TOL[mode]
+    B = 64
+    eng = make_engine(E, mode, B)
+    p0 = O.init_params(PARAM_SEED)
+    x, eps = O.make_batch(5, B)
+    recon, mu, lv = eng.forward(dev(x), dev(eps))
+    recon.requires_grad_(); mu.requires_grad_(); lv.requires_grad_()
+    bce = torch.nn.functional.binary_cross_entropy(recon, dev(x), reduction="sum")
+    kld = -0.5 * torch.sum(1 + lv - mu.pow(2) - lv.exp())
+    (bce + kld).backward()
+    eng.backward(recon.grad, mu.grad, lv.grad)
+    L, gref, _ = O.loss_and_grads(p0, x, eps)
+    assert abs(float((bce + kld).item()) - L) <= tol["loss"] * abs(L)
+    got = eng.segments_to_numpy(eng.grads)
+    for k in O.SEGMENTS:
+        assert rel_l2(got[k], gref[k]) < tol["grad"], (k, rel_l2(got[k], gref[k]))
+    # then allreduce (no-op for a 1-rank group) + Adam, like DDP + optimizer.step()
+    eng.allreduce_grads()
+    eng.adam_step()
+    tr = O.Trainer(p0)
+    tr.step([(x, eps)])
+    pN = eng.segments_to_numpy()
+    for k in O.SEGMENTS:
+        assert rel_l2(pN[k], tr.p[k]) < tol["param"], k
+    eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_host_buffer_step_equals_device_step(E, mode):
+    B = 128
+    a = make_engine(E, mode, B)
+    b = make_engine(E, mode, B)
+    for t in range(3):
+        x, eps = O.make_batch(batch_seed(t), B)
+        la = float(a.train_step(dev(x), dev(eps)).item())
+        lb = b.train_step_host(torch.from_numpy(x).pin_memory(), torch.from_numpy(eps).pin_memory())
+        assert la == lb
+    assert torch.equal(a.params, b.params)
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_philox_step_uses_and_advances_device_state(E, mode):
+    B = 128
+    eng = make_engine(E, mode, B)
+    eng.set_rng(99, 40)
+    x, _ = O.make_batch(1, B)
+    loss = eng.train_step(dev(x), None)
+    used = eng.workspace("eps", B)
+    gen = torch.Generator(device="cuda"); gen.manual_seed(99); gen.set_offset(40)
+    assert torch.equal(used, torch.randn(B, 20, device="cuda", generator=gen))
+    assert eng.state() == (1, 44)
+    # the same step with that eps supplied explicitly gives the same loss on a fresh engine
+    eng2 = make_engine(E, mode, B)
+    assert float(eng2.train_step(dev(x), used).item()) == float(loss.item())
+    eng.train_step(dev(x), None)
+    assert eng.state() == (2, 48)
+    eng.close(); eng2.close()
+
+
+def test_empty_batch_and_errors(E):
+    eng = make_engine(E, "fp32", 16)
+    before = eng.params.clone()
+    loss = eng.train_step(torch.empty(0, 784, device="cuda"), None)
+    assert float(loss.item()) == 0.0 and torch.equal(before, eng.params) and eng.state()[0] == 0
+    with pytest.raises(RuntimeError, match="max_batch"):
+        eng.train_step(torch.zeros(17, 784, device="cuda"), None)
+    eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_full_size_properties(E, mode):
+    """At BASELINE size (B=128, 784-400-20), size-independent properties: bit-reproducible runs,
+    graph == eager, loss goes down on a fixed batch, step counter and Philox offset advance."""
+    B = 128
+    x, _ = O.make_batch(3, B)
+    runs = []
+    for graph in (True, True, False):
+        eng = make_engine(E, mode, B, use_graph=graph)
+        eng.set_rng(5, 0)
+        losses = [float(eng.train_step(dev(x), None).item()) for _ in range(40)]
+        runs.append((losses, eng.params.clone()))
+        assert eng.state() == (40, 160)
+        eng.close()
+    assert runs[0][0] == runs[1][0] and torch.equal(runs[0][1], runs[1][1])
+    assert runs[0][0] == runs[2][0] and torch.equal(runs[0][1], runs[2][1])
+    assert runs[0][0][-1] < 0.99 * runs[0][0][0]
+    assert np.isfinite(runs[0][0]).all()
+
+
+def test_hidden_4096_one_step_vs_oracle(E):
+    """BASELINE config 5 shape (H=4096), one step against the oracle."""
+    dims = O.Dims(H=4096)
+    B = 32
+    p0 = O.init_params(11, dims)
+    eng = E.VAEEngine(hidden=4096, max_batch=B, gemm_mode=MODES[0])
+    eng.load_segments(p0)
+    x, eps = O.make_batch(2, B, dims)
+    loss = float(eng.train_step(dev(x), dev(eps)).item())
+    tr = O.Trainer(p0, dims)
+    lo, g = tr.step([(x, eps)])
+    tol = TOL[MODES[0]]
+    assert abs(loss - lo[0]) <= tol["loss"] * abs(lo[0])
+    got = eng.segments_to_numpy(eng.grads)
+    for k in O.SEGMENTS:
+        assert rel_l2(got[k], g[k]) < tol["grad"], k
+    eng.close()
