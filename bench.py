@@ -1,0 +1,434 @@
+#!/usr/bin/env python
+"""Headline benchmark: VAE-HPO samples/sec (whole box), BASELINE.json metric.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W]                 # this repo's B200 path
+    python bench.py --impl reference [--gpus N] [--steps K] [--warmup W] # reference CPU/gloo path
+
+A "step" is one training step (ref:vae-hpo.py:68-74: forward, BCE+KLD loss,
+backward, group all-reduce, Adam) of one trial on one batch of synthetic
+MNIST-shaped data.  Workload at N GPUs: BASELINE config 3 -- N concurrent
+single-GPU trials (the Nx1 group layout), VAE 784-400-20, batch 128 per GPU;
+weak scaling, no data-path collective.  For N>1 (torchrun, one rank per GPU) the
+other group layouts (N/2 x 2 ... 1 x N, gradient all-reduce inside each group)
+are timed after the headline and reported under "layouts".
+
+One JSON line on stdout (rank 0).  `value` = samples/s with inputs resident in
+HBM; `e2e` = the same steps through the host-buffer C-ABI call (H2D copy of every
+batch + D2H read of the loss inside the timed region).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "VAE-HPO samples/sec (whole box)"
+UNIT = "samples/s"
+D, Z = 784, 20
+POOL_BATCHES = 512          # 512 x 128 x 784 x 4 B = 205 MB of inputs, larger than the 126 MB L2
+HOST_POOL_BATCHES = 64
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20000)
+    ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--impl", default="own", choices=["own", "reference"])
+    ap.add_argument("--batch", type=int, default=128, help="per-GPU batch")
+    ap.add_argument("--hidden", type=int, default=400)
+    ap.add_argument("--gemm-mode", default=os.environ.get("MDT_GEMM", "fp32"), choices=["fp32", "tf32", "tf32x3"])
+    ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-layouts", action="store_true")
+    ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--ref-worker", default="", help=argparse.SUPPRESS)
+    ap.add_argument("--ref-groups", type=int, default=0, help=argparse.SUPPRESS)
+    return ap.parse_args()
+
+
+def workload_name(n, batch, hidden):
+    return (f"BASELINE config 3: VAE-HPO {n} concurrent single-GPU trial(s) ({n}x1 group layout), VAE {D}-{hidden}-{Z}, "
+            f"batch {batch}/GPU, Adam lr=1e-3, synthetic MNIST-shaped data")
+
+
+# --------------------------------------------------------------------------------------------
+# algorithmic bytes per kernel launch (DESIGN.md "kernels" table states the same formulas)
+# --------------------------------------------------------------------------------------------
+def algorithmic_bytes(label, B, H, total_params):
+    f = 4
+    t = {
+        "fc1_fwd": B * D + H * D + H + B * H,
+        "fc2x_fwd": B * H + 2 * Z * H + 2 * Z + B * 2 * Z,
+        "reparam": B * 2 * Z + 3 * B * Z,
+        "fc3_fwd": B * Z + H * Z + H + B * H,
+        "fc4_fwd": B * H + D * H + D + B * D,
+        "loss_bce_kl": 3 * B * D + 2 * B * 2 * Z,
+        "fc4_dW": B * D + B * H + D * H,
+        "fc4_dX": B * D + D * H + 2 * B * H,
+        "fc3_dW": B * H + B * Z + H * Z,
+        "fc3_dX": B * H + H * Z + B * Z,
+        "reparam_bwd": 3 * B * Z + 2 * B * 2 * Z,
+        "fc2x_dW": B * 2 * Z + B * H + 2 * Z * H,
+        "fc2x_dX": B * 2 * Z + 2 * Z * H + 2 * B * H,
+        "fc1_dW": B * H + B * D + H * D,
+        "bias_grads": B * (D + 2 * H + 2 * Z) + (D + 2 * H + 2 * Z),
+        "adam_flat": 7 * total_params,
+    }
+    return t.get(label, 0) * f
+
+
+def step_flops(B, H):
+    return 2 * B * (5 * D * H + 9 * Z * H)
+
+
+def step_bytes(B, H, a=4):
+    P = 2 * D * H + 3 * Z * H + 2 * H + 2 * Z + D
+    return 4 * (9 * P + D * H + 3 * Z * H) + a * B * (5 * D + 10 * H + 17 * Z)
+
+
+def load_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        j = json.load(open(p))
+        return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md, MEASURED_PEAKS.json absent)"
+
+
+# --------------------------------------------------------------------------------------------
+# clocks: nvidia-smi sampled in a side process during warm-up + timed region
+# --------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.idx = gpu_index
+        self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
+                                       "-i", str(gpu_index)], stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.p = None
+        self.t_mark = []
+
+    def mark(self):
+        self.t_mark.append(time.time())
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.12)
+        self.p.terminate()
+        try:
+            self.p.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+        self.f.flush()
+        self.f.seek(0)
+        rows = [r.strip().split(", ") for r in self.f.read().splitlines() if r.strip()]
+        os.unlink(self.f.name)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        t0 = self.t_mark[0] if self.t_mark else 0
+        t1 = self.t_mark[-1] if len(self.t_mark) > 1 else float("inf")
+        from datetime import datetime
+        for r in rows:
+            if len(r) < 9:
+                continue
+            try:
+                ts = datetime.strptime(r[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+            except ValueError:
+                ts = None
+            inside = ts is None or (t0 - 0.06 <= ts <= t1 + 0.06)
+            try:
+                c, m = float(r[2]), float(r[3])
+            except ValueError:
+                continue
+            if inside:
+                sm.append(c)
+                mx.append(m)
+                for n, v in zip(names, r[5:9]):
+                    if v.strip() == "Active":
+                        reasons.add(n)
+        if not sm:       # region shorter than the sampling period: fall back to every sample we took
+            for r in rows:
+                try:
+                    sm.append(float(r[2])); mx.append(float(r[3]))
+                except (ValueError, IndexError):
+                    pass
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# --------------------------------------------------------------------------------------------
+# this repo's arm
+# --------------------------------------------------------------------------------------------
+def run_own(args):
+    import torch
+    import torch.distributed as dist
+    from multidisttorch_b200.engine import VAEEngine
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py (own arm) needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", init_method="env://", device_id=device)
+
+    def barrier():
+        if world > 1:
+            dist.barrier(device_ids=[local])
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    B, H, K = args.batch, args.hidden, args.steps
+    W = max(args.warmup, 3)
+    from oracle import vae_numpy as O        # deterministic parameter init shared with tests (not a compute path)
+    dims = O.Dims(H=H)
+
+    g = torch.Generator(device="cpu").manual_seed(4321 + rank)
+    host_pool = torch.rand(HOST_POOL_BATCHES, B, D, generator=g).pin_memory()
+    gd = torch.Generator(device=device).manual_seed(4321 + rank)
+    pool = torch.rand(POOL_BATCHES, B, D, generator=gd, device=device)
+
+    def timed_run(eng, steps, warm):
+        for i in range(warm):
+            eng.train_step(pool[i % POOL_BATCHES], None, want_loss=False)
+        barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = eng.launch_count()
+        ev0.record(eng.stream)
+        for i in range(steps):
+            eng.train_step(pool[i % POOL_BATCHES], None, want_loss=False)
+        ev1.record(eng.stream)
+        eng.synchronize()
+        barrier()
+        return max_over_ranks(ev0.elapsed_time(ev1)), eng.launch_count() - n0
+
+    eng = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph)
+    eng.load_segments(O.init_params(1234 + rank, dims))
+    eng.set_rng(1234 + rank, 0)
+
+    clocks = ClockSampler(local) if rank == 0 else None
+    if clocks:
+        clocks.mark()
+    ms, launches = timed_run(eng, K, W)
+    if clocks:
+        clocks.mark()
+    clk = clocks.stop() if clocks else None
+    value = world * B * K / (ms * 1e-3)
+
+    # ---- e2e: host buffers through the C-ABI, copies inside the timed region
+    for i in range(W):
+        eng.train_step_host(host_pool[i % HOST_POOL_BATCHES])
+    barrier()
+    t0 = time.perf_counter()
+    loss = 0.0
+    for i in range(K):
+        loss = eng.train_step_host(host_pool[i % HOST_POOL_BATCHES])
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(time.perf_counter() - t0)
+    barrier()
+    e2e = {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * D * 4, "d2h_bytes_per_step": 4,
+           "ms_per_step": e2e_s * 1e3 / K, "last_loss": loss}
+
+    # ---- per-kernel device time (un-graphed, event after each kernel) -> roofline of the dominant kernel
+    roofline = None
+    kernels = None
+    if rank == 0:
+        prof = eng.profile_step(pool[0], iters=30)
+        tot = sum(t for _, t in prof)
+        kernels = [{"kernel": n, "avg_us": round(t * 1e3, 3), "share": round(t / tot, 4),
+                    "alg_bytes": algorithmic_bytes(n, B, H, eng.total)} for n, t in prof]
+        name, t_ms = max(prof, key=lambda r: r[1])
+        peak, peak_src = load_peaks()
+        ab = algorithmic_bytes(name, B, H, eng.total)
+        ach = ab / (t_ms * 1e-3) / 1e9
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "dram_traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp)).get(f"{args.gemm_mode}:{name}")
+        roofline = {"bound": "hbm", "kernel": name, "achieved": round(ach, 2), "peak": peak, "unit": "GB/s",
+                    "frac": round(ach / peak, 5), "traffic": traffic, "peak_source": peak_src,
+                    "alg_bytes_per_launch": ab, "avg_launch_us": round(t_ms * 1e3, 3),
+                    "step": {"alg_bytes": step_bytes(B, H), "flops": step_flops(B, H),
+                             "achieved_GBps": round(step_bytes(B, H) / (ms * 1e-3 / K) / 1e9, 2),
+                             "frac_of_hbm_peak": round(step_bytes(B, H) / (ms * 1e-3 / K) / 1e9 / peak, 5)}}
+    eng.close()
+
+    # ---- other group layouts (gradient all-reduce inside each group)
+    layouts = {f"{world}x1": round(value, 1)}
+    if world > 1 and not args.no_layouts:
+        k = 2
+        while k <= world:
+            ng = world // k
+            groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]
+            mine = groups[rank // k]
+            e2 = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph, group=mine)
+            e2.load_segments(O.init_params(1234 + rank // k, dims))
+            e2.set_rng(1234 + rank, 0)
+            e2.broadcast_params()
+            ms2, _ = timed_run(e2, K, W)
+            layouts[f"{ng}x{k}"] = round(world * B * K / (ms2 * 1e-3), 1)
+            e2.close()
+            k *= 2
+
+    total_launches = sum_over_ranks(launches)
+
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cpu_baseline = run_reference(1, B, H, steps=None, warmup=5, seconds=args.cpu_seconds)["cpu_baseline"]
+
+    if rank == 0:
+        out = {
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(world, B, H), "layout": f"{world}x1", "batch_per_gpu": B, "hidden": H,
+                       "gemm_mode": args.gemm_mode, "cuda_graph": not args.no_graph,
+                       "l2": f"inputs cycle through a {POOL_BATCHES}-batch device pool ({POOL_BATCHES * B * D * 4 / 1e6:.0f} MB > 126 MB L2); "
+                             "parameters and optimizer state are step-to-step resident by the nature of training",
+                       "eps": "Philox in-kernel (torch-CUDA-compatible stream)"},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches), "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "layouts": layouts, "kernels": kernels,
+        }
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# --------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU/gloo path (torch port, oracle/torch_port.py) on the host cores
+# --------------------------------------------------------------------------------------------
+def ref_worker(args):
+    """One CPU rank: utils-style bootstrap, DDP over gloo, Adam -- ref:vae-hpo.py:122-131 + 69-74."""
+    import torch
+    import torch.distributed as dist
+    from oracle import torch_port as TP
+    from utils import setup_ddp, setup_ddp_groups          # this repo's drop-in utils (gloo leg)
+
+    spec = json.loads(args.ref_worker)
+    torch.set_num_threads(spec["threads"])
+    size, rank = setup_ddp()
+    groups = setup_ddp_groups(spec["ngroups"])
+    group = next(gr for gr in groups if dist.get_rank(gr) >= 0)
+    torch.manual_seed(1234 + rank)
+    model = TP.VAEPort(D, spec["hidden"], Z)
+    model = torch.nn.parallel.DistributedDataParallel(model, process_group=group)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    g = torch.Generator().manual_seed(4321 + rank)
+    batches = [torch.rand(spec["batch"], 1, 28, 28, generator=g) for _ in range(16)]
+    n, dt = TP.timed_steps(model, opt, batches, spec["warmup"], spec["steps"], spec["seconds"], barrier=dist.barrier)
+    with open(os.path.join(spec["out"], f"rank{rank}.json"), "w") as f:
+        json.dump({"steps": n, "seconds": dt}, f)
+    dist.destroy_process_group()
+
+
+def run_reference(n, B, H, steps, warmup, seconds):
+    cores = os.cpu_count() or 1
+    threads = max(cores // n, 1)
+    out = tempfile.mkdtemp(prefix="mdt_ref_")
+    port = 20000 + (os.getpid() % 20000)
+    spec = {"threads": threads, "ngroups": n, "hidden": H, "batch": B, "warmup": warmup, "steps": steps,
+            "seconds": seconds, "out": out}
+    procs = []
+    for r in range(n):
+        env = dict(os.environ)
+        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "SLURM_NPROCS", "SLURM_PROCID", "SLURM_NODELIST", "LSB_HOSTS",
+                  "LSB_MCPU_HOSTS", "TORCHELASTIC_RUN_ID"):
+            env.pop(k, None)
+        env.update(OMPI_COMM_WORLD_SIZE=str(n), OMPI_COMM_WORLD_RANK=str(r), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                   DDP_BACKEND="gloo", CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS=str(threads), MDT_DROPIN="0",
+                   PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
+        procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--ref-worker", json.dumps(spec)],
+                                      env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
+    for p in procs:
+        _, err = p.communicate(timeout=1800)
+        if p.returncode != 0:
+            raise RuntimeError(f"reference worker failed:\n{err[-2000:]}")
+    res = [json.load(open(os.path.join(out, f"rank{r}.json"))) for r in range(n)]
+    n_steps = min(r["steps"] for r in res)
+    dt = max(r["seconds"] for r in res)
+    value = n * B * n_steps / dt
+    cpu_model = ""
+    try:
+        cpu_model = next(l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name"))
+    except Exception:
+        pass
+    sample = (f"{n_steps} training steps of batch {B} per rank on {n} CPU rank(s) x {threads} thread(s) (torch {_torch_version()} CPU, "
+              f"DDP over gloo, {n}x1 layout), {dt:.1f} s; same synthetic U[0,1) data shape as the GPU arm")
+    return {"value": value, "steps": n_steps, "seconds": dt,
+            "cpu_baseline": {"value": round(value, 1), "unit": UNIT, "cores": threads * n, "kind": "port", "sample": sample,
+                             "host_cores": cores, "cpu_model": cpu_model, "ms_per_step": dt * 1e3 / n_steps}}
+
+
+def _torch_version():
+    import torch
+    return torch.__version__
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return          # under torchrun only rank 0 runs the CPU arm; the others exit 0 without work
+    n, B, H = args.gpus, args.batch, args.hidden
+    W = max(min(args.warmup, 20), 3)
+    # bounded sample: at most ~60 s of CPU work, and never more steps than asked for
+    probe = run_reference(n, B, H, steps=20, warmup=3, seconds=None)
+    per_step = probe["seconds"] / probe["steps"]
+    K = max(min(args.steps, int(60.0 / per_step)), 10)
+    r = run_reference(n, B, H, steps=K, warmup=W, seconds=None)
+    out = {
+        "impl": "reference", "metric": METRIC, "value": round(r["value"], 1), "unit": UNIT, "n_gpus": n, "steps": r["steps"],
+        "warmup": W, "ms_per_step": r["seconds"] * 1e3 / r["steps"], "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(n, B, H), "layout": f"{n}x1", "batch_per_gpu": B, "hidden": H,
+                   "device": "host CPU cores (no GPU)", "requested_steps": args.steps},
+        "cpu_baseline": r["cpu_baseline"],
+        "e2e": {"value": round(r["value"], 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.ref_worker:
+        return ref_worker(args)
+    if args.impl == "reference":
+        return run_reference_arm(args)
+    return run_own(args)
+
+
+if __name__ == "__main__":
+    main()
