@@ -1,0 +1,246 @@
+"""Drop-in hooks that put the B200 engine behind the torch names the reference
+scripts call directly (SURVEY §8b "compat mode").
+
+``vae-hpo.py`` builds its trial with
+``torch.nn.parallel.DistributedDataParallel(model, process_group=group)`` and
+``optim.Adam(model.parameters(), lr=1e-3)`` (ref:vae-hpo.py:130-131) and then
+runs ``zero_grad / model(data) / loss_function / backward / step``
+(ref:vae-hpo.py:69-74).  ``install()`` (called when ``utils`` is imported on a
+CUDA box) replaces those two names with factories that
+
+* recognise the reference's VAE (five ``nn.Linear`` named fc1, fc21, fc22, fc3,
+  fc4 with encoder/decoder-consistent shapes, fp32, on CUDA) and return an
+  ``EngineModule`` / ``EngineAdam`` pair backed by ONE ``VAEEngine``;
+* fall through to the real torch classes for anything else.
+
+Inside an ``EngineModule`` the forward is one C-ABI call (tensor-core or fp32
+GEMMs + fused reparameterisation, eps drawn from the same Philox stream
+``torch.randn_like`` would use), the script's own ``loss_function`` still runs
+in torch on the returned tensors, ``loss.backward()`` lands in
+``mdt_backward`` + the subgroup gradient all-reduce, and ``optimizer.step()`` is
+the fused flat Adam kernel (with the 1/group_size scale folded in).
+There is no CPU path: on a box without CUDA nothing is patched.
+"""
+import os
+
+import torch
+import torch.distributed as dist
+from torch import nn
+
+from .engine import REF_NAMES, VAEEngine
+
+_ORIG = {}
+_ENGINE_OF_PARAM = {}     # id(parameter) -> EngineModule
+
+
+def _next_pow2(n):
+    p = 1
+    while p < n:
+        p *= 2
+    return p
+
+
+def recognise(module):
+    """(in_dim, hidden, latent) if ``module`` has the reference VAE's structure, else None."""
+    names = ("fc1", "fc21", "fc22", "fc3", "fc4")
+    if not all(isinstance(getattr(module, n, None), nn.Linear) for n in names):
+        return None
+    if len(list(module.parameters())) != 10:
+        return None
+    D, H, Z = module.fc1.in_features, module.fc1.out_features, module.fc21.out_features
+    ok = (module.fc21.in_features == H and module.fc22.in_features == H and module.fc22.out_features == Z
+          and module.fc3.in_features == Z and module.fc3.out_features == H
+          and module.fc4.in_features == H and module.fc4.out_features == D)
+    p = module.fc1.weight
+    if not ok or p.dtype != torch.float32 or not p.is_cuda:
+        return None
+    if D % 4 or H % 4 or Z % 4:
+        return None
+    return D, H, Z
+
+
+class _VAEFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, anchor, owner):
+        ctx.owner = owner
+        recon, mu, logvar = owner._engine_forward(x)
+        return recon, mu, logvar
+
+    @staticmethod
+    def backward(ctx, d_recon, d_mu, d_logvar):
+        ctx.owner._engine_backward(d_recon, d_mu, d_logvar)
+        return None, None, None
+
+
+class EngineModule(nn.Module):
+    """Stands where DistributedDataParallel(model, process_group=group) stood."""
+
+    def __init__(self, module, dims, process_group=None):
+        super().__init__()
+        self.module = module
+        self.dims = dims
+        self.process_group = process_group
+        self.gemm_mode = os.environ.get("MDT_GEMM", "fp32")
+        self.engine = None
+        self._gen = torch.cuda.default_generators[module.fc1.weight.device.index]
+        self._expect_offset = None
+        self._build(int(os.environ.get("MDT_MAX_BATCH", "1024")), first=True)
+
+    # -- engine lifetime ---------------------------------------------------------------------
+    def _build(self, max_batch, first=False):
+        D, H, Z = self.dims
+        dev = self.module.fc1.weight.device
+        old = self.engine
+        eng = VAEEngine(in_dim=D, hidden=H, latent=Z, max_batch=max_batch, gemm_mode=self.gemm_mode,
+                        use_graph=os.environ.get("MDT_GRAPH", "1") != "0", group=self.process_group, device=dev)
+        if first:
+            eng.load_reference_state_dict(self.module.state_dict())
+            if eng.group_size > 1:
+                eng.broadcast_params()          # DDP constructor: parameters of group-rank 0 win
+        else:
+            eng.params.copy_(old.params); eng.exp_avg.copy_(old.exp_avg); eng.exp_avg_sq.copy_(old.exp_avg_sq)
+            eng.grads.copy_(old.grads)
+            t, _ = old.state()
+            eng.params_changed()
+            lr, betas, eps = getattr(self, "_adam_h", (1e-3, (0.9, 0.999), 1e-8))
+            eng.set_adam(lr, betas, eps, completed_steps=t)
+            old.close()
+        self.engine = eng
+        # the script's parameters become views of the flat buffers (so decode(), state_dict(), .grad keep working)
+        pv, gv = eng.named_parameter_views(), eng.named_parameter_views(eng.grads)
+        for name, p in self.module.named_parameters():
+            p.data = pv[name]
+            p.grad = gv[name]
+            _ENGINE_OF_PARAM[id(p)] = self
+        self._sync_rng(force=True)
+
+    def _sync_rng(self, force=False):
+        off = int(self._gen.get_offset())
+        if force or off != self._expect_offset:
+            self.engine.set_rng(int(self._gen.initial_seed()), off)
+            self._expect_offset = off
+
+    # -- forward / backward --------------------------------------------------------------------
+    def _engine_forward(self, x):
+        x = x.reshape(-1, self.dims[0])
+        if x.dtype != torch.float32 or not x.is_contiguous():
+            x = x.contiguous().float()
+        if x.shape[0] > self.engine.max_batch:
+            self._build(_next_pow2(x.shape[0]))
+        self._sync_rng()
+        out = self.engine.forward(x, None)
+        # keep torch's CUDA generator in lock-step with what randn_like would have consumed
+        B, Z = x.shape[0], self.dims[2]
+        if B > 0:
+            props = torch.cuda.get_device_properties(x.device)
+            grid = min((B * Z + 255) // 256, props.multi_processor_count * (props.max_threads_per_multi_processor // 256))
+            inc = ((B * Z - 1) // (256 * grid * 4) + 1) * 4
+            self._expect_offset += inc
+            self._gen.set_offset(self._expect_offset)
+        return out
+
+    def _engine_backward(self, d_recon, d_mu, d_logvar):
+        B = d_recon.shape[0] if d_recon is not None else (d_mu.shape[0] if d_mu is not None else 0)
+        D, _, Z = self.dims
+        dev = self.engine.device
+        if d_recon is None:
+            d_recon = torch.zeros(B, D, device=dev)
+        if d_mu is None:
+            d_mu = torch.zeros(B, Z, device=dev)
+        if d_logvar is None:
+            d_logvar = torch.zeros(B, Z, device=dev)
+        self.engine.backward(d_recon, d_mu, d_logvar)
+        self.engine.allreduce_grads()        # SUM over the trial group; Adam applies 1/group_size
+
+    def forward(self, x):
+        if torch.is_grad_enabled() and self.training:
+            return _VAEFn.apply(x, self.module.fc1.weight, self)
+        return self._engine_forward(x)
+
+
+class EngineAdam:
+    """Stands where optim.Adam(model.parameters(), lr=1e-3) stood."""
+
+    def __init__(self, owner, lr, betas, eps):
+        self.owner = owner
+        self.defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False)
+        self.param_groups = [dict(self.defaults, params=list(owner.module.parameters()))]
+        owner._adam_h = (lr, betas, eps)
+        owner.engine.set_adam(lr, betas, eps, 0)
+
+    def zero_grad(self, set_to_none=True):
+        pass        # gradients are overwritten by every backward, never accumulated
+
+    def step(self, closure=None):
+        self.owner.engine.adam_step()
+        return None
+
+    def state_dict(self):
+        t, _ = self.owner.engine.state()
+        eng = self.owner.engine
+        return {"step": t, "exp_avg": eng.exp_avg.clone(), "exp_avg_sq": eng.exp_avg_sq.clone(),
+                "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
+
+
+def _wants_engine_ddp(module, args, kwargs):
+    dims = recognise(module) if not args and set(kwargs) <= {"process_group"} else None
+    if dims is None:
+        return None
+    pg = kwargs.get("process_group")
+    if pg is not None and dist.is_initialized() and dist.get_world_size(pg) > 1 and dist.get_backend(pg) != "nccl":
+        return None         # e.g. DDP_BACKEND=gloo with CUDA tensors: leave to torch
+    return dims
+
+
+def _make_shims(orig_ddp, orig_adam):
+    """Subclasses of the real torch classes whose constructors hand back the engine-backed
+    objects for the reference VAE and behave exactly like the originals otherwise
+    (isinstance checks and further subclassing keep working)."""
+
+    class DistributedDataParallel(orig_ddp):
+        def __new__(cls, module=None, *args, **kwargs):
+            if cls is DistributedDataParallel and isinstance(module, nn.Module):
+                dims = _wants_engine_ddp(module, args, kwargs)
+                if dims is not None:
+                    return EngineModule(module, dims, kwargs.get("process_group"))
+            return super().__new__(cls)
+
+    class Adam(orig_adam):
+        def __new__(cls, params=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False, **kwargs):
+            plist = list(params) if params is not None else []
+            if cls is Adam and plist and not isinstance(plist[0], dict):
+                owners = {id(_ENGINE_OF_PARAM.get(id(p))) for p in plist}
+                owner = _ENGINE_OF_PARAM.get(id(plist[0]))
+                plain = (owner is not None and len(owners) == 1 and len(plist) == 10 and weight_decay == 0
+                         and not amsgrad and not kwargs and not isinstance(lr, torch.Tensor))
+                if plain:
+                    return EngineAdam(owner, lr, betas, eps)
+            obj = super().__new__(cls)
+            obj._mdt_params = plist          # a generator argument was consumed above: hand the list to __init__
+            return obj
+
+        def __init__(self, params=None, *args, **kwargs):
+            super().__init__(self.__dict__.pop("_mdt_params", params), *args, **kwargs)
+
+    DistributedDataParallel.__qualname__ = DistributedDataParallel.__name__ = "DistributedDataParallel"
+    Adam.__qualname__ = Adam.__name__ = "Adam"
+    return DistributedDataParallel, Adam
+
+
+def install():
+    """Patch torch.nn.parallel.DistributedDataParallel and torch.optim.Adam (idempotent)."""
+    if _ORIG or not torch.cuda.is_available():
+        return False
+    _ORIG["ddp"] = torch.nn.parallel.DistributedDataParallel
+    _ORIG["adam"] = torch.optim.Adam
+    ddp, adam = _make_shims(_ORIG["ddp"], _ORIG["adam"])
+    torch.nn.parallel.DistributedDataParallel = ddp
+    torch.optim.Adam = adam
+    return True
+
+
+def uninstall():
+    if not _ORIG:
+        return
+    torch.nn.parallel.DistributedDataParallel = _ORIG.pop("ddp")
+    torch.optim.Adam = _ORIG.pop("adam")
