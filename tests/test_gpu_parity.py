@@ -105,7 +105,7 @@ def test_reparam_supplied_eps(E):
     dml = dev(ml)
     z, eo = E.reparam(dml[:, :20], dml[:, 20:], dev(eps))
     ref = ml[:, :20] + eps * np.exp(np.float32(0.5) * ml[:, 20:], dtype=np.float32)
-    np.testing.assert_allclose(z.cpu().numpy(), ref, rtol=2e-6, atol=1e-7)
+    np.testing.assert_allclose(z.cpu().numpy(), ref, rtol=2e-6, atol=5e-7)  # mu + eps*std cancels near 0
     np.testing.assert_array_equal(eo.cpu().numpy(), eps)
 
 
