@@ -185,6 +185,23 @@ int mdt_loss_bce_kl(const float* recon, const float* x, const float* mu, const f
                     int in_dim, int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar,
                     void* stream);
 
+/* Same computation and arguments as mdt_loss_bce_kl, for callers that must not trigger a
+ * device allocation: code that runs while a memory budget is already fully committed (a
+ * pre-sized pool owns the whole GPU), latency-critical loops where the implicit device
+ * synchronisation of cudaMalloc is unacceptable, and set-ups whose allocator cannot be
+ * re-entered from the calling context.  It has no counterpart in the reference.
+ * The per-block partial sums and the completion ticket live in a fixed 4352-byte array that
+ * is part of the library image (every GPU that loads the library holds it until exit), so the
+ * call performs no cudaMalloc/cudaFree.  Limit: batch*in_dim <= 1,048,576 elements (1024
+ * blocks); larger inputs are rejected with MDT_ERR_INVALID and a message.  The first call on
+ * each device also looks up the array's device address (cudaGetSymbolAddress); make that
+ * first call outside any stream capture.  All calls on a device share the one array: the
+ * ticket is re-zeroed on `stream` before every launch, but two calls that overlap on the GPU
+ * (different streams without ordering) race on it -- serialise them. */
+int mdt_loss_bce_kl_noalloc(const float* recon, const float* x, const float* mu, const float* logvar, int batch,
+                            int in_dim, int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar,
+                            void* stream);
+
 /* y[M,N] = act(x[M,K] . W[N,K]^T + b[N]) : nn.Linear (+F.relu / torch.sigmoid),
  * ref:vae-hpo.py:30-31,39-40.  `gemm_mode` selects the kernel family. */
 int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode,

@@ -48,6 +48,7 @@ _PROTOS = {
     "mdt_adam_flat": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.POINTER(mdt_adam), C.c_int64, C.c_float, _P]),
     "mdt_reparam": (C.c_int, [_P, _P, C.c_int, _P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, _P, C.c_int, _P, _P]),
     "mdt_loss_bce_kl": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
+    "mdt_loss_bce_kl_noalloc": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "mdt_linear": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "mdt_allreduce_bench": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, C.POINTER(C.c_double)]),
 }

@@ -726,6 +726,59 @@ int mdt_loss_bce_kl(const float* recon, const float* x, const float* mu, const f
   return MDT_OK;
 }
 
+}  // extern "C" (re-opened below)
+
+// ---- allocation-free variant of the loss kernel entry ------------------------------------------
+// Its scratch (one partial sum per block + the "last block" ticket) is this fixed array in the
+// library image instead of a cudaMalloc'ed buffer.  Every GPU that loads the library carries these
+// 4352 bytes until the process exits.  In HOST code the name `g_loss_static_scratch` is only a
+// stand-in for the symbol, not a device address: the address is looked up once per device with
+// cudaGetSymbolAddress and that pointer is what the kernel receives.
+constexpr int kNoAllocMaxBlocks = 1024;                                     // partial sums available
+constexpr long long kNoAllocMaxElems = (long long)kNoAllocMaxBlocks * kLossThreads * 4;  // 1,048,576 recon elements
+constexpr int kNoAllocTicketFloats = 64;                                    // ticket word lives in its own 256 bytes
+static __device__ __align__(256) float g_loss_static_scratch[kNoAllocTicketFloats + kNoAllocMaxBlocks];
+static float* g_loss_static_ptr[64] = {nullptr};                            // per device, filled at first use
+
+extern "C" {
+
+int mdt_loss_bce_kl_noalloc(const float* recon, const float* x, const float* mu, const float* logvar, int batch,
+                            int in_dim, int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar,
+                            void* stream) {
+  MDT_CHECK(recon && x && mu && logvar && loss_out, "NULL argument");
+  MDT_CHECK(batch >= 0 && in_dim > 0 && latent > 0, "bad shape");
+  for (const void* q : {(const void*)recon, (const void*)x, (const void*)d_recon})
+    MDT_CHECK(reinterpret_cast<uintptr_t>(q) % 16 == 0, "recon/x/d_recon must be 16-byte aligned");
+  const long long elems = (long long)batch * in_dim;
+  MDT_CHECK(elems <= kNoAllocMaxElems,
+            "mdt_loss_bce_kl_noalloc: batch*in_dim = %lld exceeds the fixed scratch capacity of %lld elements "
+            "(%d blocks); use mdt_loss_bce_kl for larger inputs",
+            elems, kNoAllocMaxElems, kNoAllocMaxBlocks);
+  int dev = 0;
+  MDT_CUDA(cudaGetDevice(&dev));
+  MDT_CHECK(dev >= 0 && dev < 64, "device index %d out of range", dev);
+  if (g_loss_static_ptr[dev] == nullptr) {
+    // one-time set-up for this device (it is the current one): resolve the symbol to a device address
+    float* p = nullptr;
+    MDT_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_loss_static_scratch));
+    g_loss_static_ptr[dev] = p;
+  }
+  float* scratch = g_loss_static_ptr[dev];
+  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  // the array keeps whatever the previous call left; only the ticket has to start from zero
+  MDT_CUDA(cudaMemsetAsync(scratch, 0, sizeof(unsigned int), s));
+  LossArgs a{};
+  a.recon = recon; a.x = x; a.mu = mu; a.logvar = logvar; a.ld_ml = latent; a.B = batch; a.D = in_dim; a.Z = latent;
+  a.d_recon = d_recon; a.d_mu = d_mu; a.d_logvar = d_logvar; a.ld_dml = latent;
+  a.partials = scratch + kNoAllocTicketFloats;
+  a.ticket = reinterpret_cast<unsigned int*>(scratch);
+  a.loss_out = loss_out;
+  const int grid = loss_grid(elems);   // <= kNoAllocMaxBlocks because of the size check above
+  loss_bce_kl_kernel<false><<<grid, kLossThreads, 0, s>>>(a);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
 int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode, float* y,
                void* stream) {
   MDT_CHECK(x && w && y, "NULL argument");

@@ -279,6 +279,18 @@ def loss_bce_kl(recon, x, mu, logvar, want_grads=True):
     return loss, dr, dm, dl
 
 
+def loss_bce_kl_noalloc(recon, x, mu, logvar, loss, d_recon=None, d_mu=None, d_logvar=None):
+    """mdt_loss_bce_kl_noalloc: every buffer, outputs included, is supplied by the caller, and the
+    library keeps its scratch in a fixed in-image array, so nothing is allocated anywhere on the
+    way (not by torch either).  For callers that hold a fully committed memory budget or cannot
+    afford cudaMalloc's device-wide synchronisation.  batch*in_dim <= 1,048,576."""
+    B, D = recon.shape
+    check(_lib.load().mdt_loss_bce_kl_noalloc(_ptr(recon), _ptr(x), _ptr(mu), _ptr(logvar), B, D, mu.shape[1],
+                                              _ptr(loss), _ptr(d_recon), _ptr(d_mu), _ptr(d_logvar),
+                                              _cur_stream(recon.device)))
+    return loss
+
+
 def linear(x, w, b=None, act="none", gemm_mode="fp32"):
     M, K = x.shape
     N = w.shape[0]
