@@ -6,12 +6,12 @@ import sys
 import tempfile
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-_port = [29700 + (os.getpid() % 200)]
-
-
 def next_port():
-    _port[0] += 1
-    return _port[0]
+    """A TCP port that is free right now (bind to 0 and let the kernel pick)."""
+    import socket
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
 
 
 def launch(world, argv, script=None, extra_env=None, timeout=300, cwd=None):
