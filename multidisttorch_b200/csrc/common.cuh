@@ -77,6 +77,7 @@ struct StepState {
   unsigned long long philox_offset;  // advanced by the reparameterisation kernel
   long long adam_t;                  // completed Adam steps; advanced by the Adam kernel
   double lr, beta1, beta2, eps;
+  double b1_pow, b2_pow;             // beta1^adam_t, beta2^adam_t (kept incrementally: no pow() in the kernel)
   unsigned int ticket_reparam;       // "last block done" counters (self-resetting)
   unsigned int ticket_adam;
   unsigned int ticket_loss;

@@ -291,9 +291,8 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
   __shared__ float sc[6];
   if (a.st != nullptr) {
     if (threadIdx.x == 0) {
-      const double t = (double)(a.st->adam_t + 1);
-      const double bc1 = 1.0 - pow(a.st->beta1, t);
-      const double bc2 = 1.0 - pow(a.st->beta2, t);
+      const double bc1 = 1.0 - a.st->b1_pow * a.st->beta1;   // 1 - beta1^(t+1)
+      const double bc2 = 1.0 - a.st->b2_pow * a.st->beta2;
       sc[0] = (float)(a.st->lr / bc1);
       sc[1] = (float)sqrt(bc2);
       sc[2] = (float)(1.0 - a.st->beta1);
@@ -338,6 +337,8 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
       const unsigned int done = atomicAdd(&a.st->ticket_adam, 1u);
       if (done == gridDim.x - 1) {
         a.st->adam_t += 1;
+        a.st->b1_pow *= a.st->beta1;
+        a.st->b2_pow *= a.st->beta2;
         a.st->ticket_adam = 0;
         __threadfence();
       }

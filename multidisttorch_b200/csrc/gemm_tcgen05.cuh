@@ -1,27 +1,1100 @@
-// tcgen05 / TMA / TMEM GEMM path (MDT_GEMM_TF32, MDT_GEMM_TF32X3) -- placeholder
-// until the kernels land; every entry fails loudly.
+// tcgen05 / TMA / TMEM GEMM path (MDT_GEMM_TF32, MDT_GEMM_TF32X3) for sm_100a.
+//
+//   C[M,N] = epilogue( A[M,K] . B[N,K]^T ),   A and B row-major fp32 with K contiguous ("K-major").
+//
+// * operands are staged by TMA (cp.async.bulk.tensor.2d, SWIZZLE_128B, out-of-bounds rows/columns
+//   zero-filled) into a 4-stage shared-memory ring: A tile 128 x 32 fp32 (16 KB), B tile BN x 32 fp32;
+// * one elected thread issues tcgen05.mma.cta_group::1.kind::tf32 (UMMA 128 x BN x 8), accumulating
+//   in TMEM (BN fp32 columns x 128 lanes); tcgen05.commit releases ring slots / signals the epilogue;
+// * TF32X3: four warps split every landed stage in place into hi = tf32(a) and lo = tf32(a - hi)
+//   (elementwise, so the swizzled placement is untouched) and the issuer runs three MMAs per k-step
+//   (lo.hi + hi.lo + hi.hi): fp32-grade products on the tensor cores;
+// * the same four warps then drain TMEM (tcgen05.ld 32x32b.x16) into a padded shared-memory tile and
+//   run the fused epilogue with coalesced row-major AND transposed global stores.
+//
+// Because every operand must be K-major, each activation that is later contracted over the batch
+// (dW = dY^T X) is also written transposed by the epilogue that produces it, and the three weights
+// that back-propagate (W4, W3, W2x) keep a transposed shadow refreshed after every Adam step.
 #pragma once
+
+#include <cuda.h>
+
+#include <map>
+
 #include "common.cuh"
+#include "elementwise.cuh"
 
 namespace mdt {
-struct Tc05Plan;
+
+// ------------------------------------------------------------------------------------------------
+// PTX wrappers
+// ------------------------------------------------------------------------------------------------
+namespace ptx {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void fence_mbar_init() { asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Spin on the phase parity.  A watchdog (about 2 s of wall clock) traps instead of hanging the GPU
+// if a descriptor or byte count is wrong.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  unsigned long long t0 = 0;
+  for (uint32_t spins = 0;; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spins & 0x3ff) == 0x3ff) {
+      unsigned long long t;
+      asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+      if (t0 == 0) t0 = t;
+      else if (t - t0 > 2000000000ull) __trap();
+    }
+  }
+}
+
+__device__ __forceinline__ void prefetch_tmap(const void* tmap) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");
+}
+// 2-D tiled TMA load: coordinates are {inner (K, elements), outer (row)}.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const void* tmap, int c0, int c1, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(c0), "r"(c1), "r"(bar)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t slot_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(slot_smem), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tmem_relinquish() {
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] . B[smem]^T, tf32 inputs, fp32 accumulate.
+__device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// mbarrier arrive once every tcgen05 op issued so far by this thread has completed.
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+// 32 lanes x 16 consecutive fp32 columns: thread t of the warp receives lane (base_lane + t).
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ float to_tf32(float x) {
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return __uint_as_float(r);
+}
+// Upper part of the hi/lo split: keep sign, exponent and the 10 mantissa bits tf32 has.
+__device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
+__device__ __forceinline__ void bar_sync_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }  // the 8 epilogue warps
+
+}  // namespace ptx
+
+// ------------------------------------------------------------------------------------------------
+// descriptors
+// ------------------------------------------------------------------------------------------------
+// Shared-memory matrix descriptor, K-major tile of 128-byte rows, SWIZZLE_128B (8-row x 128 B atoms,
+// 1024 B apart): start address >> 4 in bits [0,14), LBO (unused here) in [16,30), SBO >> 4 in [32,46),
+// descriptor version 1 in [46,48), layout type 2 (SWIZZLE_128B) in [61,64).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFFu) >> 4) | ((uint64_t)(1024u >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// Instruction descriptor, kind::tf32: D format F32 (bits [4,6) = 1), A and B format TF32 (bits [7,10) and
+// [10,13) = 2), both operands K-major (bits 15, 16 = 0), N >> 3 in [17,23), M >> 4 in [24,29).
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+  return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+// epilogues
+// ------------------------------------------------------------------------------------------------
+enum Tc05EpiKind {
+  EPI_BIAS_ACT = 0,     // C = act(acc + bias[n]); optional transposed copy
+  EPI_REPARAM = 1,      // fc21|fc22 tile -> ml, eps, std, z, z^T, direct KLD gradients, KLD partial sum
+  EPI_SIGMOID_BCE = 2,  // fc4 tile -> recon, BCE partial, d(logits) and its transpose; last CTA writes the loss
+  EPI_RELU_MASK = 3,    // dX tile masked by the forward activation; optional row-major and transposed stores
+  EPI_GRADW = 4,        // weight-gradient tile + bias gradient (row sums of the A operand)
+  EPI_REPARAM_BWD = 5,  // dz tile -> d[mu|logvar] and its transpose
+};
+
+struct Tc05Epi {
+  // generic
+  float* C; int ldc;
+  float* CT; int ldct;
+  const float* bias; int act;
+  const float* mask; int ldmask;
+  // reparameterisation (forward)
+  const float* eps_in; StepState* st; long long philox_S; unsigned long long philox_inc;
+  float *z, *zT, *eps_out, *sd_out, *dml_kl; int Z; int ldzT;
+  float* kl_partials;
+  // BCE
+  const float* x; int ldx; float* da4; float* da4T; int ld_da4T;
+  float* bce_partials; unsigned int* ticket; float* loss_out; int n_kl_partials;
+  // weight gradient
+  const float* a_src; int lda_src; float* db;
+  // reparameterisation (backward)
+  const float *eps, *sd; float *dml, *dmlT; int ld_dmlT;
+  // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
+  long long* dbg;
+};
+
+constexpr int kTcEpiThreads = 256;                 // warps 2-9: hi/lo split (TF32X3) + epilogue
+constexpr int kTcThreads = 64 + kTcEpiThreads;     // warp 0: TMA, warp 1: MMA + TMEM alloc
+constexpr int kTcBM = 128;
+constexpr int kTcBK = 32;        // fp32 elements = one 128-byte swizzle row
+
+template <int BN, bool kSplit>
+struct Tc05Smem {
+  static constexpr int A_BYTES = kTcBM * 128;
+  static constexpr int B_BYTES = BN * 128;
+  static constexpr int HB = A_BYTES + B_BYTES;          // bytes TMA delivers per stage
+  static constexpr int STAGE = kSplit ? 2 * HB : HB;    // + the "lo" halves in split mode
+  static constexpr int STAGES = kSplit ? 4 : 8;         // ring depth: about 190 KB either way at BN = 64
+  static constexpr int RING = STAGES * STAGE;
+  static constexpr int TILE_LD = BN + 4;                // padded epilogue tile (16-byte rows), reuses the ring
+  static constexpr int BAR_OFF = RING;
+  static constexpr int TOTAL = RING + 256 + 1024;       // barriers/tmem slot/reduction scratch + alignment slack
+  static_assert(kTcBM * (TILE_LD + 65 + 128) * 4 <= RING, "epilogue tile + transposed-store scratch must fit in the ring");
+};
+
+// ------------------------------------------------------------------------------------------------
+// fused epilogues: run by the 128 epilogue threads on the accumulator tile T[128][ldt] in shared memory
+// ------------------------------------------------------------------------------------------------
+// Epilogue math of the tensor-core path.  These run on a handful of warps per SM, where the length of the dependent
+// instruction chain per element (not throughput) sets the time, so the short-latency SFU forms are used:
+// ex2/lg2/rcp approximations are accurate to ~2 ulp, far inside the tolerance of this path, and the clamp
+// semantics of F.binary_cross_entropy are kept exactly (log(0) = -inf -> -100; denominators below 1e-12).
+__device__ __forceinline__ float fast_sigmoid(float a) { return __frcp_rn(1.0f + __expf(-a)); }
+__device__ __forceinline__ float fast_bce_term(float r, float x) {
+  const float l1 = fmaxf(__logf(1.0f - r), -100.0f);
+  const float l0 = fmaxf(__logf(r), -100.0f);
+  return (x - 1.0f) * l1 - x * l0;
+}
+// d loss / d logit = bce_grad * r(1-r): equals r - x whenever r(1-r) >= 1e-12 (the clamp is inactive)
+__device__ __forceinline__ float fast_dlogit(float r, float x) {
+  const float p = (1.0f - r) * r;
+  return p >= 1e-12f ? (r - x) : (r - x) * 1e12f * p;
+}
+
+// Transposed store of the tile: thread = (tile row, column half); reads float4 from its row, writes four scalars,
+// each of which is coalesced across the warp (consecutive lanes = consecutive m).
+template <int BN>
+__device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, float* CT, int ldct, int m0, int n0, int M,
+                                                      int N, int et) {
+  const int r = et % kTcBM, ch = et / kTcBM;     // 256 threads: two column halves
+  const int m = m0 + r;
+  if (m >= M) return;
+  constexpr int HALF = BN / 2;
+  const float* trow = T + r * ldt + ch * HALF;
+  float* tp = CT + (size_t)(n0 + ch * HALF) * ldct + m;
+  const int cvalid = N - n0 - ch * HALF;         // columns of this half that exist
+#pragma unroll
+  for (int c = 0; c < HALF; c += 4) {
+    const float4 t = *reinterpret_cast<const float4*>(trow + c);
+    if (c + 0 < cvalid) tp[(size_t)(c + 0) * ldct] = t.x;
+    if (c + 1 < cvalid) tp[(size_t)(c + 1) * ldct] = t.y;
+    if (c + 2 < cvalid) tp[(size_t)(c + 2) * ldct] = t.z;
+    if (c + 3 < cvalid) tp[(size_t)(c + 3) * ldct] = t.w;
+  }
+}
+
+template <int BN, int kEpi>
+__device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int ldt, int m0, int n0, int M, int N, int et,
+                                              float* red) {
+  const int lane = et & 31, ew = et >> 5;
+  // Element-wise epilogues: 256 threads sweep the tile row by row in float4 units.  A thread always owns the same
+  // four columns and rows rbase, rbase+RPP, ...; everything it needs (tile values from shared memory, mask / x
+  // from global) is loaded up-front, the math is straight-line code over all its elements, only stores are
+  // predicated.  N, every leading dimension and every base pointer are multiples of 4 floats (checked on the host).
+  constexpr int F4R = BN / 4;                    // float4 per tile row
+  constexpr int RPP = kTcEpiThreads / F4R;       // tile rows covered per pass
+  constexpr int ITERS = kTcBM / RPP;
+  const int c4 = et % F4R, rbase = et / F4R;
+  const int n = n0 + 4 * c4;
+  const bool nvalid = n < N;
+  const int rows_valid = nvalid ? (M - m0 - rbase + RPP - 1) / RPP : 0;   // element i is valid iff i < rows_valid
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (kEpi == EPI_BIAS_ACT || kEpi == EPI_RELU_MASK || kEpi == EPI_GRADW) {
+    float* const Cp = ep.C;
+    float* const CTp = (kEpi != EPI_GRADW) ? ep.CT : nullptr;
+    const int ldc = ep.ldc, ldct = ep.ldct, act = ep.act;
+    float4 v[ITERS];
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
+    if (kEpi == EPI_BIAS_ACT) {
+      const float4 b = (ep.bias != nullptr && nvalid) ? __ldg(reinterpret_cast<const float4*>(ep.bias + n)) : zero4;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) { v[i].x += b.x; v[i].y += b.y; v[i].z += b.z; v[i].w += b.w; }
+      if (act == MDT_ACT_RELU) {
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          v[i].x = fmaxf(v[i].x, 0.f); v[i].y = fmaxf(v[i].y, 0.f); v[i].z = fmaxf(v[i].z, 0.f); v[i].w = fmaxf(v[i].w, 0.f);
+        }
+      } else if (act == MDT_ACT_SIGMOID) {
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i) {
+          v[i].x = fast_sigmoid(v[i].x); v[i].y = fast_sigmoid(v[i].y); v[i].z = fast_sigmoid(v[i].z); v[i].w = fast_sigmoid(v[i].w);
+        }
+      }
+    } else if (kEpi == EPI_RELU_MASK) {
+      const float* const mp = ep.mask + (size_t)(m0 + rbase) * ep.ldmask + n;
+      const size_t mstep = (size_t)RPP * ep.ldmask;
+      float4 mk[ITERS];
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) mk[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(mp + i * mstep)) : zero4;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) {
+        v[i].x = mk[i].x > 0.f ? v[i].x : 0.f; v[i].y = mk[i].y > 0.f ? v[i].y : 0.f;
+        v[i].z = mk[i].z > 0.f ? v[i].z : 0.f; v[i].w = mk[i].w > 0.f ? v[i].w : 0.f;
+      }
+    }
+    if (Cp != nullptr) {
+      float* const cp = Cp + (size_t)(m0 + rbase) * ldc + n;
+      const size_t cstep = (size_t)RPP * ldc;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i)
+        if (i < rows_valid) *reinterpret_cast<float4*>(cp + i * cstep) = v[i];
+    }
+    if (CTp != nullptr) {
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
+      ptx::bar_sync_epi();
+      tc05_store_transposed<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et);
+    }
+  } else if (kEpi == EPI_SIGMOID_BCE) {
+    const int ldc = ep.ldc;
+    const float4 b = nvalid ? __ldg(reinterpret_cast<const float4*>(ep.bias + n)) : zero4;
+    float4 v[ITERS], xv[ITERS];
+    {
+      const float* const xp = ep.x + (size_t)(m0 + rbase) * ep.ldx + n;
+      const size_t xstep = (size_t)RPP * ep.ldx;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i)
+        xv[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(xp + i * xstep)) : make_float4(.5f, .5f, .5f, .5f);
+    }
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
+    float part = 0.f;
+    float* const rp = ep.C + (size_t)(m0 + rbase) * ldc + n;       // recon
+    float* const gp = ep.da4 + (size_t)(m0 + rbase) * ldc + n;     // dL/d(logits)
+    const size_t cstep = (size_t)RPP * ldc;
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) {
+      float4 r, g;
+      r.x = fast_sigmoid(v[i].x + b.x); r.y = fast_sigmoid(v[i].y + b.y);
+      r.z = fast_sigmoid(v[i].z + b.z); r.w = fast_sigmoid(v[i].w + b.w);
+      const float term = (fast_bce_term(r.x, xv[i].x) + fast_bce_term(r.y, xv[i].y)) +
+                         (fast_bce_term(r.z, xv[i].z) + fast_bce_term(r.w, xv[i].w));
+      g.x = fast_dlogit(r.x, xv[i].x); g.y = fast_dlogit(r.y, xv[i].y);
+      g.z = fast_dlogit(r.z, xv[i].z); g.w = fast_dlogit(r.w, xv[i].w);
+      const bool ok = i < rows_valid;
+      part += ok ? term : 0.f;
+      if (ok) {
+        *reinterpret_cast<float4*>(rp + i * cstep) = r;
+        *reinterpret_cast<float4*>(gp + i * cstep) = g;
+      }
+      v[i] = g;
+    }
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
+    part = warp_sum(part);
+    if (lane == 0) red[ew] = part;
+    ptx::bar_sync_epi();
+    tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
+    if (et == 0) {
+      const int ncta = gridDim.x * gridDim.y;
+      ep.bce_partials[blockIdx.y * gridDim.x + blockIdx.x] =
+          ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
+      __threadfence();
+      if (atomicAdd(ep.ticket, 1u) == (unsigned)ncta - 1) {
+        __threadfence();
+        float tot = 0.f;
+        for (int i = 0; i < ncta; ++i) tot += __ldcg(ep.bce_partials + i);
+        float kl = 0.f;
+        for (int i = 0; i < ep.n_kl_partials; ++i) kl += __ldcg(ep.kl_partials + i);
+        *ep.loss_out = tot + kl;
+        *ep.ticket = 0;
+      }
+    }
+  } else if (kEpi == EPI_REPARAM || kEpi == EPI_REPARAM_BWD) {
+    // 128 x Z block of (row, latent) pairs.  The global inputs of the block (contiguous row ranges of eps / std /
+    // dml_kl) are first streamed into shared memory with coalesced float4 loads, so the per-pair loop below has no
+    // global-load latency in it; its stores go straight to global memory (consecutive threads -> consecutive
+    // addresses) and into a small transposed-store scratch.
+    const int Z = ep.Z;
+    const int R = min(kTcBM, M - m0);            // valid rows of this tile
+    float* const T2 = T + kTcBM * ldt;           // transposed-store scratch: [128][Z+1] or [128][2Z+1]
+    float* const S0 = T2 + kTcBM * 65;           // staged inputs
+    const int nz = R * Z;
+    if (kEpi == EPI_REPARAM) {
+      float* const sE = S0;                      // eps block [R][Z]
+      float* const sB = S0 + kTcBM * 32;         // bias [2Z]
+      {
+        const float4* src = reinterpret_cast<const float4*>(ep.eps_in + (size_t)m0 * Z);
+        float4* dst = reinterpret_cast<float4*>(sE);
+#pragma unroll
+        for (int q = 0; q < kTcBM * 32 / 4 / kTcEpiThreads; ++q) {     // fixed trip count: all loads in flight
+          const int i = et + q * kTcEpiThreads;
+          if (i < nz / 4) dst[i] = __ldg(src + i);
+        }
+        if (et < 2 * Z) sB[et] = __ldg(ep.bias + et);
+      }
+      ptx::bar_sync_epi();
+      float kl = 0.f;
+      float* const ml = ep.C + (size_t)m0 * 2 * Z;
+      float* const kk = ep.dml_kl + (size_t)m0 * 2 * Z;
+      float* const zz = ep.z + (size_t)m0 * Z;
+      float* const sdo = ep.sd_out + (size_t)m0 * Z;
+      float* const eo = (ep.eps_out != ep.eps_in) ? ep.eps_out + (size_t)m0 * Z : nullptr;
+      int r = et / Z, j = et - r * Z;
+      const int dq = kTcEpiThreads / Z, dr = kTcEpiThreads - dq * Z;
+#pragma unroll 2
+      for (int idx = et; idx < nz; idx += kTcEpiThreads) {
+        const float mu = T[r * ldt + j] + sB[j];
+        const float lv = T[r * ldt + Z + j] + sB[Z + j];
+        const float e = sE[idx];
+        const float sd = __expf(0.5f * lv);
+        const float ev = __expf(lv);
+        const float zv = mu + e * sd;
+        ml[r * 2 * Z + j] = mu;
+        ml[r * 2 * Z + Z + j] = lv;
+        zz[idx] = zv;
+        if (eo) eo[idx] = e;
+        sdo[idx] = sd;
+        kk[r * 2 * Z + j] = mu;
+        kk[r * 2 * Z + Z + j] = 0.5f * (ev - 1.0f);
+        T2[r * (Z + 1) + j] = zv;
+        kl += -0.5f * (1.0f + lv - mu * mu - ev);
+        j += dr; r += dq;
+        if (j >= Z) { j -= Z; r += 1; }
+      }
+      kl = warp_sum(kl);
+      if (lane == 0) red[ew] = kl;
+      ptx::bar_sync_epi();
+      // z^T: row j of the transposed matrix holds R consecutive floats
+      for (int idx = et; idx < Z * kTcBM; idx += kTcEpiThreads) {
+        const int jj = idx / kTcBM, rr = idx - jj * kTcBM;
+        if (rr < R) ep.zT[(size_t)jj * ep.ldzT + m0 + rr] = T2[rr * (Z + 1) + jj];
+      }
+      if (et == 0)
+        ep.kl_partials[blockIdx.y] = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
+    } else {
+      float* const sE = S0;                      // eps block
+      float* const sS = S0 + kTcBM * 32;         // std block
+      float* const sK = S0 + kTcBM * 64;         // dml_kl block [R][2Z]
+      {
+        const float4* s0 = reinterpret_cast<const float4*>(ep.eps + (size_t)m0 * Z);
+        const float4* s1 = reinterpret_cast<const float4*>(ep.sd + (size_t)m0 * Z);
+        const float4* s2 = reinterpret_cast<const float4*>(ep.dml_kl + (size_t)m0 * 2 * Z);
+        float4* d0 = reinterpret_cast<float4*>(sE);
+        float4* d1 = reinterpret_cast<float4*>(sS);
+        float4* d2 = reinterpret_cast<float4*>(sK);
+        float4 t0[4], t1[4], t2[8];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {                                   // fixed trip counts: all loads in flight
+          const int i = et + q * kTcEpiThreads;
+          if (i < nz / 4) { t0[q] = __ldg(s0 + i); t1[q] = __ldg(s1 + i); }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int i = et + q * kTcEpiThreads;
+          if (i < nz / 2) t2[q] = __ldg(s2 + i);
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          const int i = et + q * kTcEpiThreads;
+          if (i < nz / 4) { d0[i] = t0[q]; d1[i] = t1[q]; }
+        }
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          const int i = et + q * kTcEpiThreads;
+          if (i < nz / 2) d2[i] = t2[q];
+        }
+      }
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[11] = clock64();
+      ptx::bar_sync_epi();
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[12] = clock64();
+      float* const dml = ep.dml + (size_t)m0 * 2 * Z;
+      int r = et / Z, j = et - r * Z;
+      const int dq = kTcEpiThreads / Z, dr = kTcEpiThreads - dq * Z;
+#pragma unroll 2
+      for (int idx = et; idx < nz; idx += kTcEpiThreads) {
+        const float g = T[r * ldt + j];
+        const float dmu = g + sK[r * 2 * Z + j];
+        const float dlv = g * sE[idx] * sS[idx] * 0.5f + sK[r * 2 * Z + Z + j];
+        dml[r * 2 * Z + j] = dmu;
+        dml[r * 2 * Z + Z + j] = dlv;
+        T2[r * (2 * Z + 1) + j] = dmu;
+        T2[r * (2 * Z + 1) + Z + j] = dlv;
+        j += dr; r += dq;
+        if (j >= Z) { j -= Z; r += 1; }
+      }
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[13] = clock64();
+      ptx::bar_sync_epi();
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[14] = clock64();
+      for (int idx = et; idx < 2 * Z * kTcBM; idx += kTcEpiThreads) {
+        const int c = idx / kTcBM, rr = idx - c * kTcBM;
+        if (rr < R) ep.dmlT[(size_t)c * ep.ld_dmlT + m0 + rr] = T2[rr * (2 * Z + 1) + c];
+      }
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// the kernel
+// ------------------------------------------------------------------------------------------------
+template <int BN, bool kSplit, int kEpi>
+__global__ void __launch_bounds__(kTcThreads, 1)
+tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
+                 int K, Tc05Epi ep) {
+  using S = Tc05Smem<BN, kSplit>;
+  // SWIZZLE_128B needs 1024-byte aligned tiles.  The kernel has no static shared memory, so the dynamic window
+  // starts at offset 0; keeping `smem` a plain shared-space array (no integer re-alignment) lets the compiler
+  // emit LDS/STS instead of generic loads/stores for every access below.
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const uint32_t smem_base = ptx::smem_u32(smem);
+  if ((smem_base & 1023u) != 0) __trap();
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * kTcBM;
+  const int num_kb = (K + kTcBK - 1) / kTcBK;
+  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+#define TC_STAMP(i) do { if (dbg) ep.dbg[i] = clock64(); } while (0)
+  if (threadIdx.x == 0) TC_STAMP(0);
+
+  const uint32_t bar_full = smem_base + S::BAR_OFF;           // [S::STAGES] TMA bytes landed
+  const uint32_t bar_split = bar_full + 8 * S::STAGES;        // [S::STAGES] hi/lo split done (split mode)
+  const uint32_t bar_empty = bar_split + 8 * S::STAGES;       // [S::STAGES] MMAs that read the slot retired
+  const uint32_t bar_accum = bar_empty + 8 * S::STAGES;       // accumulator complete
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 1));
+  float* red = reinterpret_cast<float*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 1) + 16);  // 8 floats (one per epilogue warp)
+
+  if (threadIdx.x == 0) {
+    ptx::prefetch_tmap(&tmap_a);
+    ptx::prefetch_tmap(&tmap_b);
+    for (int s = 0; s < S::STAGES; ++s) {
+      ptx::mbar_init(bar_full + 8 * s, 1);
+      ptx::mbar_init(bar_split + 8 * s, kTcEpiThreads / 32);   // one arrival per splitter warp
+      ptx::mbar_init(bar_empty + 8 * s, 1);
+    }
+    ptx::mbar_init(bar_accum, 1);
+    ptx::fence_mbar_init();
+  }
+  if (warp == 1) {
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), BN < 32 ? 32 : BN);   // power of two, at least 32 columns
+    ptx::tmem_relinquish();
+  }
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) TC_STAMP(1);
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % S::STAGES;
+        const uint32_t ph = (kb / S::STAGES) & 1;
+        ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
+        const uint32_t sa = smem_base + s * S::STAGE;
+        ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
+        ptx::tma_load_2d(sa, &tmap_a, kb * kTcBK, m0, bar_full + 8 * s);
+        ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, kb * kTcBK, n0, bar_full + 8 * s);
+      }
+      TC_STAMP(2);
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_tf32(kTcBM, BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % S::STAGES;
+        const uint32_t ph = (kb / S::STAGES) & 1;
+        ptx::mbar_wait((kSplit ? bar_split : bar_full) + 8 * s, ph);
+        ptx::tc_fence_after();
+        if (kb == 0) TC_STAMP(3);
+        const uint32_t sa = smem_base + s * S::STAGE;
+        const uint64_t a_hi = umma_desc_sw128(sa), b_hi = umma_desc_sw128(sa + S::A_BYTES);
+#pragma unroll
+        for (int k = 0; k < kTcBK / 8; ++k) {
+          const uint64_t koff = (uint64_t)((k * 8 * 4) >> 4);   // 32 bytes per UMMA_K=8 step, in 16-byte units
+          const uint32_t first = (kb | k) ? 1u : 0u;
+          if (kSplit) {
+            const uint64_t a_lo = umma_desc_sw128(sa + S::HB), b_lo = umma_desc_sw128(sa + S::HB + S::A_BYTES);
+            ptx::mma_tf32(tmem_base, a_lo + koff, b_hi + koff, idesc, first);
+            ptx::mma_tf32(tmem_base, a_hi + koff, b_lo + koff, idesc, 1u);
+            ptx::mma_tf32(tmem_base, a_hi + koff, b_hi + koff, idesc, 1u);
+          } else {
+            ptx::mma_tf32(tmem_base, a_hi + koff, b_hi + koff, idesc, first);
+          }
+        }
+        ptx::mma_commit(bar_empty + 8 * s);
+      }
+      ptx::mma_commit(bar_accum);
+      TC_STAMP(4);
+    }
+  } else {
+    // ===== split (TF32X3) + epilogue warps =====
+    const int et = threadIdx.x - 64;              // 0..255
+    const int q = warp & 3;                       // TMEM lane quadrant this warp may read
+    const int chalf = (warp - 2) >> 2;            // which half of the accumulator columns this warp drains
+    const int row = q * 32 + lane;                // accumulator row held by this thread
+    if (kSplit) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % S::STAGES;
+        const uint32_t ph = (kb / S::STAGES) & 1;
+        ptx::mbar_wait(bar_full + 8 * s, ph);
+        if (kb == 0 && et == 0) TC_STAMP(9);
+        float4* hi = reinterpret_cast<float4*>(smem + s * S::STAGE);
+        float4* lo = reinterpret_cast<float4*>(smem + s * S::STAGE + S::HB);
+#pragma unroll 4
+        for (int c = et; c < S::HB / 16; c += kTcEpiThreads) {
+          // The tensor core reads only sign, exponent and the top 10 mantissa bits of an fp32 word (it truncates),
+          // so the raw tile already IS the "hi" operand; only lo = a - trunc_tf32(a) (exact in fp32) is written.
+          const float4 v = hi[c];
+          float4 l;
+          l.x = v.x - ptx::tf32_hi(v.x); l.y = v.y - ptx::tf32_hi(v.y);
+          l.z = v.z - ptx::tf32_hi(v.z); l.w = v.w - ptx::tf32_hi(v.w);
+          lo[c] = l;
+        }
+        if (kb == 0 && et == 0) TC_STAMP(10);
+        ptx::fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core's async proxy
+        if (kb == 0 && et == 0) TC_STAMP(11);
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar_split + 8 * s);
+      }
+    }
+    // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), overlaps the main loop
+    if (kEpi == EPI_GRADW && blockIdx.x == 0 && ep.db != nullptr) {
+      // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
+      constexpr int RW = kTcBM / (kTcEpiThreads / 32);      // rows per warp (16)
+      const int ew = et >> 5;
+      const float* const abase = ep.a_src + (size_t)(m0 + ew * RW) * ep.lda_src;
+      const size_t lda = ep.lda_src;
+      const int rows_here = min(RW, M - m0 - ew * RW);
+      float acc[RW];
+#pragma unroll
+      for (int i = 0; i < RW; ++i) acc[i] = 0.f;
+      for (int k = lane; k < K; k += 32) {                 // all RW loads of a k-slice are independent: in flight together
+        float t[RW];
+#pragma unroll
+        for (int i = 0; i < RW; ++i) t[i] = (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
+#pragma unroll
+        for (int i = 0; i < RW; ++i) acc[i] += t[i];
+      }
+#pragma unroll
+      for (int i = 0; i < RW; ++i) {
+        const float t = warp_sum(acc[i]);
+        if (lane == 0 && i < rows_here) ep.db[m0 + ew * RW + i] = t;
+      }
+    }
+
+    ptx::mbar_wait(bar_accum, 0);
+    ptx::tc_fence_after();
+    if (et == 0) TC_STAMP(5);
+    // TMEM -> registers -> padded smem tile (the ring is free: every MMA has retired)
+    float* T = reinterpret_cast<float*>(smem);
+    constexpr int CH = BN / 2 < 16 ? 16 : BN / 2; // columns per warp (BN = 16: the second warp of a quadrant idles)
+#pragma unroll
+    for (int c = 0; c < CH / 16; ++c) {
+      float v[16];
+      const int col0 = chalf * CH + c * 16;
+      if (col0 >= BN) break;
+      ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
+      float4* dst = reinterpret_cast<float4*>(T + row * S::TILE_LD + col0);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+    }
+    ptx::bar_sync_epi();
+    if (et == 0) TC_STAMP(6);
+    tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red);
+    if (et == 0) TC_STAMP(7);
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    __syncwarp();
+    ptx::tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+  }
+  if (threadIdx.x == 0) TC_STAMP(8);
+#undef TC_STAMP
+}
+
+// ------------------------------------------------------------------------------------------------
+// tiled transpose (x -> x^T per step, weight shadows after Adam, da4 -> da4^T in compat mode)
+// ------------------------------------------------------------------------------------------------
+struct TrJob {
+  const float* in;   // [R][ld_in]
+  float* out;        // [C][ld_out]
+  int R, C, ld_in, ld_out;
+  int tile_begin, tiles_c;
+};
+struct TrArgs {
+  TrJob job[4];
+  int njobs;
+};
+
+__global__ void __launch_bounds__(256) transpose_kernel(TrArgs a) {
+  __shared__ float t[32][33];
+  int j = 0;
+#pragma unroll
+  for (int q = 1; q < 4; ++q)
+    if (q < a.njobs && (int)blockIdx.x >= a.job[q].tile_begin) j = q;
+  const TrJob job = a.job[j];
+  const int tile = (int)blockIdx.x - job.tile_begin;
+  const int r0 = (tile / job.tiles_c) * 32, c0 = (tile % job.tiles_c) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+  for (int i = ty; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + tx;
+    t[i][tx] = (r < job.R && c < job.C) ? job.in[(size_t)r * job.ld_in + c] : 0.f;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int i = ty; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + tx;
+    if (c < job.C && r < job.R) job.out[(size_t)c * job.ld_out + r] = t[tx][i];
+  }
+}
+
+// Step prologue: x -> x^T (tiles) and, in the blocks after the tiles, the step's eps drawn from Philox exactly
+// as torch.randn_like would on CUDA (ref:vae-hpo.py:35); the last eps block advances the device-resident offset.
+struct PrepArgs {
+  TrArgs tr;
+  int tr_blocks;
+  float* eps_out;      // NULL: caller supplied eps, nothing to generate
+  long long n_eps;
+  StepState* st;
+  long long S;
+  unsigned long long offset_inc;
+};
+
+__global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
+  if ((int)blockIdx.x < a.tr_blocks) {
+    __shared__ float t[32][33];
+    const TrJob job = a.tr.job[0];
+    const int tile = (int)blockIdx.x;
+    const int r0 = (tile / job.tiles_c) * 32, c0 = (tile % job.tiles_c) * 32;
+    const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+#pragma unroll
+    for (int i = ty; i < 32; i += 8) {
+      const int r = r0 + i, c = c0 + tx;
+      t[i][tx] = (r < job.R && c < job.C) ? job.in[(size_t)r * job.ld_in + c] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = ty; i < 32; i += 8) {
+      const int c = c0 + i, r = r0 + tx;
+      if (c < job.C && r < job.R) job.out[(size_t)c * job.ld_out + r] = t[tx][i];
+    }
+    return;
+  }
+  const unsigned long long seed = a.st->philox_seed, offset = a.st->philox_offset;
+  const int nb = (int)gridDim.x - a.tr_blocks;
+  for (long long i = (long long)((int)blockIdx.x - a.tr_blocks) * blockDim.x + threadIdx.x; i < a.n_eps;
+       i += (long long)nb * blockDim.x)
+    a.eps_out[i] = torch_cuda_randn_elem(seed, offset, i, a.S);
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&a.st->ticket_reparam, 1u) == (unsigned)nb - 1) {
+      a.st->philox_offset = offset + a.offset_inc;
+      a.st->ticket_reparam = 0;
+      __threadfence();
+    }
+  }
+}
+
+inline int tr_add(TrArgs& a, int& blocks, const float* in, float* out, int R, int C, int ld_in, int ld_out) {
+  TrJob& j = a.job[a.njobs++];
+  j.in = in; j.out = out; j.R = R; j.C = C; j.ld_in = ld_in; j.ld_out = ld_out;
+  j.tile_begin = blocks; j.tiles_c = (C + 31) / 32;
+  blocks += ((R + 31) / 32) * j.tiles_c;
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// host side: tensor maps, launchers, the per-engine plan
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*PFN_mdt_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                        const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                        CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+inline PFN_mdt_encodeTiled tc05_encode_fn() {
+  static PFN_mdt_encodeTiled fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_mdt_encodeTiled>(p);
+  }
+  return fn;
+}
+
+// K-major fp32 matrix [rows][K] with leading dimension ld (floats); box = box_rows x 32 floats, SWIZZLE_128B.
+inline int tc05_encode(CUtensorMap* out, const float* ptr, int rows, int K, int ld, int box_rows) {
+  PFN_mdt_encodeTiled fn = tc05_encode_fn();
+  if (!fn) return set_error(MDT_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
+  MDT_CHECK(rows > 0 && K > 0 && ld >= K, "tensor map: bad shape rows=%d K=%d ld=%d", rows, K, ld);
+  MDT_CHECK(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && (ld % 4) == 0, "tensor map: base and row pitch must be 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
+  cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_error(MDT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
+  return MDT_OK;
+}
+
+// Phase-timing buffer (MDT_TC05_DBG=1): 32 slots x 16 clock64 stamps; launch i writes slot i % 32 (CTA (0,0) only).
+inline int& tc05_dbg_launch_index() { static int idx = 0; return idx; }
+inline long long* tc05_dbg_buffer() {
+  static long long* buf = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    const char* e = getenv("MDT_TC05_DBG");
+    if (e && e[0] == '1' && cudaMalloc(&buf, 512 * sizeof(long long)) == cudaSuccess) cudaMemset(buf, 0, 512 * sizeof(long long));
+  }
+  return buf;
+}
+
+template <int BN, bool kSplit, int kEpi>
+inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int N, int K, const Tc05Epi& ep, cudaStream_t s) {
+  using S = Tc05Smem<BN, kSplit>;
+  static bool attr = false;
+  if (!attr) {
+    MDT_CUDA(cudaFuncSetAttribute(tc05_gemm_kernel<BN, kSplit, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
+    attr = true;
+  }
+  dim3 grid((N + BN - 1) / BN, (M + kTcBM - 1) / kTcBM);
+  Tc05Epi epd = ep;
+  epd.dbg = tc05_dbg_buffer();
+  if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
+  tc05_gemm_kernel<BN, kSplit, kEpi><<<grid, kTcThreads, S::TOTAL, s>>>(a, b, M, N, K, epd);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
+template <int kEpi>
+inline int tc05_launch(int bn, bool split, const CUtensorMap& a, const CUtensorMap& b, int M, int N, int K, const Tc05Epi& ep,
+                       cudaStream_t s) {
+  if (bn == 16) return split ? tc05_launch_t<16, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<16, false, kEpi>(a, b, M, N, K, ep, s);
+  if (bn == 32) return split ? tc05_launch_t<32, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<32, false, kEpi>(a, b, M, N, K, ep, s);
+  if (bn == 64) return split ? tc05_launch_t<64, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<64, false, kEpi>(a, b, M, N, K, ep, s);
+  return set_error(MDT_ERR_INVALID, "unsupported BLOCK_N %d", bn);
+}
+
+// What the engine hands over: its flat buffers and activation workspaces (row-major, owned by the engine).
 struct Tc05Buffers {
   float *params, *grads;
   Layout L;
   int D, H, Z, Bmax;
   float *x_stage, *h1, *ml, *eps, *sd, *z, *h3, *recon, *da4, *da3, *dz, *dml_kl, *dml, *da1;
+  float* loss_dev;
   StepState* st;
   int sm_count, max_threads_sm;
   bool split3;
+  void* note_ctx;
+  int (*note)(void* ctx, const char* label);   // engine book-keeping after every kernel launch
+  const bool* serial;                          // when *serial is true (per-kernel profiling) nothing is forked
 };
-inline int tc05_unsupported() { return set_error(MDT_ERR_UNSUPPORTED, "tcgen05 GEMM path is not built yet"); }
-inline int tc05_create(const Tc05Buffers*, cudaStream_t, Tc05Plan**) { return tc05_unsupported(); }
-inline void tc05_destroy(Tc05Plan*) {}
-inline int tc05_forward(Tc05Plan*, cudaStream_t, const float*, int, const float*, bool) { return tc05_unsupported(); }
-inline int tc05_backward(Tc05Plan*, cudaStream_t, const float*, int) { return tc05_unsupported(); }
-inline int tc05_params_changed(Tc05Plan*, cudaStream_t) { return tc05_unsupported(); }
-inline int tc05_after_external_da4(Tc05Plan*, cudaStream_t, int) { return tc05_unsupported(); }
-inline int tc05_linear(const float*, const float*, const float*, int, int, int, int, bool, float*, cudaStream_t) {
-  return tc05_unsupported();
+
+struct Tc05ActMaps {   // tensor maps whose extents depend on the batch size B
+  CUtensorMap x, h1, z, h3, da4, da3, dml;             // A operands [B, *]
+  CUtensorMap da4T, da3T, dmlT, da1T;                  // A operands [*, B]
+  CUtensorMap h3T, zT, h1T, xT;                        // B operands [*, B]
+};
+
+struct Tc05Plan {
+  Tc05Buffers b;
+  int ldB;            // leading dimension of every transposed activation (floats)
+  int bn_h, bn_d;     // BLOCK_N used for N = H and N = D
+  int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
+  char* slab = nullptr;
+  float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials;
+  unsigned int* ticket;
+  CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights)
+  std::map<int, Tc05ActMaps> maps;
+  // weight-gradient GEMMs run on a side stream, off the dX critical path (fork/join by events; capturable)
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_fork[4] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t ev_join = nullptr;
+};
+
+#define TC_NOTE(p, label) MDT_TRY((p)->b.note((p)->b.note_ctx, label))
+
+inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
+  const Tc05Buffers& b = p->b;
+  TrArgs a{};
+  int blocks = 0;
+  tr_add(a, blocks, b.params + b.L.off[W4], p->W4T, b.D, b.H, b.H, b.D);
+  tr_add(a, blocks, b.params + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H);
+  tr_add(a, blocks, b.params + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z);
+  transpose_kernel<<<blocks, 256, 0, s>>>(a);
+  TC_NOTE(p, "weights_T");
+  return MDT_OK;
 }
+
+inline int tc05_params_changed(Tc05Plan* p, cudaStream_t s) { return tc05_weight_shadows(p, s); }
+
+inline void tc05_destroy(Tc05Plan* p) {
+  if (!p) return;
+  if (p->side) cudaStreamDestroy(p->side);
+  for (auto& ev : p->ev_fork) if (ev) cudaEventDestroy(ev);
+  if (p->ev_join) cudaEventDestroy(p->ev_join);
+  if (p->slab) cudaFree(p->slab);
+  delete p;
+}
+
+inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) {
+  const Tc05Buffers& b = *bufs;
+  MDT_CHECK(2 * b.Z <= 64 && b.Z <= 32, "tcgen05 path supports latent <= 32 (got %d)", b.Z);
+  Tc05Plan* p = new Tc05Plan();
+  p->b = b;
+  p->ldB = (int)round_up(b.Bmax, 4);
+  p->bn_h = b.H >= 2048 ? 64 : 32;
+  p->bn_d = b.Bmax > 512 ? 64 : 32;
+  p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
+  const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
+  struct Item { float** ptr; size_t n; };
+  Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
+                  {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
+                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}};
+  size_t bytes = 256;
+  for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
+  cudaError_t ce = cudaMalloc(&p->slab, bytes);
+  if (ce != cudaSuccess) { delete p; return set_error(MDT_ERR_CUDA, "cudaMalloc(%zu) for the tcgen05 plan: %s", bytes, cudaGetErrorString(ce)); }
+  cudaMemsetAsync(p->slab, 0, bytes, s);
+  char* q = p->slab;
+  p->ticket = reinterpret_cast<unsigned int*>(q);
+  q += 256;
+  for (auto& it : items) { *it.ptr = reinterpret_cast<float*>(q); q += (it.n * sizeof(float) + 255) / 256 * 256; }
+  int r = MDT_OK;
+  if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "side stream");
+  for (auto& ev : p->ev_fork)
+    if (r == MDT_OK && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
+  if (r == MDT_OK && cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
+  const float* P = b.params;
+  if (r == MDT_OK) r = tc05_encode(&p->mW1, P + b.L.off[W1], b.H, b.D, b.D, p->bn_h);
+  if (r == MDT_OK) r = tc05_encode(&p->mW2x, P + b.L.off[W2X], 2 * b.Z, b.H, b.H, 64);
+  if (r == MDT_OK) r = tc05_encode(&p->mW3, P + b.L.off[W3], b.H, b.Z, b.Z, p->bn_h);
+  if (r == MDT_OK) r = tc05_encode(&p->mW4, P + b.L.off[W4], b.D, b.H, b.H, p->bn_fc4);
+  if (r == MDT_OK) r = tc05_encode(&p->mW4T, p->W4T, b.H, b.D, b.D, p->bn_h);
+  if (r == MDT_OK) r = tc05_encode(&p->mW3T, p->W3T, b.Z, b.H, b.H, 32);
+  if (r == MDT_OK) r = tc05_encode(&p->mW2xT, p->W2xT, b.H, 2 * b.Z, 2 * b.Z, p->bn_h);
+  if (r == MDT_OK) r = tc05_weight_shadows(p, s);
+  if (r != MDT_OK) { tc05_destroy(p); return r; }
+  *out = p;
+  return MDT_OK;
+}
+
+inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
+  auto it = p->maps.find(B);
+  if (it == p->maps.end()) {
+    const Tc05Buffers& b = p->b;
+    Tc05ActMaps m;
+    const int ldB = p->ldB;
+    MDT_TRY(tc05_encode(&m.x, b.x_stage, B, b.D, b.D, kTcBM));
+    MDT_TRY(tc05_encode(&m.h1, b.h1, B, b.H, b.H, kTcBM));
+    MDT_TRY(tc05_encode(&m.z, b.z, B, b.Z, b.Z, kTcBM));
+    MDT_TRY(tc05_encode(&m.h3, b.h3, B, b.H, b.H, kTcBM));
+    MDT_TRY(tc05_encode(&m.da4, b.da4, B, b.D, b.D, kTcBM));
+    MDT_TRY(tc05_encode(&m.da3, b.da3, B, b.H, b.H, kTcBM));
+    MDT_TRY(tc05_encode(&m.dml, b.dml, B, 2 * b.Z, 2 * b.Z, kTcBM));
+    MDT_TRY(tc05_encode(&m.da4T, p->da4T, b.D, B, ldB, kTcBM));
+    MDT_TRY(tc05_encode(&m.da3T, p->da3T, b.H, B, ldB, kTcBM));
+    MDT_TRY(tc05_encode(&m.dmlT, p->dmlT, 2 * b.Z, B, ldB, kTcBM));
+    MDT_TRY(tc05_encode(&m.da1T, p->da1T, b.H, B, ldB, kTcBM));
+    MDT_TRY(tc05_encode(&m.h3T, p->h3T, b.H, B, ldB, p->bn_h));
+    MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32));
+    MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_h));
+    MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_d));
+    it = p->maps.emplace(B, m).first;
+  }
+  *out = &it->second;
+  return MDT_OK;
+}
+
+// Forward.  fuse_loss: fc4's epilogue also produces the loss, d(logits) and its transpose (training step);
+// otherwise fc4 stops at recon (mdt_forward / eval / decode) and the stand-alone loss kernel may follow.
+inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, const float* eps_in, bool decode_only,
+                        bool fuse_loss) {
+  const Tc05Buffers& b = p->b;
+  const bool sp = b.split3;
+  const int D = b.D, H = b.H, Z = b.Z;
+  const float* P = b.params;
+  Tc05ActMaps* m = nullptr;
+  MDT_TRY(tc05_act_maps(p, B, &m));
+  if (!decode_only) {
+    MDT_CHECK(x == b.x_stage, "tcgen05 path reads x from the engine's stage buffer");
+    {
+      PrepArgs pa{};
+      int blocks = 0;
+      tr_add(pa.tr, blocks, x, p->xT, B, D, D, p->ldB);
+      pa.tr_blocks = blocks;
+      if (eps_in == nullptr) {
+        pa.eps_out = b.eps; pa.n_eps = (long long)B * Z; pa.st = b.st;
+        torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
+        blocks += (int)((pa.n_eps + 255) / 256);
+        eps_in = b.eps;
+      }
+      prep_kernel<<<blocks, 256, 0, s>>>(pa);
+      TC_NOTE(p, "prep_xT_eps");
+    }
+    Tc05Epi e1{};
+    e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s));
+    TC_NOTE(p, "fc1_fwd");
+    Tc05Epi e2{};
+    e2.C = b.ml; e2.ldc = 2 * Z; e2.bias = P + b.L.off[B2X]; e2.eps_in = eps_in;
+    e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
+    e2.kl_partials = p->kl_partials;
+    MDT_TRY(tc05_launch<EPI_REPARAM>(64, sp, m->h1, p->mW2x, B, 2 * Z, H, e2, s));
+    TC_NOTE(p, "fc2x_reparam_fwd");
+  }
+  Tc05Epi e3{};
+  e3.C = b.h3; e3.ldc = H; e3.CT = p->h3T; e3.ldct = p->ldB; e3.bias = P + b.L.off[B3]; e3.act = MDT_ACT_RELU;
+  MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->z, p->mW3, B, H, Z, e3, s));
+  TC_NOTE(p, "fc3_fwd");
+  if (fuse_loss && !decode_only) {
+    Tc05Epi e4{};
+    e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
+    e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
+    e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + kTcBM - 1) / kTcBM;
+    MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s));
+    TC_NOTE(p, "fc4_bce_fwd");
+  } else {
+    Tc05Epi e4{};
+    e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.act = MDT_ACT_SIGMOID;
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s));
+    TC_NOTE(p, "fc4_fwd");
+  }
+  return MDT_OK;
+}
+
+// da4 (row-major) was produced outside the fused forward (stand-alone loss kernel / compat backward): make da4^T.
+inline int tc05_after_external_da4(Tc05Plan* p, cudaStream_t s, int B) {
+  TrArgs a{};
+  int blocks = 0;
+  tr_add(a, blocks, p->b.da4, p->da4T, B, p->b.D, p->b.D, p->ldB);
+  transpose_kernel<<<blocks, 256, 0, s>>>(a);
+  TC_NOTE(p, "da4_T");
+  return MDT_OK;
+}
+
+// Backward from da4 / da4^T and dml_kl: fills the flat gradient buffer (weights and biases).
+inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
+  const Tc05Buffers& b = p->b;
+  const bool sp = b.split3;
+  const int D = b.D, H = b.H, Z = b.Z, ldB = p->ldB;
+  float* G = b.grads;
+  Tc05ActMaps* m = nullptr;
+  MDT_TRY(tc05_act_maps(p, B, &m));
+  (void)x;   // x^T was written by this step's forward prologue
+  const bool fork = !(b.serial && *b.serial);
+  cudaStream_t sw = fork ? p->side : s;          // stream of the weight-gradient GEMMs
+  int nf = 0;
+  auto fork_point = [&]() -> int {               // everything enqueued on `s` so far is visible to later work on `sw`
+    if (!fork) return MDT_OK;
+    MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
+    MDT_CUDA(cudaStreamWaitEvent(sw, p->ev_fork[nf], 0));
+    ++nf;
+    return MDT_OK;
+  };
+  Tc05Epi e{};
+  // critical path on `s`: fc4 dX -> dz/reparam -> fc2x dX ; weight gradients trail on `sw`
+  MDT_TRY(fork_point());                          // da4^T, h3^T ready
+  e = Tc05Epi{};
+  e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_h, sp, m->da4T, m->h3T, D, H, B, e, sw));
+  TC_NOTE(p, "fc4_dW");
+  e = Tc05Epi{};
+  e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
+  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s));
+  TC_NOTE(p, "fc4_dX");
+  MDT_TRY(fork_point());                          // da3^T ready (z^T since the forward)
+  e = Tc05Epi{};
+  e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
+  MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw));
+  TC_NOTE(p, "fc3_dW");
+  e = Tc05Epi{};
+  e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(32, sp, m->da3, p->mW3T, B, Z, H, e, s));
+  TC_NOTE(p, "fc3_dX_reparam_bwd");
+  MDT_TRY(fork_point());                          // dml^T ready
+  e = Tc05Epi{};
+  e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_h, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw));
+  TC_NOTE(p, "fc2x_dW");
+  e = Tc05Epi{};
+  e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
+  TC_NOTE(p, "fc2x_dX");
+  MDT_TRY(fork_point());                          // da1^T ready
+  e = Tc05Epi{};
+  e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_d, sp, m->da1T, m->xT, H, D, B, e, sw));
+  TC_NOTE(p, "fc1_dW");
+  if (fork) {                                     // join: the gradient buffer is complete once `sw` drains
+    MDT_CUDA(cudaEventRecord(p->ev_join, sw));
+    MDT_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
+  }
+  return MDT_OK;
+}
+
+// Stand-alone y = act(x W^T + b) on the tensor cores (mdt_linear): builds its two tensor maps per call.
+inline int tc05_linear(const float* x, const float* w, const float* bias, int M, int N, int K, int act, bool split,
+                       float* y, cudaStream_t s) {
+  MDT_CHECK(K % 4 == 0 && N % 4 == 0, "tcgen05 mdt_linear needs K %% 4 == 0 and N %% 4 == 0 (16-byte rows), got K=%d N=%d", K, N);
+  CUtensorMap ma, mb;
+  const int bn = (N > 32) ? 64 : 32;
+  MDT_TRY(tc05_encode(&ma, x, M, K, K, kTcBM));
+  MDT_TRY(tc05_encode(&mb, w, N, K, K, bn));
+  Tc05Epi e{};
+  e.C = y; e.ldc = N; e.bias = bias; e.act = act;
+  return tc05_launch<EPI_BIAS_ACT>(bn, split, ma, mb, M, N, K, e, s);
+}
+
 }  // namespace mdt

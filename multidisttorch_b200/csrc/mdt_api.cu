@@ -146,6 +146,8 @@ __global__ void spin_kernel(long long ns) {
   } while ((long long)(t1 - t0) < ns);
 }
 
+int note_cb(void* ctx, const char* label) { return note_launch(static_cast<mdt_engine*>(ctx), label); }
+
 int carve_workspace(mdt_engine* e) {
   const size_t B = e->Bmax, D = e->D, H = e->H, Z = e->Z;
   struct Item { float** p; size_t n; };
@@ -255,11 +257,13 @@ int enqueue_adam(mdt_engine* e, float grad_scale) {
   AdamArgs a{};
   a.p = e->params; a.g = e->grads; a.m = e->m; a.v = e->v; a.n = e->L.total; a.st = e->st; a.grad_scale = grad_scale;
   adam_flat_kernel<<<adam_grid(a.n, e->dev->sm_count), kAdamThreads, 0, e->stream>>>(a);
-  return note_launch(e, "adam_flat");
+  MDT_TRY(note_launch(e, "adam_flat"));
+  if (e->tc) MDT_TRY(tc05_params_changed(e->tc, e->stream));   // refresh the transposed weight shadows
+  return MDT_OK;
 }
 
 int enqueue_forward(mdt_engine* e, const float* x, int B, const float* eps_in, bool decode_only) {
-  if (e->tc) return tc05_forward(e->tc, e->stream, x, B, eps_in, decode_only);
+  if (e->tc) return tc05_forward(e->tc, e->stream, x, B, eps_in, decode_only, /*fuse_loss=*/false);
   return enqueue_forward_fp32(e, x, B, eps_in, decode_only);
 }
 int enqueue_backward(mdt_engine* e, const float* x, int B) {
@@ -328,23 +332,28 @@ int allreduce_grads(mdt_engine* e) {
   return MDT_OK;
 }
 
+// forward + loss + backward of one step.  On the tcgen05 path the loss and d(logits) come out of fc4's epilogue.
+int enqueue_fwd_loss_bwd(mdt_engine* e, const float* x, int B, const float* eps) {
+  if (e->tc) {
+    MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
+    return tc05_backward(e->tc, e->stream, x, B);
+  }
+  MDT_TRY(enqueue_forward_fp32(e, x, B, eps, false));
+  MDT_TRY(enqueue_loss(e, x, B, true));
+  return enqueue_backward_fp32(e, x, B);
+}
+
 int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   e->last_B = B;
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
   if (e->gsize == 1) {
     return run_cached(e, /*kind=*/0, B, eps != nullptr, [&]() -> int {
-      MDT_TRY(enqueue_forward(e, x, B, eps, false));
-      MDT_TRY(enqueue_loss(e, x, B, true));
-      MDT_TRY(enqueue_backward(e, x, B));
+      MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
       return enqueue_adam(e, gscale);
     });
   }
-  MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int {
-    MDT_TRY(enqueue_forward(e, x, B, eps, false));
-    MDT_TRY(enqueue_loss(e, x, B, true));
-    return enqueue_backward(e, x, B);
-  }));
+  MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
   MDT_TRY(allreduce_grads(e));
   return run_cached(e, /*kind=*/2, 0, 0, [&]() -> int { return enqueue_adam(e, gscale); });
 }
@@ -445,6 +454,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
     b.x_stage = e->x_stage; b.h1 = e->h1; b.ml = e->ml; b.eps = e->eps; b.sd = e->sd; b.z = e->z; b.h3 = e->h3;
     b.recon = e->recon; b.da4 = e->da4; b.da3 = e->da3; b.dz = e->dz; b.dml_kl = e->dml_kl; b.dml = e->dml; b.da1 = e->da1;
     b.st = e->st; b.sm_count = e->dev->sm_count; b.max_threads_sm = e->dev->max_threads_sm;
+    b.loss_dev = e->loss_dev; b.note_ctx = e; b.note = note_cb; b.serial = &e->prof_on;
     b.split3 = (e->cfg.gemm_mode == MDT_GEMM_TF32X3);
     MDT_TRY(tc05_create(&b, e->stream, &e->tc));
   }
@@ -464,7 +474,9 @@ int mdt_engine_broadcast_params(mdt_engine* e) {
 
 int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_steps) {
   MDT_CHECK(e && h, "NULL argument");
-  struct { long long t; double lr, b1, b2, eps; } host{completed_steps, h->lr, h->beta1, h->beta2, h->eps};
+  struct { long long t; double lr, b1, b2, eps, b1_pow, b2_pow; } host{
+      completed_steps, h->lr, h->beta1, h->beta2, h->eps, pow(h->beta1, (double)completed_steps),
+      pow(h->beta2, (double)completed_steps)};
   MDT_CUDA(cudaMemcpyAsync(&e->st->adam_t, &host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
   MDT_CUDA(cudaStreamSynchronize(e->stream));  // `host` lives on this stack frame
   return MDT_OK;
@@ -776,6 +788,16 @@ int mdt_loss_bce_kl_noalloc(const float* recon, const float* x, const float* mu,
   const int grid = loss_grid(elems);   // <= kNoAllocMaxBlocks because of the size check above
   loss_bce_kl_kernel<false><<<grid, kLossThreads, 0, s>>>(a);
   MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
+// Debug aid (not part of the public header): copies the 16 phase-timing stamps of the latest tcgen05 launch.
+int mdt_debug_tc05_stamps(long long* out512, int reset_index) {
+  long long* buf = tc05_dbg_buffer();
+  if (!buf || !out512) return set_error(MDT_ERR_STATE, "set MDT_TC05_DBG=1 before the first tcgen05 launch");
+  MDT_CUDA(cudaDeviceSynchronize());
+  MDT_CUDA(cudaMemcpy(out512, buf, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
+  if (reset_index) tc05_dbg_launch_index() = 0;
   return MDT_OK;
 }
 

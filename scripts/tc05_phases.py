@@ -1,0 +1,28 @@
+"""Phase timing of CTA (0,0) of every tcgen05 GEMM in one un-graphed training step (MDT_TC05_DBG=1)."""
+import os, sys, ctypes as C
+os.environ["MDT_TC05_DBG"] = "1"
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np, torch
+from multidisttorch_b200 import engine as E, _lib
+from oracle import vae_numpy as O
+lib = _lib.load()
+names = ["entry", "setup", "tma_issued", "first_data", "mma_done", "accum_seen", "drained", "epi_done", "exit"]
+labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dW", "fc4_dX", "fc3_dW", "dz_reparam_bwd", "fc2x_dW", "fc2x_dX", "fc1_dW"]
+out = (C.c_longlong * 512)()
+for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
+    H = int(os.environ.get("H", "400")); B = int(os.environ.get("B", "128"))
+    eng = E.VAEEngine(hidden=H, max_batch=B, gemm_mode=mode, use_graph=False)
+    eng.load_segments(O.init_params(1, O.Dims(H=H)))
+    x = torch.rand(B, 784, device="cuda")
+    for _ in range(3):
+        eng.train_step(x, None)
+    eng.synchronize(); lib.mdt_debug_tc05_stamps(out, 1)
+    eng.train_step(x, None)
+    eng.synchronize(); lib.mdt_debug_tc05_stamps(out, 1)
+    print(f"== {mode} H={H} B={B}: cycles from CTA(0,0) entry (1 cycle = 0.51 ns)")
+    for i, lab in enumerate(labels):
+        st = list(out)[16 * i: 16 * i + 16]
+        d = {n: st[j] - st[0] for j, n in enumerate(names)}
+        extra = [st[j] - st[0] for j in (11, 12, 13, 14) if st[j] > 0]
+        print(f"  {lab:16s}", " ".join(f"{n}={v}" for n, v in d.items() if n != "entry"), "extra", extra)
+    eng.close()
