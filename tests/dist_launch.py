@@ -14,7 +14,20 @@ def next_port():
         return s.getsockname()[1]
 
 
+_RENDEZVOUS_ERRORS = ("Address already in use", "Connection refused", "Connection reset", "timed out", "Timed out",
+                      "failed to connect", "Broken pipe")
+
+
 def launch(world, argv, script=None, extra_env=None, timeout=300, cwd=None):
+    """Run `world` ranks; one retry on a fresh port if the TCP rendezvous itself failed (the free port found by
+    next_port() can be taken by another process before rank 0 binds it)."""
+    out = _launch_once(world, argv, script, extra_env, timeout, cwd)
+    if any(out[1]) and any(e in log for log in out[2] for e in _RENDEZVOUS_ERRORS):
+        out = _launch_once(world, argv, script, extra_env, timeout, cwd)
+    return out
+
+
+def _launch_once(world, argv, script=None, extra_env=None, timeout=300, cwd=None):
     out_dir = tempfile.mkdtemp(prefix="mdt_test_")
     port = next_port()
     procs = []
