@@ -1,0 +1,60 @@
+"""One GPU rank of the multi-GPU parity check (launched by tests/test_gpu_multi.py or by hand):
+utils.setup_ddp / setup_ddp_groups -> engine on the subgroup's NCCL communicator -> N steps against the golden
+vectors the reference's real DDP (gloo) produced."""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from utils import *  # noqa: E402,F401,F403
+from multidisttorch_b200.engine import VAEEngine  # noqa: E402
+from oracle import vae_numpy as O  # noqa: E402
+from tests.golden_cases import PARAM_SEED, batch_seed, check_fp, load  # noqa: E402
+
+
+def main():
+    tag, mode, out_dir = sys.argv[1], sys.argv[2], sys.argv[3]
+    g = load(tag)
+    world, ng, B, n = (int(g[k]) for k in ("world", "ngroups", "B", "n_steps"))
+    size, rank = setup_ddp()
+    assert size == world, (size, world)
+    groups = setup_ddp_groups(ng)
+    gid = next(i for i, gr in enumerate(groups) if dist.get_rank(gr) >= 0)
+    group = groups[gid]
+    grank = dist.get_rank(group)
+    eng = VAEEngine(max_batch=B, gemm_mode=mode, group=group)
+    # only group-rank 0 holds the real initial parameters: the broadcast must overwrite the others (DDP ctor)
+    eng.load_segments(O.init_params(PARAM_SEED + gid if grank == 0 else 999 + rank))
+    eng.broadcast_params()
+    tol = {"fp32": (1e-5, 1e-4), "tf32x3": (1e-5, 3e-3), "tf32": (1e-3, 1e-1)}[mode]
+    res = {"rank": rank, "gid": gid, "losses": []}
+    for t in range(n):
+        x, eps = O.make_batch(batch_seed(t, rank), B)
+        loss = float(eng.train_step(torch.from_numpy(x).cuda(), torch.from_numpy(eps).cuda()).item())
+        ref = float(g[f"losses.rank{rank}"][t])
+        assert abs(loss - ref) <= tol[0] * abs(ref), (tag, mode, rank, t, loss, ref)
+        res["losses"].append(loss)
+    p = eng.segments_to_numpy()
+    for k in O.SEGMENTS:
+        check_fp(g, f"g{gid}.paramN", k, p[k], tol[1], f"{tag}/{mode}/rank{rank}")
+    # ranks of a group must hold bit-identical parameters
+    flat = eng.params.clone()
+    gathered = [torch.empty_like(flat) for _ in range(dist.get_world_size(group))]
+    dist.all_gather(gathered, flat, group=group)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "group ranks diverged"
+    res["ok"] = True
+    dist.barrier()
+    with open(os.path.join(out_dir, f"rank{rank}.json"), "w") as f:
+        json.dump(res, f)
+    eng.close()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
