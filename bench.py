@@ -322,7 +322,7 @@ def run_own(args):
             "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches), "roofline": roofline,
             "cpu_baseline": cpu_baseline, "layouts": layouts, "kernels": kernels,
         }
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -418,10 +418,28 @@ def run_reference_arm(args):
         "e2e": {"value": round(r["value"], 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(out), flush=True)
+    emit(out)
+
+
+_REAL_STDOUT = None
+
+
+def emit(obj):
+    """The ONE JSON line goes to the real stdout; everything else (NCCL banners, torchrun notes, C-level prints)
+    was redirected to stderr at start-up."""
+    line = json.dumps(obj) + "\n"
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, line.encode())
+    else:
+        sys.stdout.write(line)
+        sys.stdout.flush()
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)          # fd 1 -> stderr for libraries that print to stdout
     args = parse_args()
     if args.ref_worker:
         return ref_worker(args)

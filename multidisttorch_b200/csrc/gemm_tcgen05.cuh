@@ -501,9 +501,13 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const uint32_t bar_full = smem_base + S::BAR_OFF;           // [S::STAGES] TMA bytes landed
   const uint32_t bar_split = bar_full + 8 * S::STAGES;        // [S::STAGES] hi/lo split done (split mode)
   const uint32_t bar_empty = bar_split + 8 * S::STAGES;       // [S::STAGES] MMAs that read the slot retired
-  const uint32_t bar_accum = bar_empty + 8 * S::STAGES;       // accumulator complete
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 1));
-  float* red = reinterpret_cast<float*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 1) + 16);  // 8 floats (one per epilogue warp)
+  const uint32_t bar_accum = bar_empty + 8 * S::STAGES;       // accumulator complete (single-pass mode)
+  const uint32_t bar_afull = bar_accum + 8;                   // [2] partial accumulator of a k-block ready (TF32X3)
+  const uint32_t bar_aempty = bar_afull + 16;                 // [2] partial accumulator drained (TF32X3)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5));
+  float* red = reinterpret_cast<float*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5) + 16);  // 8 floats (one per epilogue warp)
+  constexpr int kDrainWarps = BN >= 32 ? kTcEpiThreads / 32 : 4;   // warps that own accumulator columns
+  constexpr int kTmemCols = kSplit ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
 
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmap_a);
@@ -514,10 +518,14 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::mbar_init(bar_empty + 8 * s, 1);
     }
     ptx::mbar_init(bar_accum, 1);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(bar_afull + 8 * i, 1);
+      ptx::mbar_init(bar_aempty + 8 * i, kDrainWarps);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 1) {
-    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), BN < 32 ? 32 : BN);   // power of two, at least 32 columns
+    ptx::tmem_alloc(ptx::smem_u32(tmem_slot), kTmemCols);   // power of two, at least 32 columns
     ptx::tmem_relinquish();
   }
   ptx::tc_fence_before();
@@ -548,26 +556,33 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         const int s = kb % S::STAGES;
         const uint32_t ph = (kb / S::STAGES) & 1;
         ptx::mbar_wait((kSplit ? bar_split : bar_full) + 8 * s, ph);
+        // TF32X3: every k-block accumulates into a fresh TMEM buffer (two, alternating) that the epilogue warps
+        // drain and add in fp32 registers.  The tensor core's own fp32 accumulation rounds toward zero, so a long
+        // chain in TMEM loses ~K * 2^-24; keeping each chain to 12 MMAs and summing the partials with round-to-nearest
+        // FADDs restores fp32-grade accuracy.
+        const int ab = kb & 1;
+        if (kSplit) ptx::mbar_wait(bar_aempty + 8 * ab, ((kb >> 1) & 1) ^ 1);
         ptx::tc_fence_after();
         if (kb == 0) TC_STAMP(3);
         const uint32_t sa = smem_base + s * S::STAGE;
+        const uint32_t td = tmem_base + (kSplit ? (uint32_t)(ab * BN) : 0u);
         const uint64_t a_hi = umma_desc_sw128(sa), b_hi = umma_desc_sw128(sa + S::A_BYTES);
 #pragma unroll
         for (int k = 0; k < kTcBK / 8; ++k) {
           const uint64_t koff = (uint64_t)((k * 8 * 4) >> 4);   // 32 bytes per UMMA_K=8 step, in 16-byte units
-          const uint32_t first = (kb | k) ? 1u : 0u;
           if (kSplit) {
             const uint64_t a_lo = umma_desc_sw128(sa + S::HB), b_lo = umma_desc_sw128(sa + S::HB + S::A_BYTES);
-            ptx::mma_tf32(tmem_base, a_lo + koff, b_hi + koff, idesc, first);
-            ptx::mma_tf32(tmem_base, a_hi + koff, b_lo + koff, idesc, 1u);
-            ptx::mma_tf32(tmem_base, a_hi + koff, b_hi + koff, idesc, 1u);
+            ptx::mma_tf32(td, a_lo + koff, b_hi + koff, idesc, k ? 1u : 0u);
+            ptx::mma_tf32(td, a_hi + koff, b_lo + koff, idesc, 1u);
+            ptx::mma_tf32(td, a_hi + koff, b_hi + koff, idesc, 1u);
           } else {
-            ptx::mma_tf32(tmem_base, a_hi + koff, b_hi + koff, idesc, first);
+            ptx::mma_tf32(td, a_hi + koff, b_hi + koff, idesc, (kb | k) ? 1u : 0u);
           }
         }
         ptx::mma_commit(bar_empty + 8 * s);
+        if (kSplit) ptx::mma_commit(bar_afull + 8 * ab);
       }
-      ptx::mma_commit(bar_accum);
+      if (!kSplit) ptx::mma_commit(bar_accum);
       TC_STAMP(4);
     }
   } else {
@@ -576,7 +591,29 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int q = warp & 3;                       // TMEM lane quadrant this warp may read
     const int chalf = (warp - 2) >> 2;            // which half of the accumulator columns this warp drains
     const int row = q * 32 + lane;                // accumulator row held by this thread
+    constexpr int CH = BN / 2 < 16 ? 16 : BN / 2; // accumulator columns per warp (BN = 16: the second warp of a quadrant idles)
+    const int colw = chalf * CH;                  // first column of this warp
+    const bool drains = colw < BN;
+    float pacc[kSplit ? CH : 1];                  // TF32X3: running fp32 sum of the per-k-block partial accumulators
     if (kSplit) {
+#pragma unroll
+      for (int i = 0; i < CH; ++i) pacc[i] = 0.f;
+      auto drain = [&](int j) {
+        if (!drains) return;
+        const int ab = j & 1;
+        ptx::mbar_wait(bar_afull + 8 * ab, (j >> 1) & 1);
+        ptx::tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < CH / 16; ++c) {
+          float v[16];
+          ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colw + c * 16), v);
+#pragma unroll
+          for (int i = 0; i < 16; ++i) pacc[c * 16 + i] += v[i];
+        }
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(bar_aempty + 8 * ab);
+      };
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % S::STAGES;
         const uint32_t ph = (kb / S::STAGES) & 1;
@@ -599,7 +636,9 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         if (kb == 0 && et == 0) TC_STAMP(11);
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(bar_split + 8 * s);
+        if (kb >= 1) drain(kb - 1);               // the MMAs of the previous k-block have had a whole split to finish
       }
+      drain(num_kb - 1);
     }
     // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), overlaps the main loop
     if (kEpi == EPI_GRADW && blockIdx.x == 0 && ep.db != nullptr) {
@@ -626,21 +665,30 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
 
-    ptx::mbar_wait(bar_accum, 0);
-    ptx::tc_fence_after();
+    if (!kSplit) {
+      ptx::mbar_wait(bar_accum, 0);
+      ptx::tc_fence_after();
+    }
     if (et == 0) TC_STAMP(5);
-    // TMEM -> registers -> padded smem tile (the ring is free: every MMA has retired)
+    // accumulator -> padded smem tile (the ring is free: every MMA has retired and, in TF32X3 mode, every warp has
+    // passed its last split; the barrier below orders the tile writes against stragglers' lo-writes of the last stage)
     float* T = reinterpret_cast<float*>(smem);
-    constexpr int CH = BN / 2 < 16 ? 16 : BN / 2; // columns per warp (BN = 16: the second warp of a quadrant idles)
+    if (kSplit) ptx::bar_sync_epi();
+    if (drains) {
 #pragma unroll
-    for (int c = 0; c < CH / 16; ++c) {
-      float v[16];
-      const int col0 = chalf * CH + c * 16;
-      if (col0 >= BN) break;
-      ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
-      float4* dst = reinterpret_cast<float4*>(T + row * S::TILE_LD + col0);
+      for (int c = 0; c < CH / 16; ++c) {
+        float v[16];
+        const int col0 = colw + c * 16;
+        if (kSplit) {
 #pragma unroll
-      for (int j = 0; j < 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int i = 0; i < 16; ++i) v[i] = pacc[c * 16 + i];
+        } else {
+          ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
+        }
+        float4* dst = reinterpret_cast<float4*>(T + row * S::TILE_LD + col0);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+      }
     }
     ptx::bar_sync_epi();
     if (et == 0) TC_STAMP(6);
@@ -652,7 +700,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   if (warp == 1) {
     __syncwarp();
-    ptx::tmem_dealloc(tmem_base, BN < 32 ? 32 : BN);
+    ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
   if (threadIdx.x == 0) TC_STAMP(8);
 #undef TC_STAMP
