@@ -171,6 +171,8 @@ struct Tc05Epi {
   const float* a_src; int lda_src; float* db;
   // reparameterisation (backward)
   const float *eps, *sd; float *dml, *dmlT; int ld_dmlT;
+  // split-K workspace: [tile][split][128*BN] partial tiles + one ticket counter per tile
+  float* ws; unsigned int* ws_counters;
   // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
   long long* dbg;
 };
@@ -493,7 +495,11 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if ((smem_base & 1023u) != 0) __trap();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * kTcBM;
-  const int num_kb = (K + kTcBK - 1) / kTcBK;
+  // split-K: gridDim.z CTAs share one output tile, each streaming a contiguous range of k-blocks
+  const int total_kb = (K + kTcBK - 1) / kTcBK;
+  const int kb_per_split = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
+  const int kb0 = (int)blockIdx.z * kb_per_split;
+  const int num_kb = min(kb_per_split, total_kb - kb0);      // >= 1 (the host picks gridDim.z accordingly)
   const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
 #define TC_STAMP(i) do { if (dbg) ep.dbg[i] = clock64(); } while (0)
   if (threadIdx.x == 0) TC_STAMP(0);
@@ -543,8 +549,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
         const uint32_t sa = smem_base + s * S::STAGE;
         ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
-        ptx::tma_load_2d(sa, &tmap_a, kb * kTcBK, m0, bar_full + 8 * s);
-        ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, kb * kTcBK, n0, bar_full + 8 * s);
+        ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * s);
+        ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * s);
       }
       TC_STAMP(2);
     }
@@ -641,7 +647,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       drain(num_kb - 1);
     }
     // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), overlaps the main loop
-    if (kEpi == EPI_GRADW && blockIdx.x == 0 && ep.db != nullptr) {
+    if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
       // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
       constexpr int RW = kTcBM / (kTcEpiThreads / 32);      // rows per warp (16)
       const int ew = et >> 5;
@@ -692,7 +698,55 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     ptx::bar_sync_epi();
     if (et == 0) TC_STAMP(6);
-    tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red);
+    bool run_epilogue = true;
+    if (gridDim.z > 1) {
+      // Deterministic split-K reduction: every split parks its partial tile in the workspace; the CTA that takes the
+      // last ticket of the tile adds the partials in split order (independent of arrival order) and runs the epilogue.
+      constexpr int F4 = kTcBM * BN / 4;                       // float4 per tile
+      constexpr int PER = (F4 + kTcEpiThreads - 1) / kTcEpiThreads;
+      const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+      const int nsplit = gridDim.z;
+      float4* const ws = reinterpret_cast<float4*>(ep.ws) + (size_t)tile_id * nsplit * F4;
+      float4* const mine = ws + (size_t)blockIdx.z * F4;
+#pragma unroll
+      for (int i = 0; i < PER; ++i) {
+        const int f = et + i * kTcEpiThreads;
+        if (f < F4) mine[f] = *reinterpret_cast<const float4*>(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4);
+      }
+      __threadfence();
+      ptx::bar_sync_epi();
+      if (et == 0) {
+        const unsigned int t = atomicAdd(ep.ws_counters + tile_id, 1u);
+        const bool last = (t == (unsigned)nsplit - 1);
+        if (last) ep.ws_counters[tile_id] = 0;                 // ready for the next launch
+        __threadfence();
+        red[8] = last ? 1.f : 0.f;
+      }
+      ptx::bar_sync_epi();
+      run_epilogue = red[8] != 0.f;
+      if (run_epilogue) {
+        float4 acc[PER];
+#pragma unroll
+        for (int i = 0; i < PER; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int z = 0; z < nsplit; ++z) {
+          float4 v[PER];
+#pragma unroll
+          for (int i = 0; i < PER; ++i) {
+            const int f = et + i * kTcEpiThreads;
+            v[i] = (f < F4) ? __ldcg(ws + (size_t)z * F4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+#pragma unroll
+          for (int i = 0; i < PER; ++i) { acc[i].x += v[i].x; acc[i].y += v[i].y; acc[i].z += v[i].z; acc[i].w += v[i].w; }
+        }
+#pragma unroll
+        for (int i = 0; i < PER; ++i) {
+          const int f = et + i * kTcEpiThreads;
+          if (f < F4) *reinterpret_cast<float4*>(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4) = acc[i];
+        }
+        ptx::bar_sync_epi();
+      }
+    }
+    if (run_epilogue) tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red);
     if (et == 0) TC_STAMP(7);
   }
 
@@ -849,14 +903,15 @@ inline long long* tc05_dbg_buffer() {
 }
 
 template <int BN, bool kSplit, int kEpi>
-inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int N, int K, const Tc05Epi& ep, cudaStream_t s) {
+inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int N, int K, const Tc05Epi& ep, cudaStream_t s,
+                         int nsplit) {
   using S = Tc05Smem<BN, kSplit>;
   static bool attr = false;
   if (!attr) {
     MDT_CUDA(cudaFuncSetAttribute(tc05_gemm_kernel<BN, kSplit, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, S::TOTAL));
     attr = true;
   }
-  dim3 grid((N + BN - 1) / BN, (M + kTcBM - 1) / kTcBM);
+  dim3 grid((N + BN - 1) / BN, (M + kTcBM - 1) / kTcBM, nsplit);
   Tc05Epi epd = ep;
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
@@ -865,12 +920,29 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   return MDT_OK;
 }
 
+// Number of K-splits for a GEMM: only when a workspace is given, at least 4 k-blocks (128 K-values) per split, and
+// no more CTAs than SMs (one wave).
+inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc05Epi& ep, size_t ws_floats) {
+  if (ep.ws == nullptr || ep.ws_counters == nullptr) return 1;
+  const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
+  const int total_kb = (K + kTcBK - 1) / kTcBK;
+  int want = total_kb / 4;
+  const int cap = sm_count / tiles;
+  if (want > cap) want = cap;
+  if (want > 8) want = 8;
+  if (want < 2) return 1;
+  const int per = (total_kb + want - 1) / want;
+  const int ns = (total_kb + per - 1) / per;                 // every split gets at least one k-block
+  if ((size_t)tiles * ns * kTcBM * bn > ws_floats || tiles > 4096) return 1;
+  return ns;
+}
+
 template <int kEpi>
 inline int tc05_launch(int bn, bool split, const CUtensorMap& a, const CUtensorMap& b, int M, int N, int K, const Tc05Epi& ep,
-                       cudaStream_t s) {
-  if (bn == 16) return split ? tc05_launch_t<16, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<16, false, kEpi>(a, b, M, N, K, ep, s);
-  if (bn == 32) return split ? tc05_launch_t<32, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<32, false, kEpi>(a, b, M, N, K, ep, s);
-  if (bn == 64) return split ? tc05_launch_t<64, true, kEpi>(a, b, M, N, K, ep, s) : tc05_launch_t<64, false, kEpi>(a, b, M, N, K, ep, s);
+                       cudaStream_t s, int nsplit = 1) {
+  if (bn == 16) return split ? tc05_launch_t<16, true, kEpi>(a, b, M, N, K, ep, s, nsplit) : tc05_launch_t<16, false, kEpi>(a, b, M, N, K, ep, s, nsplit);
+  if (bn == 32) return split ? tc05_launch_t<32, true, kEpi>(a, b, M, N, K, ep, s, nsplit) : tc05_launch_t<32, false, kEpi>(a, b, M, N, K, ep, s, nsplit);
+  if (bn == 64) return split ? tc05_launch_t<64, true, kEpi>(a, b, M, N, K, ep, s, nsplit) : tc05_launch_t<64, false, kEpi>(a, b, M, N, K, ep, s, nsplit);
   return set_error(MDT_ERR_INVALID, "unsupported BLOCK_N %d", bn);
 }
 
@@ -901,8 +973,10 @@ struct Tc05Plan {
   int bn_h, bn_d;     // BLOCK_N used for N = H and N = D
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
   char* slab = nullptr;
-  float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials;
+  float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws;
   unsigned int* ticket;
+  unsigned int* ws_counters;
+  static constexpr size_t kWsFloats = 2u << 20;   // 8 MB split-K workspace
   CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights)
   std::map<int, Tc05ActMaps> maps;
   // weight-gradient GEMMs run on a side stream, off the dX critical path (fork/join by events; capturable)
@@ -949,7 +1023,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
                   {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
-                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}};
+                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 4096}};
   size_t bytes = 256;
   for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
   cudaError_t ce = cudaMalloc(&p->slab, bytes);
@@ -1005,6 +1079,14 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
   return MDT_OK;
 }
 
+// Split-K factor for a main-stream GEMM of the step (they run one after another, so they share the workspace).
+inline int tc05_splits(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
+  if (getenv("MDT_NO_SPLITK")) return 1;
+  e.ws = p->ws;
+  e.ws_counters = p->ws_counters;
+  return tc05_pick_splits(M, N, K, bn, p->b.sm_count, e, Tc05Plan::kWsFloats);
+}
+
 // Forward.  fuse_loss: fc4's epilogue also produces the loss, d(logits) and its transpose (training step);
 // otherwise fc4 stops at recon (mdt_forward / eval / decode) and the stand-alone loss kernel may follow.
 inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, const float* eps_in, bool decode_only,
@@ -1033,13 +1115,13 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     }
     Tc05Epi e1{};
     e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
-    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s));
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
     Tc05Epi e2{};
     e2.C = b.ml; e2.ldc = 2 * Z; e2.bias = P + b.L.off[B2X]; e2.eps_in = eps_in;
     e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
     e2.kl_partials = p->kl_partials;
-    MDT_TRY(tc05_launch<EPI_REPARAM>(64, sp, m->h1, p->mW2x, B, 2 * Z, H, e2, s));
+    MDT_TRY(tc05_launch<EPI_REPARAM>(64, sp, m->h1, p->mW2x, B, 2 * Z, H, e2, s, tc05_splits(p, e2, B, 2 * Z, H, 64)));
     TC_NOTE(p, "fc2x_reparam_fwd");
   }
   Tc05Epi e3{};
@@ -1051,12 +1133,12 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
     e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
     e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + kTcBM - 1) / kTcBM;
-    MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s));
+    MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_bce_fwd");
   } else {
     Tc05Epi e4{};
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.act = MDT_ACT_SIGMOID;
-    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s));
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_fwd");
   }
   return MDT_OK;
@@ -1100,7 +1182,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   TC_NOTE(p, "fc4_dW");
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
-  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s));
+  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
   MDT_TRY(fork_point());                          // da3^T ready (z^T since the forward)
   e = Tc05Epi{};
@@ -1109,7 +1191,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   TC_NOTE(p, "fc3_dW");
   e = Tc05Epi{};
   e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
-  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(32, sp, m->da3, p->mW3T, B, Z, H, e, s));
+  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(32, sp, m->da3, p->mW3T, B, Z, H, e, s, tc05_splits(p, e, B, Z, H, 32)));
   TC_NOTE(p, "fc3_dX_reparam_bwd");
   MDT_TRY(fork_point());                          // dml^T ready
   e = Tc05Epi{};
