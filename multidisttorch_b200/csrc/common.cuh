@@ -6,6 +6,7 @@
 
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 
@@ -83,6 +84,35 @@ struct StepState {
   unsigned int ticket_loss;
   unsigned int pad;
 };
+
+// ---------------------------------------------------------------- programmatic dependent launch
+// Kernels of a step are chained with PDL: a kernel may be scheduled while its predecessor in the stream is still
+// running, sets up (barriers, TMEM, descriptor prefetch) and then blocks in pdl_wait() until the predecessor has
+// completed and flushed its memory; pdl_trigger() lets the successor start its own set-up.  Both are no-ops for
+// launches without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+inline bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) on = getenv("MDT_NO_PDL") ? 0 : 1;
+  return on == 1;
+}
+
+template <class... KArgs, class... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, Args... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
 
 // ---------------------------------------------------------------- device helpers
 __device__ __forceinline__ float warp_sum(float v) {

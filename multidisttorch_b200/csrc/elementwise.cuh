@@ -289,6 +289,8 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
 
 __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
   __shared__ float sc[6];
+  pdl_wait();
+  pdl_trigger();
   if (a.st != nullptr) {
     if (threadIdx.x == 0) {
       const double bc1 = 1.0 - a.st->b1_pow * a.st->beta1;   // 1 - beta1^(t+1)

@@ -468,9 +468,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
         j += dr; r += dq;
         if (j >= Z) { j -= Z; r += 1; }
       }
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[13] = clock64();
       ptx::bar_sync_epi();
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[14] = clock64();
       for (int idx = et; idx < 2 * Z * kTcBM; idx += kTcEpiThreads) {
         const int c = idx / kTcBM, rr = idx - c * kTcBM;
         if (rr < R) ep.dmlT[(size_t)c * ep.ld_dmlT + m0 + rr] = T2[rr * (2 * Z + 1) + c];
@@ -500,9 +498,12 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int kb_per_split = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
   const int kb0 = (int)blockIdx.z * kb_per_split;
   const int num_kb = min(kb_per_split, total_kb - kb0);      // >= 1 (the host picks gridDim.z accordingly)
-  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0;
+  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == gridDim.z - 1;
 #define TC_STAMP(i) do { if (dbg) ep.dbg[i] = clock64(); } while (0)
-  if (threadIdx.x == 0) TC_STAMP(0);
+  if (threadIdx.x == 0) {
+    TC_STAMP(0);
+    if (dbg) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[14] = (long long)g; }
+  }
 
   const uint32_t bar_full = smem_base + S::BAR_OFF;           // [S::STAGES] TMA bytes landed
   const uint32_t bar_split = bar_full + 8 * S::STAGES;        // [S::STAGES] hi/lo split done (split mode)
@@ -538,7 +539,15 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above touched only shared memory, TMEM and kernel parameters: from here on the kernel reads what
+  // its predecessor wrote
+  pdl_wait();
+  pdl_trigger();
   if (threadIdx.x == 0) TC_STAMP(1);
+  if (ep.dbg != nullptr && threadIdx.x == 0) {   // grid-wide: earliest moment any CTA got past the dependency wait
+    unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+    atomicMin(reinterpret_cast<unsigned long long*>(ep.dbg + 13), g);
+  }
 
   if (warp == 0) {
     // ===== TMA producer =====
@@ -597,6 +606,31 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int q = warp & 3;                       // TMEM lane quadrant this warp may read
     const int chalf = (warp - 2) >> 2;            // which half of the accumulator columns this warp drains
     const int row = q * 32 + lane;                // accumulator row held by this thread
+    // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), done first: it overlaps the latency of the first TMA loads
+    if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
+      // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
+      constexpr int RW = kTcBM / (kTcEpiThreads / 32);      // rows per warp (16)
+      const int ew = et >> 5;
+      const float* const abase = ep.a_src + (size_t)(m0 + ew * RW) * ep.lda_src;
+      const size_t lda = ep.lda_src;
+      const int rows_here = min(RW, M - m0 - ew * RW);
+      float acc[RW];
+#pragma unroll
+      for (int i = 0; i < RW; ++i) acc[i] = 0.f;
+      for (int k = lane; k < K; k += 32) {                 // all RW loads of a k-slice are independent: in flight together
+        float t[RW];
+#pragma unroll
+        for (int i = 0; i < RW; ++i) t[i] = (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
+#pragma unroll
+        for (int i = 0; i < RW; ++i) acc[i] += t[i];
+      }
+#pragma unroll
+      for (int i = 0; i < RW; ++i) {
+        const float t = warp_sum(acc[i]);
+        if (lane == 0 && i < rows_here) ep.db[m0 + ew * RW + i] = t;
+      }
+    }
+
     constexpr int CH = BN / 2 < 16 ? 16 : BN / 2; // accumulator columns per warp (BN = 16: the second warp of a quadrant idles)
     const int colw = chalf * CH;                  // first column of this warp
     const bool drains = colw < BN;
@@ -646,31 +680,6 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
       drain(num_kb - 1);
     }
-    // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), overlaps the main loop
-    if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
-      // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
-      constexpr int RW = kTcBM / (kTcEpiThreads / 32);      // rows per warp (16)
-      const int ew = et >> 5;
-      const float* const abase = ep.a_src + (size_t)(m0 + ew * RW) * ep.lda_src;
-      const size_t lda = ep.lda_src;
-      const int rows_here = min(RW, M - m0 - ew * RW);
-      float acc[RW];
-#pragma unroll
-      for (int i = 0; i < RW; ++i) acc[i] = 0.f;
-      for (int k = lane; k < K; k += 32) {                 // all RW loads of a k-slice are independent: in flight together
-        float t[RW];
-#pragma unroll
-        for (int i = 0; i < RW; ++i) t[i] = (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
-#pragma unroll
-        for (int i = 0; i < RW; ++i) acc[i] += t[i];
-      }
-#pragma unroll
-      for (int i = 0; i < RW; ++i) {
-        const float t = warp_sum(acc[i]);
-        if (lane == 0 && i < rows_here) ep.db[m0 + ew * RW + i] = t;
-      }
-    }
-
     if (!kSplit) {
       ptx::mbar_wait(bar_accum, 0);
       ptx::tc_fence_after();
@@ -756,7 +765,13 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncwarp();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
-  if (threadIdx.x == 0) TC_STAMP(8);
+  if (threadIdx.x == 0) {
+    TC_STAMP(8);
+    if (ep.dbg != nullptr) {                     // grid-wide: the moment the last CTA left
+      unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g));
+      atomicMax(reinterpret_cast<unsigned long long*>(ep.dbg + 15), g);
+    }
+  }
 #undef TC_STAMP
 }
 
@@ -776,6 +791,8 @@ struct TrArgs {
 
 __global__ void __launch_bounds__(256) transpose_kernel(TrArgs a) {
   __shared__ float t[32][33];
+  pdl_wait();
+  pdl_trigger();
   int j = 0;
 #pragma unroll
   for (int q = 1; q < 4; ++q)
@@ -810,6 +827,8 @@ struct PrepArgs {
 };
 
 __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
+  pdl_wait();
+  pdl_trigger();
   if ((int)blockIdx.x < a.tr_blocks) {
     __shared__ float t[32][33];
     const TrJob job = a.tr.job[0];
@@ -915,8 +934,7 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   Tc05Epi epd = ep;
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
-  tc05_gemm_kernel<BN, kSplit, kEpi><<<grid, kTcThreads, S::TOTAL, s>>>(a, b, M, N, K, epd);
-  MDT_CUDA(cudaGetLastError());
+  MDT_CUDA(launch_pdl(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(kTcThreads), (size_t)S::TOTAL, s, a, b, M, N, K, epd));
   return MDT_OK;
 }
 
@@ -971,6 +989,7 @@ struct Tc05Plan {
   Tc05Buffers b;
   int ldB;            // leading dimension of every transposed activation (floats)
   int bn_h, bn_d;     // BLOCK_N used for N = H and N = D
+  int bn_dw;          // BLOCK_N of the weight-gradient GEMMs (wide tiles: fewer CTAs next to the dX GEMM they overlap)
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
   char* slab = nullptr;
   float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws;
@@ -994,7 +1013,7 @@ inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
   tr_add(a, blocks, b.params + b.L.off[W4], p->W4T, b.D, b.H, b.H, b.D);
   tr_add(a, blocks, b.params + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H);
   tr_add(a, blocks, b.params + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z);
-  transpose_kernel<<<blocks, 256, 0, s>>>(a);
+  MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
   TC_NOTE(p, "weights_T");
   return MDT_OK;
 }
@@ -1013,12 +1032,14 @@ inline void tc05_destroy(Tc05Plan* p) {
 inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) {
   const Tc05Buffers& b = *bufs;
   MDT_CHECK(2 * b.Z <= 64 && b.Z <= 32, "tcgen05 path supports latent <= 32 (got %d)", b.Z);
+  (void)tc05_dbg_buffer();          // allocate the optional phase-timing buffer outside any stream capture
   Tc05Plan* p = new Tc05Plan();
   p->b = b;
   p->ldB = (int)round_up(b.Bmax, 4);
   p->bn_h = b.H >= 2048 ? 64 : 32;
   p->bn_d = b.Bmax > 512 ? 64 : 32;
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
+  p->bn_dw = 64;
   const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
@@ -1069,10 +1090,10 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
     MDT_TRY(tc05_encode(&m.da3T, p->da3T, b.H, B, ldB, kTcBM));
     MDT_TRY(tc05_encode(&m.dmlT, p->dmlT, 2 * b.Z, B, ldB, kTcBM));
     MDT_TRY(tc05_encode(&m.da1T, p->da1T, b.H, B, ldB, kTcBM));
-    MDT_TRY(tc05_encode(&m.h3T, p->h3T, b.H, B, ldB, p->bn_h));
+    MDT_TRY(tc05_encode(&m.h3T, p->h3T, b.H, B, ldB, p->bn_dw));
     MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32));
-    MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_h));
-    MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_d));
+    MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_dw));
+    MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_dw));
     it = p->maps.emplace(B, m).first;
   }
   *out = &it->second;
@@ -1110,7 +1131,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
         blocks += (int)((pa.n_eps + 255) / 256);
         eps_in = b.eps;
       }
-      prep_kernel<<<blocks, 256, 0, s>>>(pa);
+      MDT_CUDA(launch_pdl(prep_kernel, dim3(blocks), dim3(256), 0, s, pa));
       TC_NOTE(p, "prep_xT_eps");
     }
     Tc05Epi e1{};
@@ -1149,7 +1170,7 @@ inline int tc05_after_external_da4(Tc05Plan* p, cudaStream_t s, int B) {
   TrArgs a{};
   int blocks = 0;
   tr_add(a, blocks, p->b.da4, p->da4T, B, p->b.D, p->b.D, p->ldB);
-  transpose_kernel<<<blocks, 256, 0, s>>>(a);
+  MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
   TC_NOTE(p, "da4_T");
   return MDT_OK;
 }
@@ -1178,7 +1199,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // da4^T, h3^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_h, sp, m->da4T, m->h3T, D, H, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw));
   TC_NOTE(p, "fc4_dW");
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
@@ -1196,7 +1217,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // dml^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_h, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw));
   TC_NOTE(p, "fc2x_dW");
   e = Tc05Epi{};
   e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
@@ -1205,7 +1226,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // da1^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_d, sp, m->da1T, m->xT, H, D, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, sw));
   TC_NOTE(p, "fc1_dW");
   if (fork) {                                     // join: the gradient buffer is complete once `sw` drains
     MDT_CUDA(cudaEventRecord(p->ev_join, sw));

@@ -256,7 +256,7 @@ int enqueue_backward_fp32(mdt_engine* e, const float* x, int B) {
 int enqueue_adam(mdt_engine* e, float grad_scale) {
   AdamArgs a{};
   a.p = e->params; a.g = e->grads; a.m = e->m; a.v = e->v; a.n = e->L.total; a.st = e->st; a.grad_scale = grad_scale;
-  adam_flat_kernel<<<adam_grid(a.n, e->dev->sm_count), kAdamThreads, 0, e->stream>>>(a);
+  MDT_CUDA(launch_pdl(adam_flat_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a));
   MDT_TRY(note_launch(e, "adam_flat"));
   if (e->tc) MDT_TRY(tc05_params_changed(e->tc, e->stream));   // refresh the transposed weight shadows
   return MDT_OK;
@@ -798,6 +798,10 @@ int mdt_debug_tc05_stamps(long long* out512, int reset_index) {
   MDT_CUDA(cudaDeviceSynchronize());
   MDT_CUDA(cudaMemcpy(out512, buf, 512 * sizeof(long long), cudaMemcpyDeviceToHost));
   if (reset_index) tc05_dbg_launch_index() = 0;
+  // re-arm: zeros everywhere, +inf in the atomicMin slot (13) of every launch slot
+  static long long init[512];
+  for (int i = 0; i < 512; ++i) init[i] = (i % 16 == 13) ? 0x7fffffffffffffffLL : 0;
+  MDT_CUDA(cudaMemcpy(buf, init, sizeof(init), cudaMemcpyHostToDevice));
   return MDT_OK;
 }
 

@@ -11,7 +11,7 @@ labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dW", "fc4_dX", "
 out = (C.c_longlong * 512)()
 for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
     H = int(os.environ.get("H", "400")); B = int(os.environ.get("B", "128"))
-    eng = E.VAEEngine(hidden=H, max_batch=B, gemm_mode=mode, use_graph=False)
+    eng = E.VAEEngine(hidden=H, max_batch=B, gemm_mode=mode, use_graph=os.environ.get("GRAPH", "0") == "1")
     eng.load_segments(O.init_params(1, O.Dims(H=H)))
     x = torch.rand(B, 784, device="cuda")
     for _ in range(3):
@@ -23,6 +23,8 @@ for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
     for i, lab in enumerate(labels):
         st = list(out)[16 * i: 16 * i + 16]
         d = {n: st[j] - st[0] for j, n in enumerate(names)}
-        extra = [st[j] - st[0] for j in (11, 12, 13, 14) if st[j] > 0]
-        print(f"  {lab:16s}", " ".join(f"{n}={v}" for n, v in d.items() if n != "entry"), "extra", extra)
+        if i == 0:
+            t_first = st[13]
+        print(f"  {lab:16s} go +{(st[13] - t_first) / 1e3:6.1f} us  end +{(st[15] - t_first) / 1e3:6.1f} us  dur {(st[15] - st[13]) / 1e3:5.1f} us |",
+              " ".join(f"{n}={v}" for n, v in d.items() if n != "entry"))
     eng.close()
