@@ -80,7 +80,7 @@ class EngineModule(nn.Module):
         self.module = module
         self.dims = dims
         self.process_group = process_group
-        self.gemm_mode = os.environ.get("MDT_GEMM", "fp32")
+        self.gemm_mode = os.environ.get("MDT_GEMM", "tf32x3")
         self.engine = None
         self._gen = torch.cuda.default_generators[module.fc1.weight.device.index]
         self._expect_offset = None

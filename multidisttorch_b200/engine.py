@@ -41,7 +41,7 @@ def nccl_comm_ptr(group, device):
 
 
 class VAEEngine:
-    def __init__(self, in_dim=784, hidden=400, latent=20, max_batch=128, gemm_mode="fp32", use_graph=True,
+    def __init__(self, in_dim=784, hidden=400, latent=20, max_batch=128, gemm_mode="tf32x3", use_graph=True,
                  group=None, device=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
         if not torch.cuda.is_available():
             raise RuntimeError("multidisttorch_b200.VAEEngine needs a CUDA device; there is no CPU path")
