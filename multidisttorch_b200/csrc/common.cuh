@@ -79,6 +79,8 @@ struct StepState {
   long long adam_t;                  // completed Adam steps; advanced by the Adam kernel
   double lr, beta1, beta2, eps;
   double b1_pow, b2_pow;             // beta1^adam_t, beta2^adam_t (kept incrementally: no pow() in the kernel)
+  float next[6];                     // fp32 scalars of the NEXT Adam step (step_size, sqrt(bc2), 1-b1, b2, 1-b2, eps),
+  float pad2[2];                     // refreshed by the last block of every Adam launch and by mdt_engine_set_adam
   unsigned int ticket_reparam;       // "last block done" counters (self-resetting)
   unsigned int ticket_adam;
   unsigned int ticket_loss;

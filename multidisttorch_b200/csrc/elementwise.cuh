@@ -287,28 +287,27 @@ __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v,
   p = p - step_size * __fdiv_rn(m, denom);
 }
 
+// scalars of step t+1 from the state (beta powers are those of t completed steps)
+__host__ __device__ inline void adam_next_scalars(double lr, double beta1, double beta2, double eps, double b1_pow,
+                                                  double b2_pow, float* out) {
+  const double bc1 = 1.0 - b1_pow * beta1;   // 1 - beta1^(t+1)
+  const double bc2 = 1.0 - b2_pow * beta2;
+  out[0] = (float)(lr / bc1);
+  out[1] = (float)sqrt(bc2);
+  out[2] = (float)(1.0 - beta1);
+  out[3] = (float)beta2;
+  out[4] = (float)(1.0 - beta2);
+  out[5] = (float)eps;
+}
+
 __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
-  __shared__ float sc[6];
   pdl_wait();
   pdl_trigger();
-  if (a.st != nullptr) {
-    if (threadIdx.x == 0) {
-      const double bc1 = 1.0 - a.st->b1_pow * a.st->beta1;   // 1 - beta1^(t+1)
-      const double bc2 = 1.0 - a.st->b2_pow * a.st->beta2;
-      sc[0] = (float)(a.st->lr / bc1);
-      sc[1] = (float)sqrt(bc2);
-      sc[2] = (float)(1.0 - a.st->beta1);
-      sc[3] = (float)a.st->beta2;
-      sc[4] = (float)(1.0 - a.st->beta2);
-      sc[5] = (float)a.st->eps;
-    }
-    __syncthreads();
-  } else if (threadIdx.x == 0) {
-    sc[0] = a.step_size; sc[1] = a.bc2_sqrt; sc[2] = a.one_minus_b1;
-    sc[3] = a.b2; sc[4] = a.one_minus_b2; sc[5] = a.eps;
+  float step_size = a.step_size, bc2_sqrt = a.bc2_sqrt, omb1 = a.one_minus_b1, b2 = a.b2, omb2 = a.one_minus_b2, eps = a.eps;
+  if (a.st != nullptr) {     // six broadcast loads, issued together with the first p/g/m/v loads below
+    step_size = a.st->next[0]; bc2_sqrt = a.st->next[1]; omb1 = a.st->next[2];
+    b2 = a.st->next[3]; omb2 = a.st->next[4]; eps = a.st->next[5];
   }
-  __syncthreads();
-  const float step_size = sc[0], bc2_sqrt = sc[1], omb1 = sc[2], b2 = sc[3], omb2 = sc[4], eps = sc[5];
   const float gs = a.grad_scale;
 
   const long long n4 = a.n >> 2;
@@ -341,6 +340,7 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
         a.st->adam_t += 1;
         a.st->b1_pow *= a.st->beta1;
         a.st->b2_pow *= a.st->beta2;
+        adam_next_scalars(a.st->lr, a.st->beta1, a.st->beta2, a.st->eps, a.st->b1_pow, a.st->b2_pow, a.st->next);
         a.st->ticket_adam = 0;
         __threadfence();
       }

@@ -147,11 +147,11 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
 // ------------------------------------------------------------------------------------------------
 enum Tc05EpiKind {
   EPI_BIAS_ACT = 0,     // C = act(acc + bias[n]); optional transposed copy
-  EPI_REPARAM = 1,      // fc21|fc22 tile -> ml, eps, std, z, z^T, direct KLD gradients, KLD partial sum
+  EPI_REPARAM = 1,      // (fc21|fc22)^T tile -> ml, eps, std, z, z^T, direct KLD gradients, KLD partial sum
   EPI_SIGMOID_BCE = 2,  // fc4 tile -> recon, BCE partial, d(logits) and its transpose; last CTA writes the loss
   EPI_RELU_MASK = 3,    // dX tile masked by the forward activation; optional row-major and transposed stores
   EPI_GRADW = 4,        // weight-gradient tile + bias gradient (row sums of the A operand)
-  EPI_REPARAM_BWD = 5,  // dz tile -> d[mu|logvar] and its transpose
+  EPI_REPARAM_BWD = 5,  // dz^T tile -> d[mu|logvar] and its transpose
 };
 
 struct Tc05Epi {
@@ -193,7 +193,7 @@ struct Tc05Smem {
   static constexpr int TILE_LD = BN + 4;                // padded epilogue tile (16-byte rows), reuses the ring
   static constexpr int BAR_OFF = RING;
   static constexpr int TOTAL = RING + 256 + 1024;       // barriers/tmem slot/reduction scratch + alignment slack
-  static_assert(kTcBM * (TILE_LD + 65 + 128) * 4 <= RING, "epilogue tile + transposed-store scratch must fit in the ring");
+  static_assert((kTcBM * TILE_LD + BN * 128) * 4 <= RING, "epilogue tile + transposed-store scratch must fit in the ring");
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -356,122 +356,91 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       }
     }
   } else if (kEpi == EPI_REPARAM || kEpi == EPI_REPARAM_BWD) {
-    // 128 x Z block of (row, latent) pairs.  The global inputs of the block (contiguous row ranges of eps / std /
-    // dml_kl) are first streamed into shared memory with coalesced float4 loads, so the per-pair loop below has no
-    // global-load latency in it; its stores go straight to global memory (consecutive threads -> consecutive
-    // addresses) and into a small transposed-store scratch.
+    // These two GEMMs have a skinny output (2Z or Z features), so they run as the TRANSPOSED problem
+    // C^T[feature, sample] = W[feature, K] . X[sample, K]^T: the batch becomes the tiled N dimension and the work
+    // spreads over B/BN CTAs instead of one.  T[f][n] holds feature f of sample n0 + n.  The per-sample inputs of
+    // the tile (eps / std / dml_kl rows n0..n0+nb) are contiguous in global memory and are staged through shared
+    // memory with coalesced float4 loads, so the element loop has no global-load latency in it.
     const int Z = ep.Z;
-    const int R = min(kTcBM, M - m0);            // valid rows of this tile
-    float* const T2 = T + kTcBM * ldt;           // transposed-store scratch: [128][Z+1] or [128][2Z+1]
-    float* const S0 = T2 + kTcBM * 65;           // staged inputs
-    const int nz = R * Z;
+    const int nb = min(BN, N - n0);              // valid samples of this tile (N = batch)
+    const int ne = nb * Z;
+    float* const S0 = T + kTcBM * ldt;
     if (kEpi == EPI_REPARAM) {
-      float* const sE = S0;                      // eps block [R][Z]
-      float* const sB = S0 + kTcBM * 32;         // bias [2Z]
+      float* const sE = S0;                      // eps [nb][Z]
+      float* const sB = S0 + BN * 32;            // bias [2Z]
       {
-        const float4* src = reinterpret_cast<const float4*>(ep.eps_in + (size_t)m0 * Z);
+        const float4* src = reinterpret_cast<const float4*>(ep.eps_in + (size_t)n0 * Z);
         float4* dst = reinterpret_cast<float4*>(sE);
 #pragma unroll
-        for (int q = 0; q < kTcBM * 32 / 4 / kTcEpiThreads; ++q) {     // fixed trip count: all loads in flight
+        for (int q = 0; q < (BN * 32 / 4 + kTcEpiThreads - 1) / kTcEpiThreads; ++q) {
           const int i = et + q * kTcEpiThreads;
-          if (i < nz / 4) dst[i] = __ldg(src + i);
+          if (i < ne / 4) dst[i] = __ldg(src + i);
         }
         if (et < 2 * Z) sB[et] = __ldg(ep.bias + et);
       }
       ptx::bar_sync_epi();
       float kl = 0.f;
-      float* const ml = ep.C + (size_t)m0 * 2 * Z;
-      float* const kk = ep.dml_kl + (size_t)m0 * 2 * Z;
-      float* const zz = ep.z + (size_t)m0 * Z;
-      float* const sdo = ep.sd_out + (size_t)m0 * Z;
-      float* const eo = (ep.eps_out != ep.eps_in) ? ep.eps_out + (size_t)m0 * Z : nullptr;
-      int r = et / Z, j = et - r * Z;
-      const int dq = kTcEpiThreads / Z, dr = kTcEpiThreads - dq * Z;
-#pragma unroll 2
-      for (int idx = et; idx < nz; idx += kTcEpiThreads) {
-        const float mu = T[r * ldt + j] + sB[j];
-        const float lv = T[r * ldt + Z + j] + sB[Z + j];
+      for (int idx = et; idx < ne; idx += kTcEpiThreads) {
+        const int n = idx / Z, j = idx - n * Z;
+        const size_t m = (size_t)(n0 + n);
+        const float mu = T[j * ldt + n] + sB[j];
+        const float lv = T[(Z + j) * ldt + n] + sB[Z + j];
         const float e = sE[idx];
         const float sd = __expf(0.5f * lv);
         const float ev = __expf(lv);
         const float zv = mu + e * sd;
-        ml[r * 2 * Z + j] = mu;
-        ml[r * 2 * Z + Z + j] = lv;
-        zz[idx] = zv;
-        if (eo) eo[idx] = e;
-        sdo[idx] = sd;
-        kk[r * 2 * Z + j] = mu;
-        kk[r * 2 * Z + Z + j] = 0.5f * (ev - 1.0f);
-        T2[r * (Z + 1) + j] = zv;
+        ep.C[m * 2 * Z + j] = mu;
+        ep.C[m * 2 * Z + Z + j] = lv;
+        ep.z[m * Z + j] = zv;
+        ep.zT[(size_t)j * ep.ldzT + m] = zv;
+        if (ep.eps_out != ep.eps_in) ep.eps_out[m * Z + j] = e;
+        ep.sd_out[m * Z + j] = sd;
+        ep.dml_kl[m * 2 * Z + j] = mu;
+        ep.dml_kl[m * 2 * Z + Z + j] = 0.5f * (ev - 1.0f);
         kl += -0.5f * (1.0f + lv - mu * mu - ev);
-        j += dr; r += dq;
-        if (j >= Z) { j -= Z; r += 1; }
       }
       kl = warp_sum(kl);
       if (lane == 0) red[ew] = kl;
       ptx::bar_sync_epi();
-      // z^T: row j of the transposed matrix holds R consecutive floats
-      for (int idx = et; idx < Z * kTcBM; idx += kTcEpiThreads) {
-        const int jj = idx / kTcBM, rr = idx - jj * kTcBM;
-        if (rr < R) ep.zT[(size_t)jj * ep.ldzT + m0 + rr] = T2[rr * (Z + 1) + jj];
-      }
       if (et == 0)
-        ep.kl_partials[blockIdx.y] = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
+        ep.kl_partials[blockIdx.x] = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
     } else {
-      float* const sE = S0;                      // eps block
-      float* const sS = S0 + kTcBM * 32;         // std block
-      float* const sK = S0 + kTcBM * 64;         // dml_kl block [R][2Z]
+      float* const sE = S0;                      // eps [nb][Z]
+      float* const sS = S0 + BN * 32;            // std [nb][Z]
+      float* const sK = S0 + BN * 64;            // dml_kl [nb][2Z]
       {
-        const float4* s0 = reinterpret_cast<const float4*>(ep.eps + (size_t)m0 * Z);
-        const float4* s1 = reinterpret_cast<const float4*>(ep.sd + (size_t)m0 * Z);
-        const float4* s2 = reinterpret_cast<const float4*>(ep.dml_kl + (size_t)m0 * 2 * Z);
+        const float4* s0 = reinterpret_cast<const float4*>(ep.eps + (size_t)n0 * Z);
+        const float4* s1 = reinterpret_cast<const float4*>(ep.sd + (size_t)n0 * Z);
+        const float4* s2 = reinterpret_cast<const float4*>(ep.dml_kl + (size_t)n0 * 2 * Z);
         float4* d0 = reinterpret_cast<float4*>(sE);
         float4* d1 = reinterpret_cast<float4*>(sS);
         float4* d2 = reinterpret_cast<float4*>(sK);
-        float4 t0[4], t1[4], t2[8];
+        constexpr int Q = (BN * 64 / 4 + kTcEpiThreads - 1) / kTcEpiThreads;
+        float4 t0[Q], t1[Q], t2[Q];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {                                   // fixed trip counts: all loads in flight
+        for (int q = 0; q < Q; ++q) {              // fixed trip count: every load is in flight before the first store
           const int i = et + q * kTcEpiThreads;
-          if (i < nz / 4) { t0[q] = __ldg(s0 + i); t1[q] = __ldg(s1 + i); }
+          if (i < ne / 4) { t0[q] = __ldg(s0 + i); t1[q] = __ldg(s1 + i); }
+          if (i < ne / 2) t2[q] = __ldg(s2 + i);
         }
 #pragma unroll
-        for (int q = 0; q < 8; ++q) {
+        for (int q = 0; q < Q; ++q) {
           const int i = et + q * kTcEpiThreads;
-          if (i < nz / 2) t2[q] = __ldg(s2 + i);
-        }
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const int i = et + q * kTcEpiThreads;
-          if (i < nz / 4) { d0[i] = t0[q]; d1[i] = t1[q]; }
-        }
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          const int i = et + q * kTcEpiThreads;
-          if (i < nz / 2) d2[i] = t2[q];
+          if (i < ne / 4) { d0[i] = t0[q]; d1[i] = t1[q]; }
+          if (i < ne / 2) d2[i] = t2[q];
         }
       }
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[11] = clock64();
       ptx::bar_sync_epi();
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[12] = clock64();
-      float* const dml = ep.dml + (size_t)m0 * 2 * Z;
-      int r = et / Z, j = et - r * Z;
-      const int dq = kTcEpiThreads / Z, dr = kTcEpiThreads - dq * Z;
-#pragma unroll 2
-      for (int idx = et; idx < nz; idx += kTcEpiThreads) {
-        const float g = T[r * ldt + j];
-        const float dmu = g + sK[r * 2 * Z + j];
-        const float dlv = g * sE[idx] * sS[idx] * 0.5f + sK[r * 2 * Z + Z + j];
-        dml[r * 2 * Z + j] = dmu;
-        dml[r * 2 * Z + Z + j] = dlv;
-        T2[r * (2 * Z + 1) + j] = dmu;
-        T2[r * (2 * Z + 1) + Z + j] = dlv;
-        j += dr; r += dq;
-        if (j >= Z) { j -= Z; r += 1; }
-      }
-      ptx::bar_sync_epi();
-      for (int idx = et; idx < 2 * Z * kTcBM; idx += kTcEpiThreads) {
-        const int c = idx / kTcBM, rr = idx - c * kTcBM;
-        if (rr < R) ep.dmlT[(size_t)c * ep.ld_dmlT + m0 + rr] = T2[rr * (2 * Z + 1) + c];
+      for (int idx = et; idx < ne; idx += kTcEpiThreads) {
+        const int n = idx / Z, j = idx - n * Z;
+        const size_t m = (size_t)(n0 + n);
+        const float g = T[j * ldt + n];
+        const float dmu = g + sK[n * 2 * Z + j];
+        const float dlv = g * sE[idx] * sS[idx] * 0.5f + sK[n * 2 * Z + Z + j];
+        ep.dml[m * 2 * Z + j] = dmu;
+        ep.dml[m * 2 * Z + Z + j] = dlv;
+        ep.dmlT[(size_t)j * ep.ld_dmlT + m] = dmu;
+        ep.dmlT[(size_t)(Z + j) * ep.ld_dmlT + m] = dlv;
       }
     }
   }
@@ -983,12 +952,14 @@ struct Tc05ActMaps {   // tensor maps whose extents depend on the batch size B
   CUtensorMap x, h1, z, h3, da4, da3, dml;             // A operands [B, *]
   CUtensorMap da4T, da3T, dmlT, da1T;                  // A operands [*, B]
   CUtensorMap h3T, zT, h1T, xT;                        // B operands [*, B]
+  CUtensorMap h1B, da3B;                               // B operands [B, *] of the transposed (skinny-output) GEMMs
 };
 
 struct Tc05Plan {
   Tc05Buffers b;
   int ldB;            // leading dimension of every transposed activation (floats)
   int bn_h, bn_d;     // BLOCK_N used for N = H and N = D
+  int bn_skinny;      // BLOCK_N (samples per tile) of the transposed fc21|fc22 and dz GEMMs
   int bn_dw;          // BLOCK_N of the weight-gradient GEMMs (wide tiles: fewer CTAs next to the dX GEMM they overlap)
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
   char* slab = nullptr;
@@ -996,7 +967,7 @@ struct Tc05Plan {
   unsigned int* ticket;
   unsigned int* ws_counters;
   static constexpr size_t kWsFloats = 2u << 20;   // 8 MB split-K workspace
-  CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights)
+  CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights); mW2x / mW3T are A operands (transposed problems)
   std::map<int, Tc05ActMaps> maps;
   // weight-gradient GEMMs run on a side stream, off the dX critical path (fork/join by events; capturable)
   cudaStream_t side = nullptr;
@@ -1031,7 +1002,7 @@ inline void tc05_destroy(Tc05Plan* p) {
 
 inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) {
   const Tc05Buffers& b = *bufs;
-  MDT_CHECK(2 * b.Z <= 64 && b.Z <= 32, "tcgen05 path supports latent <= 32 (got %d)", b.Z);
+  MDT_CHECK(b.Z <= 32, "tcgen05 path supports latent <= 32 (got %d)", b.Z);
   (void)tc05_dbg_buffer();          // allocate the optional phase-timing buffer outside any stream capture
   Tc05Plan* p = new Tc05Plan();
   p->b = b;
@@ -1040,6 +1011,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_d = b.Bmax > 512 ? 64 : 32;
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
   p->bn_dw = 64;
+  p->bn_skinny = b.Bmax > 1024 ? 64 : (b.Bmax > 256 ? 32 : 16);
   const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
@@ -1061,11 +1033,11 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   if (r == MDT_OK && cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
   const float* P = b.params;
   if (r == MDT_OK) r = tc05_encode(&p->mW1, P + b.L.off[W1], b.H, b.D, b.D, p->bn_h);
-  if (r == MDT_OK) r = tc05_encode(&p->mW2x, P + b.L.off[W2X], 2 * b.Z, b.H, b.H, 64);
+  if (r == MDT_OK) r = tc05_encode(&p->mW2x, P + b.L.off[W2X], 2 * b.Z, b.H, b.H, kTcBM);
   if (r == MDT_OK) r = tc05_encode(&p->mW3, P + b.L.off[W3], b.H, b.Z, b.Z, p->bn_h);
   if (r == MDT_OK) r = tc05_encode(&p->mW4, P + b.L.off[W4], b.D, b.H, b.H, p->bn_fc4);
   if (r == MDT_OK) r = tc05_encode(&p->mW4T, p->W4T, b.H, b.D, b.D, p->bn_h);
-  if (r == MDT_OK) r = tc05_encode(&p->mW3T, p->W3T, b.Z, b.H, b.H, 32);
+  if (r == MDT_OK) r = tc05_encode(&p->mW3T, p->W3T, b.Z, b.H, b.H, kTcBM);
   if (r == MDT_OK) r = tc05_encode(&p->mW2xT, p->W2xT, b.H, 2 * b.Z, 2 * b.Z, p->bn_h);
   if (r == MDT_OK) r = tc05_weight_shadows(p, s);
   if (r != MDT_OK) { tc05_destroy(p); return r; }
@@ -1094,6 +1066,8 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
     MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32));
     MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_dw));
     MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_dw));
+    MDT_TRY(tc05_encode(&m.h1B, b.h1, B, b.H, b.H, p->bn_skinny));
+    MDT_TRY(tc05_encode(&m.da3B, b.da3, B, b.H, b.H, p->bn_skinny));
     it = p->maps.emplace(B, m).first;
   }
   *out = &it->second;
@@ -1142,7 +1116,8 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e2.C = b.ml; e2.ldc = 2 * Z; e2.bias = P + b.L.off[B2X]; e2.eps_in = eps_in;
     e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
     e2.kl_partials = p->kl_partials;
-    MDT_TRY(tc05_launch<EPI_REPARAM>(64, sp, m->h1, p->mW2x, B, 2 * Z, H, e2, s, tc05_splits(p, e2, B, 2 * Z, H, 64)));
+    MDT_TRY(tc05_launch<EPI_REPARAM>(p->bn_skinny, sp, p->mW2x, m->h1B, 2 * Z, B, H, e2, s,
+                                      tc05_splits(p, e2, 2 * Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc2x_reparam_fwd");
   }
   Tc05Epi e3{};
@@ -1153,7 +1128,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     Tc05Epi e4{};
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
     e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
-    e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + kTcBM - 1) / kTcBM;
+    e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + p->bn_skinny - 1) / p->bn_skinny;
     MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_bce_fwd");
   } else {
@@ -1212,7 +1187,8 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   TC_NOTE(p, "fc3_dW");
   e = Tc05Epi{};
   e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
-  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(32, sp, m->da3, p->mW3T, B, Z, H, e, s, tc05_splits(p, e, B, Z, H, 32)));
+  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
+                                        tc05_splits(p, e, Z, B, H, p->bn_skinny)));
   TC_NOTE(p, "fc3_dX_reparam_bwd");
   MDT_TRY(fork_point());                          // dml^T ready
   e = Tc05Epi{};

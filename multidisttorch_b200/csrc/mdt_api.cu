@@ -476,9 +476,10 @@ int mdt_engine_broadcast_params(mdt_engine* e) {
 
 int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_steps) {
   MDT_CHECK(e && h, "NULL argument");
-  struct { long long t; double lr, b1, b2, eps, b1_pow, b2_pow; } host{
+  struct { long long t; double lr, b1, b2, eps, b1_pow, b2_pow; float next[6]; } host{
       completed_steps, h->lr, h->beta1, h->beta2, h->eps, pow(h->beta1, (double)completed_steps),
-      pow(h->beta2, (double)completed_steps)};
+      pow(h->beta2, (double)completed_steps), {0, 0, 0, 0, 0, 0}};
+  adam_next_scalars(host.lr, host.b1, host.b2, host.eps, host.b1_pow, host.b2_pow, host.next);
   MDT_CUDA(cudaMemcpyAsync(&e->st->adam_t, &host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
   MDT_CUDA(cudaStreamSynchronize(e->stream));  // `host` lives on this stack frame
   return MDT_OK;
