@@ -946,6 +946,7 @@ struct Tc05Buffers {
   void* note_ctx;
   int (*note)(void* ctx, const char* label);   // engine book-keeping after every kernel launch
   const bool* serial;                          // when *serial is true (per-kernel profiling) nothing is forked
+  int (*bucket_ready)(void* ctx, int bucket, cudaStream_t on);   // gradient bucket complete on stream `on` (or NULL)
 };
 
 struct Tc05ActMaps {   // tensor maps whose extents depend on the batch size B
@@ -1176,6 +1177,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw));
   TC_NOTE(p, "fc4_dW");
+  if (b.bucket_ready) MDT_TRY(b.bucket_ready(b.note_ctx, 0, sw));   // fc4.weight + fc4.bias gradients: DDP's first bucket
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));

@@ -112,6 +112,14 @@ struct mdt_engine {
 
   Tc05Plan* tc = nullptr;  // tcgen05 path state (tensor maps, transposed shadows); NULL in fp32 mode
 
+  // gradient all-reduce of a multi-rank trial group: its own stream, forked from / joined to the step by events so
+  // bucket 0 (fc4, ready first -- DDP's order) travels while the rest of backward still runs
+  cudaStream_t comm_stream = nullptr;
+  cudaEvent_t ev_bucket[2] = {nullptr, nullptr};
+  cudaEvent_t ev_comm_done = nullptr;
+  bool bucket0_sent = false;
+  bool defer_buckets = false;   // compat-mode backward: the caller all-reduces later (mdt_allreduce_grads)
+
   struct Graph { cudaGraphExec_t exec; long long kernels; };
   std::map<std::tuple<int, int, int>, Graph> graphs;
 
@@ -322,15 +330,50 @@ int stage_inputs(mdt_engine* e, const float** x, int B, const float** eps, cudaM
   return MDT_OK;
 }
 
+// The two DDP buckets are contiguous ranges of the flat gradient buffer: bucket 0 = [off(W4), total) (fc4.weight, fc4.bias:
+// first to be complete in backward), bucket 1 = [0, off(W4)).
+int allreduce_bucket(mdt_engine* e, int bucket, cudaStream_t on) {
+  const int64_t split = e->L.off[W4];
+  float* p = bucket == 0 ? e->grads + split : e->grads;
+  const size_t n = bucket == 0 ? (size_t)(e->L.total - split) : (size_t)split;
+  MDT_NCCL(g_nccl.AllReduce(p, p, n, ncclFloat, ncclSum, e->comm, on));
+  return MDT_OK;
+}
+
 int allreduce_grads(mdt_engine* e) {
   if (e->gsize <= 1) return MDT_OK;
   if (e->comm == nullptr)
     return set_error(MDT_ERR_STATE, "group_size %d but no NCCL communicator was given to mdt_engine_create", e->gsize);
   MDT_TRY(load_nccl());
-  // two buckets in DDP's order (fc4 first, then the rest): both are contiguous ranges of the flat buffer
-  const int64_t split = e->L.off[W4];
-  MDT_NCCL(g_nccl.AllReduce(e->grads + split, e->grads + split, (size_t)(e->L.total - split), ncclFloat, ncclSum, e->comm, e->stream));
-  MDT_NCCL(g_nccl.AllReduce(e->grads, e->grads, (size_t)split, ncclFloat, ncclSum, e->comm, e->stream));
+  MDT_TRY(allreduce_bucket(e, 0, e->stream));
+  return allreduce_bucket(e, 1, e->stream);
+}
+
+// Called by the backward pass as soon as the kernels that produce a bucket have been enqueued on stream `on`:
+// the all-reduce of that bucket goes to the communication stream behind an event.
+int bucket_ready_cb(void* ctx, int bucket, cudaStream_t on) {
+  mdt_engine* e = static_cast<mdt_engine*>(ctx);
+  if (e->gsize <= 1 || e->comm == nullptr || e->prof_on || e->defer_buckets) return MDT_OK;
+  MDT_TRY(load_nccl());
+  MDT_CUDA(cudaEventRecord(e->ev_bucket[bucket], on));
+  MDT_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_bucket[bucket], 0));
+  MDT_TRY(allreduce_bucket(e, bucket, e->comm_stream));
+  if (bucket == 0) e->bucket0_sent = true;
+  return MDT_OK;
+}
+
+// All-reduce whatever has not been sent yet and make the step's stream wait for the communication stream.
+int finish_allreduce(mdt_engine* e) {
+  if (e->gsize <= 1) return MDT_OK;
+  if (e->comm == nullptr)
+    return set_error(MDT_ERR_STATE, "group_size %d but no NCCL communicator was given to mdt_engine_create", e->gsize);
+  MDT_TRY(load_nccl());
+  if (e->prof_on) { e->bucket0_sent = false; return allreduce_grads(e); }
+  if (!e->bucket0_sent) MDT_TRY(bucket_ready_cb(e, 0, e->stream));
+  MDT_TRY(bucket_ready_cb(e, 1, e->stream));
+  e->bucket0_sent = false;
+  MDT_CUDA(cudaEventRecord(e->ev_comm_done, e->comm_stream));
+  MDT_CUDA(cudaStreamWaitEvent(e->stream, e->ev_comm_done, 0));
   return MDT_OK;
 }
 
@@ -355,9 +398,17 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
       return enqueue_adam(e, gscale);
     });
   }
-  MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
-  MDT_TRY(allreduce_grads(e));
-  return run_cached(e, /*kind=*/2, 0, 0, [&]() -> int { return enqueue_adam(e, gscale); });
+  if (getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0') {   // NCCL outside the graphs
+    MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
+    MDT_TRY(finish_allreduce(e));
+    return run_cached(e, /*kind=*/2, 0, 0, [&]() -> int { return enqueue_adam(e, gscale); });
+  }
+  // one graph for the whole step, the group's NCCL all-reduces included (bucket 0 overlaps the rest of backward)
+  return run_cached(e, /*kind=*/6, B, eps != nullptr, [&]() -> int {
+    MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
+    MDT_TRY(finish_allreduce(e));
+    return enqueue_adam(e, gscale);
+  });
 }
 
 }  // namespace
@@ -410,6 +461,13 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
     e->own_stream = true;
   }
   int r = carve_workspace(e);
+  if (r == MDT_OK && group_size > 1) {
+    if (cudaStreamCreateWithFlags(&e->comm_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_bucket[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_bucket[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&e->ev_comm_done, cudaEventDisableTiming) != cudaSuccess)
+      r = set_error(MDT_ERR_CUDA, "could not create the communication stream/events");
+  }
   if (r == MDT_OK) {
     cudaError_t ce = cudaMallocHost(&e->loss_pinned, 256);
     if (ce != cudaSuccess) r = set_error(MDT_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(ce));
@@ -428,6 +486,9 @@ void mdt_engine_destroy(mdt_engine* e) {
   cudaStreamSynchronize(e->stream);
   for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
   if (e->tc) tc05_destroy(e->tc);
+  if (e->comm_stream) { cudaStreamSynchronize(e->comm_stream); cudaStreamDestroy(e->comm_stream); }
+  for (auto& ev : e->ev_bucket) if (ev) cudaEventDestroy(ev);
+  if (e->ev_comm_done) cudaEventDestroy(e->ev_comm_done);
   if (e->slab) cudaFree(e->slab);
   if (e->loss_pinned) cudaFreeHost(e->loss_pinned);
   if (e->own_stream) cudaStreamDestroy(e->stream);
@@ -457,6 +518,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
     b.recon = e->recon; b.da4 = e->da4; b.da3 = e->da3; b.dz = e->dz; b.dml_kl = e->dml_kl; b.dml = e->dml; b.da1 = e->da1;
     b.st = e->st; b.sm_count = e->dev->sm_count; b.max_threads_sm = e->dev->max_threads_sm;
     b.loss_dev = e->loss_dev; b.note_ctx = e; b.note = note_cb; b.serial = &e->prof_on;
+    b.bucket_ready = (e->gsize > 1) ? bucket_ready_cb : nullptr;
     b.split3 = (e->cfg.gemm_mode == MDT_GEMM_TF32X3);
     MDT_TRY(tc05_create(&b, e->stream, &e->tc));
   }
@@ -537,12 +599,15 @@ int mdt_backward(mdt_engine* e, const float* d_recon, const float* d_mu, const f
   sigmoid_bwd_pack_kernel<<<blocks, 256, 0, e->stream>>>(d_recon, e->recon, n, e->da4, d_mu, d_logvar, B, e->Z, e->dml_kl);
   MDT_TRY(note_launch(e, "sigmoid_bwd"));
   if (e->tc) MDT_TRY(tc05_after_external_da4(e->tc, e->stream, B));
-  return run_cached(e, 4, B, 0, [&]() -> int { return enqueue_backward(e, e->x_stage, B); });
+  e->defer_buckets = true;
+  const int rc = run_cached(e, 4, B, 0, [&]() -> int { return enqueue_backward(e, e->x_stage, B); });
+  e->defer_buckets = false;
+  return rc;
 }
 
 int mdt_allreduce_grads(mdt_engine* e) {
   MDT_TRY(check_batch(e, 0));
-  return allreduce_grads(e);
+  return finish_allreduce(e);
 }
 
 int mdt_adam_step(mdt_engine* e, float grad_scale) {
