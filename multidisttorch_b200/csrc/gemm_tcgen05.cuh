@@ -586,12 +586,18 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       float acc[RW];
 #pragma unroll
       for (int i = 0; i < RW; ++i) acc[i] = 0.f;
-      for (int k = lane; k < K; k += 32) {                 // all RW loads of a k-slice are independent: in flight together
-        float t[RW];
+      const int K4 = K & ~3;                               // lda is a multiple of 4 floats: rows are 16-byte aligned
+      for (int k = 4 * lane; k < K4; k += 128) {           // RW independent 16-byte loads in flight per step
+        float4 t[RW];
 #pragma unroll
-        for (int i = 0; i < RW; ++i) t[i] = (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
+        for (int i = 0; i < RW; ++i)
+          t[i] = (i < rows_here) ? __ldg(reinterpret_cast<const float4*>(abase + i * lda + k)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-        for (int i = 0; i < RW; ++i) acc[i] += t[i];
+        for (int i = 0; i < RW; ++i) acc[i] += (t[i].x + t[i].y) + (t[i].z + t[i].w);
+      }
+      for (int k = K4 + lane; k < K; k += 32) {            // ragged batch tail
+#pragma unroll
+        for (int i = 0; i < RW; ++i) acc[i] += (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
       }
 #pragma unroll
       for (int i = 0; i < RW; ++i) {
@@ -964,7 +970,7 @@ struct Tc05Plan {
   int bn_dw;          // BLOCK_N of the weight-gradient GEMMs (wide tiles: fewer CTAs next to the dX GEMM they overlap)
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
   char* slab = nullptr;
-  float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws;
+  float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws, *ws_dw;
   unsigned int* ticket;
   unsigned int* ws_counters;
   static constexpr size_t kWsFloats = 2u << 20;   // 8 MB split-K workspace
@@ -1017,7 +1023,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
                   {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
-                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 4096}};
+                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 4096}};
   size_t bytes = 256;
   for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
   cudaError_t ce = cudaMalloc(&p->slab, bytes);
@@ -1081,6 +1087,18 @@ inline int tc05_splits(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
   e.ws = p->ws;
   e.ws_counters = p->ws_counters;
   return tc05_pick_splits(M, N, K, bn, p->b.sm_count, e, Tc05Plan::kWsFloats);
+}
+
+// Same for the weight-gradient GEMMs, which run on the side stream concurrently with the main-stream GEMMs and
+// therefore own a separate workspace and ticket range.
+inline int tc05_splits_dw(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
+  if (getenv("MDT_NO_SPLITK")) return 1;
+  e.ws = p->ws_dw;
+  e.ws_counters = p->ws_counters + 2048;
+  const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
+  if (tiles > 2048) return 1;
+  // the side stream shares the GPU with the dX GEMM it overlaps: aim for about half the SMs
+  return tc05_pick_splits(M, N, K, bn, p->b.sm_count / 2, e, Tc05Plan::kWsFloats);
 }
 
 // Forward.  fuse_loss: fc4's epilogue also produces the loss, d(logits) and its transpose (training step);
@@ -1175,7 +1193,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // da4^T, h3^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw, tc05_splits_dw(p, e, D, H, B, p->bn_dw)));
   TC_NOTE(p, "fc4_dW");
   if (b.bucket_ready) MDT_TRY(b.bucket_ready(b.note_ctx, 0, sw));   // fc4.weight + fc4.bias gradients: DDP's first bucket
   e = Tc05Epi{};
@@ -1185,7 +1203,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // da3^T ready (z^T since the forward)
   e = Tc05Epi{};
   e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
-  MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw, tc05_splits_dw(p, e, H, Z, B, 32)));
   TC_NOTE(p, "fc3_dW");
   e = Tc05Epi{};
   e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
@@ -1195,7 +1213,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // dml^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw, tc05_splits_dw(p, e, 2 * Z, H, B, p->bn_dw)));
   TC_NOTE(p, "fc2x_dW");
   e = Tc05Epi{};
   e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
@@ -1204,7 +1222,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(fork_point());                          // da1^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, sw));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, sw, tc05_splits_dw(p, e, H, D, B, p->bn_dw)));
   TC_NOTE(p, "fc1_dW");
   if (fork) {                                     // join: the gradient buffer is complete once `sw` drains
     MDT_CUDA(cudaEventRecord(p->ev_join, sw));
