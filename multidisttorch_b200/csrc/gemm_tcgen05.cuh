@@ -179,6 +179,8 @@ struct Tc05Epi {
 
 constexpr int kTcEpiThreads = 256;                 // warps 2-9: hi/lo split (TF32X3) + epilogue
 constexpr int kTcThreads = 64 + kTcEpiThreads;     // warp 0: TMA, warp 1: MMA + TMEM alloc
+constexpr int kTcDrainThreads = 128;               // TF32X3 only: warps 10-13 drain the per-k-block partial accumulators
+constexpr int tc_threads(bool split) { return split ? kTcThreads + kTcDrainThreads : kTcThreads; }
 constexpr int kTcBM = 128;
 constexpr int kTcBK = 32;        // fp32 elements = one 128-byte swizzle row
 
@@ -450,7 +452,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
 // the kernel
 // ------------------------------------------------------------------------------------------------
 template <int BN, bool kSplit, int kEpi>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(tc_threads(kSplit), 1)
 tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
                  int K, Tc05Epi ep) {
   using S = Tc05Smem<BN, kSplit>;
@@ -482,7 +484,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const uint32_t bar_aempty = bar_afull + 16;                 // [2] partial accumulator drained (TF32X3)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5));
   float* red = reinterpret_cast<float*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5) + 16);  // 8 floats (one per epilogue warp)
-  constexpr int kDrainWarps = BN >= 32 ? kTcEpiThreads / 32 : 4;   // warps that own accumulator columns
+  constexpr int kDrainWarps = kTcDrainThreads / 32;                 // TF32X3: one drain warp per TMEM lane quadrant
   constexpr int kTmemCols = kSplit ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
 
   if (threadIdx.x == 0) {
@@ -569,6 +571,35 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (!kSplit) ptx::mma_commit(bar_accum);
       TC_STAMP(4);
     }
+  } else if (kSplit && warp >= 2 + kTcEpiThreads / 32) {
+    // ===== TF32X3 drain warps: sum the per-k-block partial accumulators in fp32 registers =====
+    const int q = warp & 3;                       // TMEM lane quadrant of this warp
+    const int row = q * 32 + lane;
+    float pacc[BN];
+#pragma unroll
+    for (int i = 0; i < BN; ++i) pacc[i] = 0.f;
+    for (int j = 0; j < num_kb; ++j) {
+      const int ab = j & 1;
+      ptx::mbar_wait(bar_afull + 8 * ab, (j >> 1) & 1);
+      ptx::tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < BN / 16; ++c) {
+        float v[16];
+        ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + c * 16), v);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) pacc[c * 16 + i] += v[i];
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(bar_aempty + 8 * ab);
+    }
+    // every MMA has retired (the last afull fired), and it was issued only after all split warps finished their last
+    // stage: the ring is free -> park the tile where the epilogue warps expect it and release them
+    float* T = reinterpret_cast<float*>(smem);
+#pragma unroll
+    for (int c = 0; c < BN / 4; ++c)
+      *reinterpret_cast<float4*>(T + row * S::TILE_LD + 4 * c) = make_float4(pacc[4 * c], pacc[4 * c + 1], pacc[4 * c + 2], pacc[4 * c + 3]);
+    asm volatile("bar.sync 2, 384;" ::: "memory");
   } else {
     // ===== split (TF32X3) + epilogue warps =====
     const int et = threadIdx.x - 64;              // 0..255
@@ -609,31 +640,11 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     constexpr int CH = BN / 2 < 16 ? 16 : BN / 2; // accumulator columns per warp (BN = 16: the second warp of a quadrant idles)
     const int colw = chalf * CH;                  // first column of this warp
     const bool drains = colw < BN;
-    float pacc[kSplit ? CH : 1];                  // TF32X3: running fp32 sum of the per-k-block partial accumulators
     if (kSplit) {
-#pragma unroll
-      for (int i = 0; i < CH; ++i) pacc[i] = 0.f;
-      auto drain = [&](int j) {
-        if (!drains) return;
-        const int ab = j & 1;
-        ptx::mbar_wait(bar_afull + 8 * ab, (j >> 1) & 1);
-        ptx::tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < CH / 16; ++c) {
-          float v[16];
-          ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(ab * BN + colw + c * 16), v);
-#pragma unroll
-          for (int i = 0; i < 16; ++i) pacc[c * 16 + i] += v[i];
-        }
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(bar_aempty + 8 * ab);
-      };
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % S::STAGES;
         const uint32_t ph = (kb / S::STAGES) & 1;
         ptx::mbar_wait(bar_full + 8 * s, ph);
-        if (kb == 0 && et == 0) TC_STAMP(9);
         float4* hi = reinterpret_cast<float4*>(smem + s * S::STAGE);
         float4* lo = reinterpret_cast<float4*>(smem + s * S::STAGE + S::HB);
 #pragma unroll 4
@@ -646,14 +657,10 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           l.z = v.z - ptx::tf32_hi(v.z); l.w = v.w - ptx::tf32_hi(v.w);
           lo[c] = l;
         }
-        if (kb == 0 && et == 0) TC_STAMP(10);
         ptx::fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core's async proxy
-        if (kb == 0 && et == 0) TC_STAMP(11);
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(bar_split + 8 * s);
-        if (kb >= 1) drain(kb - 1);               // the MMAs of the previous k-block have had a whole split to finish
       }
-      drain(num_kb - 1);
     }
     if (!kSplit) {
       ptx::mbar_wait(bar_accum, 0);
@@ -663,24 +670,22 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // accumulator -> padded smem tile (the ring is free: every MMA has retired and, in TF32X3 mode, every warp has
     // passed its last split; the barrier below orders the tile writes against stragglers' lo-writes of the last stage)
     float* T = reinterpret_cast<float*>(smem);
-    if (kSplit) ptx::bar_sync_epi();
-    if (drains) {
+    if (kSplit) {
+      asm volatile("bar.sync 2, 384;" ::: "memory");   // the drain warps have parked the summed tile in T
+    } else {
+      if (drains) {
 #pragma unroll
-      for (int c = 0; c < CH / 16; ++c) {
-        float v[16];
-        const int col0 = colw + c * 16;
-        if (kSplit) {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] = pacc[c * 16 + i];
-        } else {
+        for (int c = 0; c < CH / 16; ++c) {
+          float v[16];
+          const int col0 = colw + c * 16;
           ptx::tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)col0, v);
-        }
-        float4* dst = reinterpret_cast<float4*>(T + row * S::TILE_LD + col0);
+          float4* dst = reinterpret_cast<float4*>(T + row * S::TILE_LD + col0);
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+          for (int j = 0; j < 4; ++j) dst[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+        }
       }
+      ptx::bar_sync_epi();
     }
-    ptx::bar_sync_epi();
     if (et == 0) TC_STAMP(6);
     bool run_epilogue = true;
     if (gridDim.z > 1) {
@@ -909,7 +914,7 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   Tc05Epi epd = ep;
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
-  MDT_CUDA(launch_pdl(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(kTcThreads), (size_t)S::TOTAL, s, a, b, M, N, K, epd));
+  MDT_CUDA(launch_pdl(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(tc_threads(kSplit)), (size_t)S::TOTAL, s, a, b, M, N, K, epd));
   return MDT_OK;
 }
 
