@@ -187,7 +187,7 @@ class ClockSampler:
 def run_own(args):
     import torch
     import torch.distributed as dist
-    from multidisttorch_b200.engine import VAEEngine
+    from multidisttorch_b200.engine import VAEEngine, train_step_many
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -310,6 +310,30 @@ def run_own(args):
             msm, _ = timed_run(em, min(K, 2000), W)
             modes[m] = round(world * B * min(K, 2000) / (msm * 1e-3), 1)
             em.close()
+    # ---- SURVEY section 8f-3 (next row): several independent trials per GPU, each its own engine, stream and CUDA graph,
+    #      stepped round-robin from this process; the kernels of different trials overlap on idle SMs
+    multi_trial = None
+    if world == 1 and not args.no_modes:
+        multi_trial = {"1": round(value, 1)}
+        for T in (2, 4, 8):
+            engs = []
+            for t in range(T):
+                et_ = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph)
+                et_.load_segments(O.init_params(2000 + t, dims))
+                et_.set_rng(2000 + t, 0)
+                engs.append(et_)
+            Km = min(K, 2000)
+            for i in range(W):
+                train_step_many(engs, [pool[(i * T + t) % POOL_BATCHES] for t in range(T)])
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(Km):
+                train_step_many(engs, [pool[(i * T + t) % POOL_BATCHES] for t in range(T)])
+            torch.cuda.synchronize()
+            dt = time.perf_counter() - t0
+            multi_trial[str(T)] = round(T * B * Km / dt, 1)
+            for e_ in engs:
+                e_.close()
     eng.close()
 
     # ---- other group layouts (gradient all-reduce inside each group)
@@ -346,7 +370,8 @@ def run_own(args):
                              "parameters and optimizer state are step-to-step resident by the nature of training",
                        "eps": "Philox in-kernel (torch-CUDA-compatible stream)"},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches), "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "layouts": layouts, "modes": modes, "kernels": kernels,
+            "cpu_baseline": cpu_baseline, "layouts": layouts, "modes": modes,
+            "trials_per_gpu": multi_trial, "kernels": kernels,
         }
         emit(out)
     if world > 1:

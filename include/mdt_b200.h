@@ -137,6 +137,13 @@ int mdt_adam_step(mdt_engine* e, float grad_scale);
  * `loss_out` (device, may be NULL) receives the summed loss of this rank's batch. */
 int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out);
 
+/* SURVEY section 8f-3 (several independent trials on one GPU): one step of each of `n_trials` engines, every engine on
+ * its own stream / CUDA graph so their kernels overlap on idle SMs.  xs[i] is trial i's device batch; eps comes from
+ * each engine's Philox state; losses stay in the engines (mdt_engine_workspace "loss").  Equivalent to calling
+ * mdt_train_step on each engine; it exists to take the per-call host overhead out of the HPO driver's loop.
+ * Replaces: nothing in the reference (it runs one trial per rank, ref:vae-hpo.py:200-202). */
+int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch);
+
 /* Same, with HOST buffers: copies x (and eps) host->device, runs the step, copies
  * the loss back and synchronises (the `loss.item()` of ref:vae-hpo.py:73).
  * Pinned host memory makes the copies asynchronous; pageable memory also works. */

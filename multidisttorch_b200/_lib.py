@@ -39,6 +39,7 @@ _PROTOS = {
     "mdt_allreduce_grads": (C.c_int, [_P]),
     "mdt_adam_step": (C.c_int, [_P, C.c_float]),
     "mdt_train_step": (C.c_int, [_P, _P, C.c_int, _P, _P]),
+    "mdt_train_step_many": (C.c_int, [C.POINTER(_P), C.POINTER(_P), C.c_int, C.c_int]),
     "mdt_train_step_host": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_float)]),
     "mdt_eval_step": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     "mdt_decode": (C.c_int, [_P, _P, C.c_int, _P]),

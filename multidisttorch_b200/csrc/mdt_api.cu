@@ -626,6 +626,12 @@ int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or
   return MDT_OK;
 }
 
+int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch) {
+  MDT_CHECK(engines && xs && n_trials >= 0, "bad argument");
+  for (int i = 0; i < n_trials; ++i) MDT_TRY(mdt_train_step(engines[i], xs[i], batch, nullptr, nullptr));
+  return MDT_OK;
+}
+
 int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
                         float* loss_host) {
   MDT_TRY(check_batch(e, batch));

@@ -251,6 +251,15 @@ def _cur_stream(dev):
     return C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
 
 
+def train_step_many(engines, xs):
+    """One step of several independent trials on one GPU in a single C-ABI call; xs[i] is the
+    [B, D] device batch of engines[i]."""
+    n = len(engines)
+    hs = (C.c_void_p * n)(*[e._h for e in engines])
+    ps = (C.c_void_p * n)(*[x.data_ptr() for x in xs])
+    check(_lib.load().mdt_train_step_many(hs, ps, n, xs[0].shape[0]))
+
+
 def adam_flat(p, g, m, v, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
     h = mdt_adam(lr, betas[0], betas[1], eps)
     check(_lib.load().mdt_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), C.byref(h), step, grad_scale,

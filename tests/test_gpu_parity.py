@@ -307,3 +307,27 @@ def test_hidden_4096_one_step_vs_oracle(E, mode):
     for k in O.SEGMENTS:
         assert rel_l2(got[k], g[k]) < tol["grad"], k
     eng.close()
+
+
+def test_many_trials_on_one_gpu_equal_sequential_trials(E):
+    """T independent trials stepped concurrently (own engine/stream/graph each) end bit-identical to the
+    same trials stepped one after another."""
+    B, T = 128, 3
+    xs = [dev(O.make_batch(50 + t, B)[0]) for t in range(T)]
+    seq, con = [], []
+    for t in range(T):
+        for group in (seq, con):
+            e = E.VAEEngine(max_batch=B)
+            e.load_segments(O.init_params(300 + t))
+            e.set_rng(300 + t, 0)
+            group.append(e)
+    for step in range(4):
+        for t in range(T):
+            seq[t].train_step(xs[(t + step) % T], None, want_loss=False)
+        E.train_step_many(con, [xs[(t + step) % T] for t in range(T)])
+    for t in range(T):
+        seq[t].synchronize(); con[t].synchronize()
+        assert torch.equal(seq[t].params, con[t].params)
+        assert con[t].state() == (4, 16)
+    for e in seq + con:
+        e.close()
