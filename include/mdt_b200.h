@@ -209,6 +209,13 @@ int mdt_loss_bce_kl_noalloc(const float* recon, const float* x, const float* mu,
                             int in_dim, int latent, float* loss_out, float* d_recon, float* d_mu, float* d_logvar,
                             void* stream);
 
+/* SURVEY section 8f-1 (device-resident data path): x_out[b, :] = images[indices[b], :] / 255 as fp32 -- the values
+ * datasets.MNIST + transforms.ToTensor() + the DataLoader collate hand to the step (ref:vae-hpo.py:135-150,67-68),
+ * gathered on the device (e.g. straight into mdt_engine_input_buffer) from a uint8 image table that stays in HBM.
+ * `indices` are device int64 sample indices (the DistributedSampler order); in_dim % 16 == 0. */
+int mdt_gather_u8(const uint8_t* images, int64_t n_images, const int64_t* indices, int batch, int in_dim, float* x_out,
+                  void* stream);
+
 /* y[M,N] = act(x[M,K] . W[N,K]^T + b[N]) : nn.Linear (+F.relu / torch.sigmoid),
  * ref:vae-hpo.py:30-31,39-40.  `gemm_mode` selects the kernel family. */
 int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode,

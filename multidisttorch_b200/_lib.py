@@ -50,6 +50,7 @@ _PROTOS = {
     "mdt_reparam": (C.c_int, [_P, _P, C.c_int, _P, C.c_uint64, C.c_uint64, C.c_int, C.c_int, _P, C.c_int, _P, _P]),
     "mdt_loss_bce_kl": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
     "mdt_loss_bce_kl_noalloc": (C.c_int, [_P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P, _P, _P, _P]),
+    "mdt_gather_u8": (C.c_int, [_P, C.c_int64, _P, C.c_int, C.c_int, _P, _P]),
     "mdt_linear": (C.c_int, [_P, _P, _P, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, _P, _P]),
     "mdt_allreduce_bench": (C.c_int, [_P, _P, C.c_size_t, C.c_int, _P, C.POINTER(C.c_double)]),
 }

@@ -348,6 +348,35 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
   }
 }
 
+// ============================================================================
+// Device-resident data path: x[b, :] = images_u8[idx[b], :] / 255   -- what
+// transforms.ToTensor() + the DataLoader collate produce on the host (ref:vae-hpo.py:135-150),
+// gathered straight into the step's stage buffer.  16 pixels per thread (one 16-byte load, four
+// float4 stores); IEEE division so the values are bit-identical to torch's uint8 -> float / 255.
+// ============================================================================
+__global__ void __launch_bounds__(256) gather_u8_kernel(const uint8_t* __restrict__ images, const long long* __restrict__ idx,
+                                                        int B, int D, long long n_images, float* __restrict__ x) {
+  const int chunks = D >> 4;                       // 16-byte chunks per row (D % 16 == 0)
+  const long long total = (long long)B * chunks;
+  for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < total; t += (long long)gridDim.x * blockDim.x) {
+    const int b = (int)(t / chunks), c = (int)(t - (long long)b * chunks);
+    long long src = idx[b];
+    if (src < 0 || src >= n_images) src = 0;       // never read out of bounds; the host validates indices
+    const uint4 raw = __ldg(reinterpret_cast<const uint4*>(images + src * D) + c);
+    const unsigned int w[4] = {raw.x, raw.y, raw.z, raw.w};
+    float4* out = reinterpret_cast<float4*>(x + (size_t)b * D + (size_t)c * 16);
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float4 v;
+      v.x = __fdiv_rn((float)(w[q] & 0xffu), 255.0f);
+      v.y = __fdiv_rn((float)((w[q] >> 8) & 0xffu), 255.0f);
+      v.z = __fdiv_rn((float)((w[q] >> 16) & 0xffu), 255.0f);
+      v.w = __fdiv_rn((float)(w[q] >> 24), 255.0f);
+      out[q] = v;
+    }
+  }
+}
+
 inline int adam_grid(long long n, int sm_count) {
   long long blocks = ((n >> 2) + kAdamThreads - 1) / kAdamThreads;
   const long long cap = (long long)sm_count * 8;

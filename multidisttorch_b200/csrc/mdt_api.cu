@@ -883,6 +883,24 @@ int mdt_debug_tc05_stamps(long long* out512, int reset_index) {
   return MDT_OK;
 }
 
+int mdt_gather_u8(const uint8_t* images, int64_t n_images, const int64_t* indices, int batch, int in_dim, float* x_out,
+                  void* stream) {
+  MDT_CHECK(images && indices && x_out, "NULL argument");
+  MDT_CHECK(batch >= 0 && in_dim > 0 && n_images > 0, "bad shape");
+  MDT_CHECK(in_dim % 16 == 0, "in_dim must be a multiple of 16 (16-byte pixel rows), got %d", in_dim);
+  MDT_CHECK(reinterpret_cast<uintptr_t>(images) % 16 == 0 && reinterpret_cast<uintptr_t>(x_out) % 16 == 0,
+            "images and x_out must be 16-byte aligned");
+  DeviceInfo* di = nullptr;
+  MDT_TRY(device_info(&di));
+  if (batch == 0) return MDT_OK;
+  long long blocks = ((long long)batch * (in_dim / 16) + 255) / 256;
+  if (blocks > di->sm_count * 8) blocks = di->sm_count * 8;
+  gather_u8_kernel<<<(int)blocks, 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(
+      images, reinterpret_cast<const long long*>(indices), batch, in_dim, (long long)n_images, x_out);
+  MDT_CUDA(cudaGetLastError());
+  return MDT_OK;
+}
+
 int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int K, int act, int gemm_mode, float* y,
                void* stream) {
   MDT_CHECK(x && w && y, "NULL argument");

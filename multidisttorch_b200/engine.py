@@ -173,6 +173,12 @@ class VAEEngine:
         check(self.lib.mdt_train_step(self._h, _ptr(x), x.shape[0], _ptr(eps), _ptr(self._loss) if want_loss else None))
         return self._loss if want_loss else None
 
+    def train_step_staged(self, batch, eps=None, want_loss=True):
+        """Step on a batch that is already in the engine's stage buffer (device-resident data path: no copy)."""
+        check(self.lib.mdt_train_step(self._h, C.c_void_p(self.input_buffer_ptr()), batch, _ptr(eps),
+                                      _ptr(self._loss) if want_loss else None))
+        return self._loss if want_loss else None
+
     def train_step_host(self, x_host, eps_host=None):
         """Same step with HOST tensors (pinned for async copies); returns float loss."""
         x = self._x2d(x_host)
