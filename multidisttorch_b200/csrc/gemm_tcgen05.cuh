@@ -342,18 +342,27 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     if (lane == 0) red[ew] = part;
     ptx::bar_sync_epi();
     tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
+    const int ncta = gridDim.x * gridDim.y;
     if (et == 0) {
-      const int ncta = gridDim.x * gridDim.y;
       ep.bce_partials[blockIdx.y * gridDim.x + blockIdx.x] =
           ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
       __threadfence();
-      if (atomicAdd(ep.ticket, 1u) == (unsigned)ncta - 1) {
-        __threadfence();
-        float tot = 0.f;
-        for (int i = 0; i < ncta; ++i) tot += __ldcg(ep.bce_partials + i);
-        float kl = 0.f;
-        for (int i = 0; i < ep.n_kl_partials; ++i) kl += __ldcg(ep.kl_partials + i);
-        *ep.loss_out = tot + kl;
+      red[8] = (atomicAdd(ep.ticket, 1u) == (unsigned)ncta - 1) ? 1.f : 0.f;
+    }
+    ptx::bar_sync_epi();
+    if (red[8] != 0.f) {
+      // last tile of the grid: all 256 threads fetch the per-tile partials at once (one L2 round trip instead of one
+      // per tile) and add them with a fixed-shape tree -> the loss is bit-reproducible run to run
+      __threadfence();
+      float t = 0.f;
+      for (int i = et; i < ncta; i += kTcEpiThreads) t += __ldcg(ep.bce_partials + i);
+      for (int i = et; i < ep.n_kl_partials; i += kTcEpiThreads) t += __ldcg(ep.kl_partials + i);
+      t = warp_sum(t);
+      ptx::bar_sync_epi();                        // red[] is reused below
+      if (lane == 0) red[ew] = t;
+      ptx::bar_sync_epi();
+      if (et == 0) {
+        *ep.loss_out = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
         *ep.ticket = 0;
       }
     }
@@ -928,6 +937,7 @@ inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc0
   const int cap = sm_count / tiles;
   if (want > cap) want = cap;
   if (want > 8) want = 8;
+  if (const char* v = getenv("MDT_MAX_SPLITS")) { const int c = atoi(v); if (want > c) want = c; }
   if (want < 2) return 1;
   const int per = (total_kb + want - 1) / want;
   const int ns = (total_kb + per - 1) / per;                 // every split gets at least one k-block
@@ -1023,6 +1033,9 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_d = b.Bmax > 512 ? 64 : 32;
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
   p->bn_dw = 64;
+  if (const char* v = getenv("MDT_BN_FC4")) p->bn_fc4 = atoi(v);          // tuning knobs (16 / 32 / 64)
+  if (const char* v = getenv("MDT_BN_H")) p->bn_h = atoi(v);
+  if (const char* v = getenv("MDT_BN_SKINNY")) p->bn_skinny = atoi(v);
   p->bn_skinny = b.Bmax > 1024 ? 64 : (b.Bmax > 256 ? 32 : 16);
   const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
   struct Item { float** ptr; size_t n; };
