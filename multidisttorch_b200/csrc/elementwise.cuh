@@ -277,6 +277,10 @@ struct AdamArgs {
   StepState* st;  // NULL -> host scalars below
   float step_size, bc2_sqrt, one_minus_b1, b2, one_minus_b2, eps;
   float grad_scale;
+  // optional: block 0 also adds the step's loss partials (written by earlier kernels of the step) in a fixed order
+  const float* loss_part_a; int n_part_a;
+  const float* loss_part_b; int n_part_b;
+  float* loss_out;
 };
 
 __device__ __forceinline__ void adam_elem(float& p, float g, float& m, float& v, float step_size, float bc2_sqrt,
@@ -309,6 +313,14 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
     b2 = a.st->next[3]; omb2 = a.st->next[4]; eps = a.st->next[5];
   }
   const float gs = a.grad_scale;
+  if (a.loss_out != nullptr && blockIdx.x == 0) {     // block-uniform branch
+    __shared__ float red[32];
+    float t = 0.f;
+    for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) t += __ldcg(a.loss_part_a + i);
+    for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) t += __ldcg(a.loss_part_b + i);
+    t = block_sum(t, red);
+    if (threadIdx.x == 0) *a.loss_out = t;
+  }
 
   const long long n4 = a.n >> 2;
   float4* p4 = reinterpret_cast<float4*>(a.p);

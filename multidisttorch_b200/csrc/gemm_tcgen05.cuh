@@ -239,9 +239,44 @@ __device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, f
   }
 }
 
+// Global inputs of the element-wise epilogues (bias, ReLU mask / BCE target) that do not depend on this kernel's own
+// result: fetched into registers right after the dependency wait, so their L2 latency hides behind the main loop
+// instead of sitting at the head of the epilogue.
+template <int BN>
+struct Tc05Pre {
+  static constexpr int ITERS = kTcBM / (kTcEpiThreads / (BN / 4));
+  float4 bias;
+  float4 aux[ITERS];
+};
+
+template <int BN, int kEpi>
+__device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0, int M, int N, int et, Tc05Pre<BN>& pre) {
+  constexpr int F4R = BN / 4;
+  constexpr int RPP = kTcEpiThreads / F4R;
+  constexpr int ITERS = kTcBM / RPP;
+  const int c4 = et % F4R, rbase = et / F4R;
+  const int n = n0 + 4 * c4;
+  const bool nvalid = n < N;
+  const int rows_valid = nvalid ? (M - m0 - rbase + RPP - 1) / RPP : 0;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+  pre.bias = zero4;
+  if ((kEpi == EPI_BIAS_ACT || kEpi == EPI_SIGMOID_BCE) && ep.bias != nullptr && nvalid)
+    pre.bias = __ldg(reinterpret_cast<const float4*>(ep.bias + n));
+  if (kEpi == EPI_RELU_MASK || kEpi == EPI_SIGMOID_BCE) {
+    const float* const src = (kEpi == EPI_RELU_MASK) ? ep.mask : ep.x;
+    const int ld = (kEpi == EPI_RELU_MASK) ? ep.ldmask : ep.ldx;
+    const float* const sp = src + (size_t)(m0 + rbase) * ld + n;
+    const size_t step = (size_t)RPP * ld;
+    const float fill = (kEpi == EPI_RELU_MASK) ? 0.f : 0.5f;
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i)
+      pre.aux[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(sp + i * step)) : make_float4(fill, fill, fill, fill);
+  }
+}
+
 template <int BN, int kEpi>
 __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int ldt, int m0, int n0, int M, int N, int et,
-                                              float* red) {
+                                              float* red, const Tc05Pre<BN>& pre) {
   const int lane = et & 31, ew = et >> 5;
   // Element-wise epilogues: 256 threads sweep the tile row by row in float4 units.  A thread always owns the same
   // four columns and rows rbase, rbase+RPP, ...; everything it needs (tile values from shared memory, mask / x
@@ -263,7 +298,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
     if (kEpi == EPI_BIAS_ACT) {
-      const float4 b = (ep.bias != nullptr && nvalid) ? __ldg(reinterpret_cast<const float4*>(ep.bias + n)) : zero4;
+      const float4 b = pre.bias;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) { v[i].x += b.x; v[i].y += b.y; v[i].z += b.z; v[i].w += b.w; }
       if (act == MDT_ACT_RELU) {
@@ -278,15 +313,11 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
         }
       }
     } else if (kEpi == EPI_RELU_MASK) {
-      const float* const mp = ep.mask + (size_t)(m0 + rbase) * ep.ldmask + n;
-      const size_t mstep = (size_t)RPP * ep.ldmask;
-      float4 mk[ITERS];
-#pragma unroll
-      for (int i = 0; i < ITERS; ++i) mk[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(mp + i * mstep)) : zero4;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) {
-        v[i].x = mk[i].x > 0.f ? v[i].x : 0.f; v[i].y = mk[i].y > 0.f ? v[i].y : 0.f;
-        v[i].z = mk[i].z > 0.f ? v[i].z : 0.f; v[i].w = mk[i].w > 0.f ? v[i].w : 0.f;
+        const float4 mk = pre.aux[i];
+        v[i].x = mk.x > 0.f ? v[i].x : 0.f; v[i].y = mk.y > 0.f ? v[i].y : 0.f;
+        v[i].z = mk.z > 0.f ? v[i].z : 0.f; v[i].w = mk.w > 0.f ? v[i].w : 0.f;
       }
     }
     if (Cp != nullptr) {
@@ -304,18 +335,14 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     }
   } else if (kEpi == EPI_SIGMOID_BCE) {
     const int ldc = ep.ldc;
-    const float4 b = nvalid ? __ldg(reinterpret_cast<const float4*>(ep.bias + n)) : zero4;
+    const float4 b = pre.bias;
     float4 v[ITERS], xv[ITERS];
-    {
-      const float* const xp = ep.x + (size_t)(m0 + rbase) * ep.ldx + n;
-      const size_t xstep = (size_t)RPP * ep.ldx;
 #pragma unroll
-      for (int i = 0; i < ITERS; ++i)
-        xv[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(xp + i * xstep)) : make_float4(.5f, .5f, .5f, .5f);
-    }
+    for (int i = 0; i < ITERS; ++i) xv[i] = pre.aux[i];
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
     float part = 0.f;
+    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[9] = clock64();
     float* const rp = ep.C + (size_t)(m0 + rbase) * ldc + n;       // recon
     float* const gp = ep.da4 + (size_t)(m0 + rbase) * ldc + n;     // dL/d(logits)
     const size_t cstep = (size_t)RPP * ldc;
@@ -336,36 +363,20 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       }
       v[i] = g;
     }
+    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[10] = clock64();
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
     part = warp_sum(part);
     if (lane == 0) red[ew] = part;
     ptx::bar_sync_epi();
+    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[11] = clock64();
     tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
-    const int ncta = gridDim.x * gridDim.y;
-    if (et == 0) {
+    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[12] = clock64();
+    // per-tile partial only: the loss itself is not needed by any later kernel of the step, so the fixed-order sum
+    // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here
+    if (et == 0)
       ep.bce_partials[blockIdx.y * gridDim.x + blockIdx.x] =
           ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
-      __threadfence();
-      red[8] = (atomicAdd(ep.ticket, 1u) == (unsigned)ncta - 1) ? 1.f : 0.f;
-    }
-    ptx::bar_sync_epi();
-    if (red[8] != 0.f) {
-      // last tile of the grid: all 256 threads fetch the per-tile partials at once (one L2 round trip instead of one
-      // per tile) and add them with a fixed-shape tree -> the loss is bit-reproducible run to run
-      __threadfence();
-      float t = 0.f;
-      for (int i = et; i < ncta; i += kTcEpiThreads) t += __ldcg(ep.bce_partials + i);
-      for (int i = et; i < ep.n_kl_partials; i += kTcEpiThreads) t += __ldcg(ep.kl_partials + i);
-      t = warp_sum(t);
-      ptx::bar_sync_epi();                        // red[] is reused below
-      if (lane == 0) red[ew] = t;
-      ptx::bar_sync_epi();
-      if (et == 0) {
-        *ep.loss_out = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
-        *ep.ticket = 0;
-      }
-    }
   } else if (kEpi == EPI_REPARAM || kEpi == EPI_REPARAM_BWD) {
     // These two GEMMs have a skinny output (2Z or Z features), so they run as the TRANSPOSED problem
     // C^T[feature, sample] = W[feature, K] . X[sample, K]^T: the batch becomes the tiled N dimension and the work
@@ -615,6 +626,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int q = warp & 3;                       // TMEM lane quadrant this warp may read
     const int chalf = (warp - 2) >> 2;            // which half of the accumulator columns this warp drains
     const int row = q * 32 + lane;                // accumulator row held by this thread
+    Tc05Pre<BN> pre;
+    tc05_prefetch<BN, kEpi>(ep, m0, n0, M, N, et, pre);
     // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), done first: it overlaps the latency of the first TMA loads
     if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
       // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
@@ -744,7 +757,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::bar_sync_epi();
       }
     }
-    if (run_epilogue) tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red);
+    if (run_epilogue) tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre);
     if (et == 0) TC_STAMP(7);
   }
 
@@ -1012,6 +1025,16 @@ inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
 }
 
 inline int tc05_params_changed(Tc05Plan* p, cudaStream_t s) { return tc05_weight_shadows(p, s); }
+
+// Where the fused training forward left the loss partials of a batch of B samples (BCE per fc4 tile, KLD per
+// reparameterisation tile); the Adam kernel adds them.
+inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* na, const float** b, int* nb) {
+  const int D = p->b.D;
+  *a = p->bce_partials;
+  *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM);
+  *b = p->kl_partials;
+  *nb = (B + p->bn_skinny - 1) / p->bn_skinny;
+}
 
 inline void tc05_destroy(Tc05Plan* p) {
   if (!p) return;

@@ -263,9 +263,13 @@ int enqueue_backward_fp32(mdt_engine* e, const float* x, int B) {
   return note_launch(e, "bias_grads");
 }
 
-int enqueue_adam(mdt_engine* e, float grad_scale) {
+int enqueue_adam(mdt_engine* e, float grad_scale, bool finalize_loss = false) {
   AdamArgs a{};
   a.p = e->params; a.g = e->grads; a.m = e->m; a.v = e->v; a.n = e->L.total; a.st = e->st; a.grad_scale = grad_scale;
+  if (finalize_loss && e->tc) {   // the fused forward of the tcgen05 path leaves per-tile loss partials
+    tc05_loss_partials(e->tc, e->last_B, &a.loss_part_a, &a.n_part_a, &a.loss_part_b, &a.n_part_b);
+    a.loss_out = e->loss_dev;
+  }
   MDT_CUDA(launch_pdl(adam_flat_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a));
   MDT_TRY(note_launch(e, "adam_flat"));
   if (e->tc) MDT_TRY(tc05_params_changed(e->tc, e->stream));   // refresh the transposed weight shadows
@@ -395,19 +399,19 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   if (e->gsize == 1) {
     return run_cached(e, /*kind=*/0, B, eps != nullptr, [&]() -> int {
       MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
-      return enqueue_adam(e, gscale);
+      return enqueue_adam(e, gscale, true);
     });
   }
   if (getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0') {   // NCCL outside the graphs
     MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
     MDT_TRY(finish_allreduce(e));
-    return run_cached(e, /*kind=*/2, 0, 0, [&]() -> int { return enqueue_adam(e, gscale); });
+    return run_cached(e, /*kind=*/2, B, 0, [&]() -> int { return enqueue_adam(e, gscale, true); });
   }
   // one graph for the whole step, the group's NCCL all-reduces included (bucket 0 overlaps the rest of backward)
   return run_cached(e, /*kind=*/6, B, eps != nullptr, [&]() -> int {
     MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
     MDT_TRY(finish_allreduce(e));
-    return enqueue_adam(e, gscale);
+    return enqueue_adam(e, gscale, true);
   });
 }
 
