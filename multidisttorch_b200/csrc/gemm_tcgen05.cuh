@@ -342,7 +342,6 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
     float part = 0.f;
-    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[9] = clock64();
     float* const rp = ep.C + (size_t)(m0 + rbase) * ldc + n;       // recon
     float* const gp = ep.da4 + (size_t)(m0 + rbase) * ldc + n;     // dL/d(logits)
     const size_t cstep = (size_t)RPP * ldc;
@@ -363,15 +362,12 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       }
       v[i] = g;
     }
-    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[10] = clock64();
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
     part = warp_sum(part);
     if (lane == 0) red[ew] = part;
     ptx::bar_sync_epi();
-    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[11] = clock64();
     tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
-    if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) ep.dbg[12] = clock64();
     // per-tile partial only: the loss itself is not needed by any later kernel of the step, so the fixed-order sum
     // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here
     if (et == 0)
@@ -682,6 +678,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::fence_proxy_async();                 // generic-proxy writes -> visible to the tensor core's async proxy
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(bar_split + 8 * s);
+        if (gridDim.z == 1 && kb < 4 && et == 0) TC_STAMP(9 + kb);
       }
     }
     if (!kSplit) {
@@ -736,18 +733,26 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::bar_sync_epi();
       run_epilogue = red[8] != 0.f;
       if (run_epilogue) {
+        if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
         float4 acc[PER];
 #pragma unroll
         for (int i = 0; i < PER; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-        for (int z = 0; z < nsplit; ++z) {
-          float4 v[PER];
+        constexpr int ZG = PER <= 2 ? 8 : (PER <= 4 ? 4 : 2);   // splits fetched together: their L2 latencies overlap
+        for (int z0 = 0; z0 < nsplit; z0 += ZG) {
+          float4 v[ZG][PER];
 #pragma unroll
-          for (int i = 0; i < PER; ++i) {
-            const int f = et + i * kTcEpiThreads;
-            v[i] = (f < F4) ? __ldcg(ws + (size_t)z * F4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
-          }
+          for (int zz = 0; zz < ZG; ++zz)
 #pragma unroll
-          for (int i = 0; i < PER; ++i) { acc[i].x += v[i].x; acc[i].y += v[i].y; acc[i].z += v[i].z; acc[i].w += v[i].w; }
+            for (int i = 0; i < PER; ++i) {
+              const int f = et + i * kTcEpiThreads;
+              v[zz][i] = (z0 + zz < nsplit && f < F4) ? __ldcg(ws + (size_t)(z0 + zz) * F4 + f) : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+          for (int zz = 0; zz < ZG; ++zz)        // still added strictly in split order: deterministic
+#pragma unroll
+            for (int i = 0; i < PER; ++i) {
+              acc[i].x += v[zz][i].x; acc[i].y += v[zz][i].y; acc[i].z += v[zz][i].z; acc[i].w += v[zz][i].w;
+            }
         }
 #pragma unroll
         for (int i = 0; i < PER; ++i) {
@@ -755,9 +760,13 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (f < F4) *reinterpret_cast<float4*>(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4) = acc[i];
         }
         ptx::bar_sync_epi();
+        if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
       }
     }
-    if (run_epilogue) tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre);
+    if (run_epilogue) {
+      tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre);
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[11] = (long long)g; }
+    }
     if (et == 0) TC_STAMP(7);
   }
 

@@ -26,5 +26,5 @@ for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
         if i == 0:
             t_first = st[13]
         print(f"  {lab:16s} go +{(st[13] - t_first) / 1e3:6.1f} us  end +{(st[15] - t_first) / 1e3:6.1f} us  dur {(st[15] - st[13]) / 1e3:5.1f} us |",
-              " ".join(f"{n}={v}" for n, v in d.items() if n != "entry"), "x", [st[j] - st[0] for j in (9, 10, 11, 12) if st[j] > 0])
+              " ".join(f"{n}={v}" for n, v in d.items() if n != "entry"), "| tile(0,0) last split: ticket +%.1f reduced +%.1f epilogue +%.1f us after go" % tuple((st[j] - st[13]) / 1e3 for j in (9, 10, 11)) if abs(st[9] - st[0]) > 10**8 else ("split done kb0..3: %s" % [st[j] - st[0] for j in (9, 10, 11, 12)]))
     eng.close()
