@@ -377,3 +377,24 @@ def test_batches_beyond_one_row_tile_vs_oracle(E, mode, B):
         lim = tol["param"] * ((50.0 if flipped else 1.0) if mode != "tf32" else 3.0)
         assert rel_l2(a, b) < lim, (k, rel_l2(a, b))
     eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("B", [1, 48, 130])
+def test_no_stray_writes_into_layout_padding(E, mode, B):
+    """compute-sanitizer is closed on this pool, so stray stores are hunted with canaries: the alignment gaps between
+    the flat-buffer segments must still be exactly zero after training steps with ragged batches (a tile epilogue that
+    ignored its row/column bounds would dirty them), and Adam must keep them zero in params and moments."""
+    eng = make_engine(E, mode, B)
+    lay, total = O.layout(O.Dims())
+    gap = np.ones(total, dtype=bool)
+    for off, n in lay.values():
+        gap[off:off + n] = False
+    assert gap.sum() > 0
+    for t in range(3):
+        x, _ = O.make_batch(batch_seed(t), B)
+        eng.train_step(dev(x), None)
+    eng.synchronize()
+    for name, buf in (("params", eng.params), ("grads", eng.grads), ("exp_avg", eng.exp_avg), ("exp_avg_sq", eng.exp_avg_sq)):
+        assert not buf.cpu().numpy()[gap].any(), name
+    eng.close()
