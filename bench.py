@@ -93,6 +93,11 @@ def algorithmic_bytes(label, B, H, total_params):
         "fc4_bce_fwd": B * H + D * H + D + 3 * B * D,
         "fc3_dX_reparam_bwd": B * H + H * Z + 2 * B * Z + 2 * B * 2 * Z,
         "weights_T": 2 * (D * H + H * Z + 2 * Z * H),
+        # weight gradient with the Adam update fused in: GEMM operands + gradient write + 3 reads/3 writes of p, m, v
+        "fc4_dW_adam": B * D + B * H + D * H + 6 * (D * H + D),
+        "fc3_dW_adam": B * H + B * Z + H * Z + 6 * (H * Z + H),
+        "fc2x_dW_adam": B * 2 * Z + B * H + 2 * Z * H + 6 * (2 * Z * H + 2 * Z),
+        "fc1_dW_adam": B * H + B * D + H * D + 6 * (H * D + H),
     }
     return t.get(label, 0) * f
 

@@ -171,6 +171,13 @@ struct Tc05Epi {
   const float* a_src; int lda_src; float* db;
   // reparameterisation (backward)
   const float *eps, *sd; float *dml, *dmlT; int ld_dmlT;
+  // weight-gradient GEMM with the Adam update fused in (single-rank trial groups): parameter / moment segments of
+  // this weight (same [M][ldc] layout as the gradient), its transposed shadow (or NULL), the bias segments, the
+  // device-resident step state and, for the CTA that takes the step's last ticket, the loss partials to add up
+  float *adam_p, *adam_m, *adam_v, *adam_pT; int adam_ldpT;
+  float *adam_pb, *adam_mb, *adam_vb;
+  StepState* adam_st; int adam_total_ctas;
+  const float* loss_part_a; int n_part_a; const float* loss_part_b; int n_part_b; float* adam_loss_out;
   // split-K workspace: [tile][split][128*BN] partial tiles + one ticket counter per tile
   float* ws; unsigned int* ws_counters;
   // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
@@ -217,6 +224,19 @@ __device__ __forceinline__ float fast_dlogit(float r, float x) {
   return p >= 1e-12f ? (r - x) : (r - x) * 1e12f * p;
 }
 
+// Adam element update for the fused weight-gradient epilogue.  Same formula as adam_elem (elementwise.cuh); the
+// square root and the quotient use the branch-free SFU forms (rsqrt / rcp approximations, <= 2 ulp) so that the 32
+// elements a thread owns form independent instruction chains the scheduler can interleave -- with the IEEE forms
+// (slow-path branches) the epilogue is a serial dependency chain on a handful of warps.
+__device__ __forceinline__ void adam_elem_fast(float& p, float g, float& m, float& v, float step_size, float inv_bc2_sqrt,
+                                               float omb1, float b2, float omb2, float eps) {
+  m = m + (g - m) * omb1;
+  v = v * b2 + omb2 * g * g;
+  const float sq = v > 0.f ? v * rsqrtf(v) : 0.f;
+  const float denom = sq * inv_bc2_sqrt + eps;
+  p = p - step_size * __fdividef(m, denom);
+}
+
 // Transposed store of the tile: thread = (tile row, column half); reads float4 from its row, writes four scalars,
 // each of which is coalesced across the warp (consecutive lanes = consecutive m).
 template <int BN>
@@ -247,6 +267,12 @@ struct Tc05Pre {
   static constexpr int ITERS = kTcBM / (kTcEpiThreads / (BN / 4));
   float4 bias;
   float4 aux[ITERS];
+  // fused Adam (EPI_GRADW): the step's scalars, and -- for narrow tiles, where they fit in registers -- this thread's
+  // slice of the weight and both moments, fetched before the main loop so the epilogue starts with them in hand
+  static constexpr bool kAdamRegs = ITERS <= 4;
+  float as[6];
+  float4 ap[kAdamRegs ? ITERS : 1], am[kAdamRegs ? ITERS : 1], av[kAdamRegs ? ITERS : 1];
+  bool adam_loaded;
 };
 
 template <int BN, int kEpi>
@@ -272,6 +298,25 @@ __device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0,
     for (int i = 0; i < ITERS; ++i)
       pre.aux[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(sp + i * step)) : make_float4(fill, fill, fill, fill);
   }
+  pre.adam_loaded = false;
+  if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
+    // Safe this early: the scalars change only after every CTA of the step's weight-gradient GEMMs has taken its
+    // ticket (kernel tail), and nobody else writes this tile of p / m / v.  Plain loads (the data is rewritten below).
+#pragma unroll
+    for (int k = 0; k < 6; ++k) pre.as[k] = ep.adam_st->next[k];
+    if (Tc05Pre<BN>::kAdamRegs && gridDim.z == 1) {
+      const size_t off0 = (size_t)(m0 + rbase) * ep.ldc + n, ostep = (size_t)RPP * ep.ldc;
+#pragma unroll
+      for (int i = 0; i < (Tc05Pre<BN>::kAdamRegs ? ITERS : 1); ++i) {
+        const bool ok = i < rows_valid;
+        const size_t o = off0 + (size_t)i * ostep;
+        pre.ap[i] = ok ? *reinterpret_cast<const float4*>(ep.adam_p + o) : zero4;
+        pre.am[i] = ok ? *reinterpret_cast<const float4*>(ep.adam_m + o) : zero4;
+        pre.av[i] = ok ? *reinterpret_cast<const float4*>(ep.adam_v + o) : zero4;
+      }
+      pre.adam_loaded = true;
+    }
+  }
 }
 
 template <int BN, int kEpi>
@@ -292,8 +337,8 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   if (kEpi == EPI_BIAS_ACT || kEpi == EPI_RELU_MASK || kEpi == EPI_GRADW) {
     float* const Cp = ep.C;
-    float* const CTp = (kEpi != EPI_GRADW) ? ep.CT : nullptr;
-    const int ldc = ep.ldc, ldct = ep.ldct, act = ep.act;
+    float* const CTp0 = (kEpi != EPI_GRADW) ? ep.CT : nullptr;
+    const int ldc = ep.ldc, act = ep.act;
     float4 v[ITERS];
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) v[i] = *reinterpret_cast<const float4*>(T + (rbase + i * RPP) * ldt + 4 * c4);
@@ -327,6 +372,49 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       for (int i = 0; i < ITERS; ++i)
         if (i < rows_valid) *reinterpret_cast<float4*>(cp + i * cstep) = v[i];
     }
+    float* CTp = CTp0;
+    if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
+      // fused Adam on this tile of the weight (adam_elem_fast: same formula as adam_flat_kernel, SFU sqrt/quotient)
+      const float step_size = pre.as[0], bc2_sqrt = __frcp_rn(pre.as[1]), omb1 = pre.as[2], b2 = pre.as[3], omb2 = pre.as[4],
+                  aeps = pre.as[5];
+      const size_t off0 = (size_t)(m0 + rbase) * ldc + n, ostep = (size_t)RPP * ldc;
+      constexpr int CHK = ITERS < 4 ? ITERS : 4;           // rows per batch of loads (register budget)
+#pragma unroll
+      for (int i0 = 0; i0 < ITERS; i0 += CHK) {
+        float4 pp[CHK], mm[CHK], vv[CHK];
+#pragma unroll
+        for (int c = 0; c < CHK; ++c) {
+          const bool ok = i0 + c < rows_valid;
+          const size_t o = off0 + (size_t)(i0 + c) * ostep;
+          if (Tc05Pre<BN>::kAdamRegs && pre.adam_loaded) {
+            pp[c] = pre.ap[Tc05Pre<BN>::kAdamRegs ? i0 + c : 0];
+            mm[c] = pre.am[Tc05Pre<BN>::kAdamRegs ? i0 + c : 0];
+            vv[c] = pre.av[Tc05Pre<BN>::kAdamRegs ? i0 + c : 0];
+          } else {
+            pp[c] = ok ? *reinterpret_cast<const float4*>(ep.adam_p + o) : zero4;
+            mm[c] = ok ? *reinterpret_cast<const float4*>(ep.adam_m + o) : zero4;
+            vv[c] = ok ? *reinterpret_cast<const float4*>(ep.adam_v + o) : zero4;
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < CHK; ++c) {
+          const float4 g = v[i0 + c];
+          adam_elem_fast(pp[c].x, g.x, mm[c].x, vv[c].x, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
+          adam_elem_fast(pp[c].y, g.y, mm[c].y, vv[c].y, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
+          adam_elem_fast(pp[c].z, g.z, mm[c].z, vv[c].z, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
+          adam_elem_fast(pp[c].w, g.w, mm[c].w, vv[c].w, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
+          if (i0 + c < rows_valid) {
+            const size_t o = off0 + (size_t)(i0 + c) * ostep;
+            *reinterpret_cast<float4*>(ep.adam_p + o) = pp[c];
+            *reinterpret_cast<float4*>(ep.adam_m + o) = mm[c];
+            *reinterpret_cast<float4*>(ep.adam_v + o) = vv[c];
+          }
+          v[i0 + c] = pp[c];                               // the updated weight feeds the transposed shadow below
+        }
+      }
+      CTp = ep.adam_pT;
+    }
+    const int ldct = (kEpi == EPI_GRADW) ? ep.adam_ldpT : ep.ldct;
     if (CTp != nullptr) {
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
@@ -648,10 +736,21 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int i = 0; i < RW; ++i) acc[i] += (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
       }
+      float mine = 0.f;                                   // lane i keeps the sum of row i
 #pragma unroll
       for (int i = 0; i < RW; ++i) {
         const float t = warp_sum(acc[i]);
-        if (lane == 0 && i < rows_here) ep.db[m0 + ew * RW + i] = t;
+        if (lane == i) mine = t;
+      }
+      if (lane < rows_here) {
+        const int m = m0 + ew * RW + lane;
+        ep.db[m] = mine;
+        if (ep.adam_pb != nullptr) {                        // fused Adam on the bias element
+          float pb = ep.adam_pb[m], mb = ep.adam_mb[m], vb = ep.adam_vb[m];
+          adam_elem_fast(pb, mine, mb, vb, ep.adam_st->next[0], __frcp_rn(ep.adam_st->next[1]), ep.adam_st->next[2],
+                         ep.adam_st->next[3], ep.adam_st->next[4], ep.adam_st->next[5]);
+          ep.adam_pb[m] = pb; ep.adam_mb[m] = mb; ep.adam_vb[m] = vb;
+        }
       }
     }
 
@@ -775,6 +874,36 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   if (warp == 1) {
     __syncwarp();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
+  }
+  if (kEpi == EPI_GRADW && ep.adam_total_ctas > 0) {
+    // Every CTA of the step's four weight-gradient GEMMs takes a ticket once it no longer needs the Adam scalars; the
+    // last one advances the device-resident optimizer state and adds up the step's loss partials (fixed order).
+    float* scr = reinterpret_cast<float*>(smem);
+    if (threadIdx.x == 0) {
+      __threadfence();
+      scr[64] = (atomicAdd(&ep.adam_st->ticket_adam, 1u) == (unsigned)ep.adam_total_ctas - 1) ? 1.f : 0.f;
+    }
+    __syncthreads();
+    if (scr[64] != 0.f) {
+      float t = 0.f;
+      for (int i = threadIdx.x; i < ep.n_part_a; i += blockDim.x) t += __ldcg(ep.loss_part_a + i);
+      for (int i = threadIdx.x; i < ep.n_part_b; i += blockDim.x) t += __ldcg(ep.loss_part_b + i);
+      t = warp_sum(t);
+      if (lane == 0) scr[warp] = t;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        float tot = 0.f;
+        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += scr[w];
+        if (ep.adam_loss_out != nullptr) *ep.adam_loss_out = tot;
+        StepState* st = ep.adam_st;
+        st->adam_t += 1;
+        st->b1_pow *= st->beta1;
+        st->b2_pow *= st->beta2;
+        adam_next_scalars(st->lr, st->beta1, st->beta2, st->eps, st->b1_pow, st->b2_pow, st->next);
+        st->ticket_adam = 0;
+        __threadfence();
+      }
+    }
   }
   if (threadIdx.x == 0) {
     TC_STAMP(8);
@@ -978,7 +1107,7 @@ inline int tc05_launch(int bn, bool split, const CUtensorMap& a, const CUtensorM
 
 // What the engine hands over: its flat buffers and activation workspaces (row-major, owned by the engine).
 struct Tc05Buffers {
-  float *params, *grads;
+  float *params, *grads, *exp_avg, *exp_avg_sq;
   Layout L;
   int D, H, Z, Bmax;
   float *x_stage, *h1, *ml, *eps, *sd, *z, *h3, *recon, *da4, *da3, *dz, *dml_kl, *dml, *da1;
@@ -997,6 +1126,7 @@ struct Tc05ActMaps {   // tensor maps whose extents depend on the batch size B
   CUtensorMap da4T, da3T, dmlT, da1T;                  // A operands [*, B]
   CUtensorMap h3T, zT, h1T, xT;                        // B operands [*, B]
   CUtensorMap h1B, da3B;                               // B operands [B, *] of the transposed (skinny-output) GEMMs
+  CUtensorMap h3Ta, h1Ta, xTa;                         // B operands [*, B] of the Adam-fused weight-gradient GEMMs (bn_dwa rows)
 };
 
 struct Tc05Plan {
@@ -1006,6 +1136,7 @@ struct Tc05Plan {
   int bn_skinny;      // BLOCK_N (samples per tile) of the transposed fc21|fc22 and dz GEMMs
   int bn_dw;          // BLOCK_N of the weight-gradient GEMMs (wide tiles: fewer CTAs next to the dX GEMM they overlap)
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
+  int bn_dwa;         // BLOCK_N of the Adam-fused weight-gradient GEMMs (narrow: the update's traffic is bound per SM)
   char* slab = nullptr;
   float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws, *ws_dw;
   unsigned int* ticket;
@@ -1014,9 +1145,9 @@ struct Tc05Plan {
   CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights); mW2x / mW3T are A operands (transposed problems)
   std::map<int, Tc05ActMaps> maps;
   // weight-gradient GEMMs run on a side stream, off the dX critical path (fork/join by events; capturable)
-  cudaStream_t side = nullptr;
+  cudaStream_t side = nullptr, side2 = nullptr, side3 = nullptr, side4 = nullptr;
   cudaEvent_t ev_fork[4] = {nullptr, nullptr, nullptr, nullptr};
-  cudaEvent_t ev_join = nullptr;
+  cudaEvent_t ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr, ev_join4 = nullptr;
 };
 
 #define TC_NOTE(p, label) MDT_TRY((p)->b.note((p)->b.note_ctx, label))
@@ -1048,6 +1179,8 @@ inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* n
 inline void tc05_destroy(Tc05Plan* p) {
   if (!p) return;
   if (p->side) cudaStreamDestroy(p->side);
+  for (cudaStream_t st : {p->side2, p->side3, p->side4}) if (st) cudaStreamDestroy(st);
+  for (cudaEvent_t ev : {p->ev_join2, p->ev_join3, p->ev_join4}) if (ev) cudaEventDestroy(ev);
   for (auto& ev : p->ev_fork) if (ev) cudaEventDestroy(ev);
   if (p->ev_join) cudaEventDestroy(p->ev_join);
   if (p->slab) cudaFree(p->slab);
@@ -1065,6 +1198,8 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_d = b.Bmax > 512 ? 64 : 32;
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
   p->bn_dw = 64;
+  p->bn_dwa = 32;
+  if (const char* v = getenv("MDT_BN_DWA")) p->bn_dwa = atoi(v);
   if (const char* v = getenv("MDT_BN_FC4")) p->bn_fc4 = atoi(v);          // tuning knobs (16 / 32 / 64)
   if (const char* v = getenv("MDT_BN_H")) p->bn_h = atoi(v);
   if (const char* v = getenv("MDT_BN_SKINNY")) p->bn_skinny = atoi(v);
@@ -1073,7 +1208,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
                   {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
-                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 4096}};
+                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, 2 * Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 8192}};
   size_t bytes = 256;
   for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
   cudaError_t ce = cudaMalloc(&p->slab, bytes);
@@ -1084,7 +1219,14 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   q += 256;
   for (auto& it : items) { *it.ptr = reinterpret_cast<float*>(q); q += (it.n * sizeof(float) + 255) / 256 * 256; }
   int r = MDT_OK;
-  if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "side stream");
+  if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&p->side2, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&p->side3, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&p->side4, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_join2, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_join3, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_join4, cudaEventDisableTiming) != cudaSuccess)
+    r = set_error(MDT_ERR_CUDA, "side streams");
   for (auto& ev : p->ev_fork)
     if (r == MDT_OK && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
   if (r == MDT_OK && cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
@@ -1123,6 +1265,9 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
     MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32));
     MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_dw));
     MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_dw));
+    MDT_TRY(tc05_encode(&m.h3Ta, p->h3T, b.H, B, ldB, p->bn_dwa));
+    MDT_TRY(tc05_encode(&m.h1Ta, p->h1T, b.H, B, ldB, p->bn_dwa));
+    MDT_TRY(tc05_encode(&m.xTa, p->xT, b.D, B, ldB, p->bn_dwa));
     MDT_TRY(tc05_encode(&m.h1B, b.h1, B, b.H, b.H, p->bn_skinny));
     MDT_TRY(tc05_encode(&m.da3B, b.da3, B, b.H, b.H, p->bn_skinny));
     it = p->maps.emplace(B, m).first;
@@ -1141,14 +1286,15 @@ inline int tc05_splits(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
 
 // Same for the weight-gradient GEMMs, which run on the side stream concurrently with the main-stream GEMMs and
 // therefore own a separate workspace and ticket range.
-inline int tc05_splits_dw(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
+inline int tc05_splits_dw(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn, int slot = 0) {
   if (getenv("MDT_NO_SPLITK")) return 1;
-  e.ws = p->ws_dw;
-  e.ws_counters = p->ws_counters + 2048;
+  // up to four weight-gradient GEMMs can be in flight at once (one side stream each): every slot owns 4 MB of workspace
+  e.ws = p->ws_dw + (size_t)slot * (Tc05Plan::kWsFloats / 2);
+  e.ws_counters = p->ws_counters + 2048 + slot * 1024;
   const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
-  if (tiles > 2048) return 1;
+  if (tiles > 1024) return 1;
   // the side stream shares the GPU with the dX GEMM it overlaps: aim for about half the SMs
-  return tc05_pick_splits(M, N, K, bn, p->b.sm_count / 2, e, Tc05Plan::kWsFloats);
+  return tc05_pick_splits(M, N, K, bn, p->b.sm_count / 2, e, Tc05Plan::kWsFloats / 2);
 }
 
 // Forward.  fuse_loss: fc4's epilogue also produces the loss, d(logits) and its transpose (training step);
@@ -1277,6 +1423,96 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   if (fork) {                                     // join: the gradient buffer is complete once `sw` drains
     MDT_CUDA(cudaEventRecord(p->ev_join, sw));
     MDT_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
+  }
+  return MDT_OK;
+}
+
+// Backward with the Adam update fused into the weight-gradient GEMMs (single-rank trial groups: nothing to
+// all-reduce).  Each dW_l GEMM updates W_l (and its transposed shadow) in its epilogue, so it may only start once the
+// dX GEMM that still reads the old W_l^T has finished:
+//   main  : fc4 dX --E1--> dz --E2--> fc2x dX --E3-->
+//   side  :          E1: fc4 dW
+//   side2 :                     E2: fc3 dW
+//   side3 :                                            E3: fc1 dW
+//   side4 :                                            E3: fc2x dW
+// (one stream each: an update is bound by the SM<->L2 bandwidth of the SMs its tiles run on, so the four should not
+// queue behind each other; narrow tiles -- bn_dwa -- spread each update over more SMs).  The CTA that takes the step's last ticket advances the optimizer state and sums the loss partials.
+inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
+  const Tc05Buffers& b = p->b;
+  const bool sp = b.split3;
+  const int D = b.D, H = b.H, Z = b.Z, ldB = p->ldB;
+  float* G = b.grads;
+  Tc05ActMaps* m = nullptr;
+  MDT_TRY(tc05_act_maps(p, B, &m));
+  const bool fork = !(b.serial && *b.serial);
+  cudaStream_t sa = fork ? p->side : s, sb = fork ? p->side2 : s, sc = fork ? p->side3 : s, sd = fork ? p->side4 : s;
+  const int bna = p->bn_dwa;
+  int nf = 0;
+  auto after_main = [&](cudaStream_t t1, cudaStream_t t2) -> int {   // later work on t1 (and t2) sees `s` so far
+    if (!fork) return MDT_OK;
+    MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
+    MDT_CUDA(cudaStreamWaitEvent(t1, p->ev_fork[nf], 0));
+    if (t2) MDT_CUDA(cudaStreamWaitEvent(t2, p->ev_fork[nf], 0));
+    ++nf;
+    return MDT_OK;
+  };
+  struct Dw { int seg_w, seg_b, M, N, bn, slot; const CUtensorMap *a, *bm; const float* a_src; float* pT; int ldpT; const char* label; int ns; };
+  Dw dw[4] = {
+      {W4, B4, D, H, bna, 0, &m->da4T, &m->h3Ta, p->da4T, p->W4T, D, "fc4_dW_adam", 1},
+      {W3, B3, H, Z, 32, 1, &m->da3T, &m->zT, p->da3T, p->W3T, H, "fc3_dW_adam", 1},
+      {W2X, B2X, 2 * Z, H, bna, 2, &m->dmlT, &m->h1Ta, p->dmlT, p->W2xT, 2 * Z, "fc2x_dW_adam", 1},
+      {W1, B1, H, D, bna, 3, &m->da1T, &m->xTa, p->da1T, nullptr, 0, "fc1_dW_adam", 1},
+  };
+  Tc05Epi ed[4];
+  int total_ctas = 0;
+  for (int i = 0; i < 4; ++i) {
+    Tc05Epi& e = ed[i];
+    e = Tc05Epi{};
+    const int64_t ow = b.L.off[dw[i].seg_w], ob = b.L.off[dw[i].seg_b];
+    e.C = G + ow; e.ldc = dw[i].N; e.a_src = dw[i].a_src; e.lda_src = ldB; e.db = G + ob;
+    e.adam_p = b.params + ow; e.adam_m = b.exp_avg + ow; e.adam_v = b.exp_avg_sq + ow;
+    e.adam_pT = dw[i].pT; e.adam_ldpT = dw[i].ldpT;
+    e.adam_pb = b.params + ob; e.adam_mb = b.exp_avg + ob; e.adam_vb = b.exp_avg_sq + ob;
+    e.adam_st = b.st;
+    dw[i].ns = tc05_splits_dw(p, e, dw[i].M, dw[i].N, B, dw[i].bn, dw[i].slot);
+    total_ctas += ((dw[i].N + dw[i].bn - 1) / dw[i].bn) * ((dw[i].M + kTcBM - 1) / kTcBM) * dw[i].ns;
+  }
+  for (int i = 0; i < 4; ++i) {
+    ed[i].adam_total_ctas = total_ctas;
+    tc05_loss_partials(p, B, &ed[i].loss_part_a, &ed[i].n_part_a, &ed[i].loss_part_b, &ed[i].n_part_b);
+    ed[i].adam_loss_out = b.loss_dev;
+  }
+  auto launch_dw = [&](int i, cudaStream_t st) -> int {
+    MDT_TRY(tc05_launch<EPI_GRADW>(dw[i].bn, sp, *dw[i].a, *dw[i].bm, dw[i].M, dw[i].N, B, ed[i], st, dw[i].ns));
+    return b.note(b.note_ctx, dw[i].label);
+  };
+  Tc05Epi e{};
+  e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
+  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
+  TC_NOTE(p, "fc4_dX");
+  MDT_TRY(after_main(sa, nullptr));               // E1: W4^T no longer needed, da3^T ready
+  MDT_TRY(launch_dw(0, sa));
+  e = Tc05Epi{};
+  e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
+                                        tc05_splits(p, e, Z, B, H, p->bn_skinny)));
+  TC_NOTE(p, "fc3_dX_reparam_bwd");
+  MDT_TRY(after_main(sb, nullptr));               // E2: W3^T no longer needed, dml^T ready
+  MDT_TRY(launch_dw(1, sb));
+  e = Tc05Epi{};
+  e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
+  TC_NOTE(p, "fc2x_dX");
+  MDT_TRY(after_main(sc, sd));                    // E3: W2x^T no longer needed, da1^T ready
+  MDT_TRY(launch_dw(3, sc));
+  MDT_TRY(launch_dw(2, sd));
+  if (fork) {
+    cudaStream_t st[4] = {sa, sb, sc, sd};
+    cudaEvent_t ev[4] = {p->ev_join, p->ev_join2, p->ev_join3, p->ev_join4};
+    for (int i = 0; i < 4; ++i) {
+      MDT_CUDA(cudaEventRecord(ev[i], st[i]));
+      MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+    }
   }
   return MDT_OK;
 }

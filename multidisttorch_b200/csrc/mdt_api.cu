@@ -396,6 +396,13 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   e->last_B = B;
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
+  if (e->gsize == 1 && e->tc && !getenv("MDT_NO_FUSED_ADAM")) {
+    // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
+    return run_cached(e, /*kind=*/7, B, eps != nullptr, [&]() -> int {
+      MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
+      return tc05_backward_fused_adam(e->tc, e->stream, B);
+    });
+  }
   if (e->gsize == 1) {
     return run_cached(e, /*kind=*/0, B, eps != nullptr, [&]() -> int {
       MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
@@ -517,7 +524,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
   if (e->cfg.gemm_mode != MDT_GEMM_FP32) {
     if (e->tc) { tc05_destroy(e->tc); e->tc = nullptr; }
     Tc05Buffers b{};
-    b.params = params; b.grads = grads; b.L = e->L; b.D = e->D; b.H = e->H; b.Z = e->Z; b.Bmax = e->Bmax;
+    b.params = params; b.grads = grads; b.exp_avg = exp_avg; b.exp_avg_sq = exp_avg_sq; b.L = e->L; b.D = e->D; b.H = e->H; b.Z = e->Z; b.Bmax = e->Bmax;
     b.x_stage = e->x_stage; b.h1 = e->h1; b.ml = e->ml; b.eps = e->eps; b.sd = e->sd; b.z = e->z; b.h3 = e->h3;
     b.recon = e->recon; b.da4 = e->da4; b.da3 = e->da3; b.dz = e->dz; b.dml_kl = e->dml_kl; b.dml = e->dml; b.da1 = e->da1;
     b.st = e->st; b.sm_count = e->dev->sm_count; b.max_threads_sm = e->dev->max_threads_sm;

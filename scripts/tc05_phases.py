@@ -7,7 +7,7 @@ from multidisttorch_b200 import engine as E, _lib
 from oracle import vae_numpy as O
 lib = _lib.load()
 names = ["entry", "setup", "tma_issued", "first_data", "mma_done", "accum_seen", "drained", "epi_done", "exit"]
-labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dW", "fc4_dX", "fc3_dW", "dz_reparam_bwd", "fc2x_dW", "fc2x_dX", "fc1_dW"]
+labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "dz_reparam_bwd", "fc3_dW", "fc2x_dX", "fc1_dW", "fc2x_dW"]
 out = (C.c_longlong * 512)()
 for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
     H = int(os.environ.get("H", "400")); B = int(os.environ.get("B", "128"))
