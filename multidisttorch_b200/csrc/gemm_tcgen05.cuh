@@ -959,6 +959,9 @@ __global__ void __launch_bounds__(256) transpose_kernel(TrArgs a) {
 struct PrepArgs {
   TrArgs tr;
   int tr_blocks;
+  float* x_copy;       // non-NULL: x lives in the caller's buffer; also copy it (row-major, ld = C) into the stage
+                       // buffer the later kernels read.  The engine re-points job[0].in / x_copy per launch of a
+                       // cached graph (kernel-node parameter update), so no separate staging copy is needed.
   float* eps_out;      // NULL: caller supplied eps, nothing to generate
   long long n_eps;
   StepState* st;
@@ -978,7 +981,10 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
 #pragma unroll
     for (int i = ty; i < 32; i += 8) {
       const int r = r0 + i, c = c0 + tx;
-      t[i][tx] = (r < job.R && c < job.C) ? job.in[(size_t)r * job.ld_in + c] : 0.f;
+      const bool ok = r < job.R && c < job.C;
+      const float v = ok ? job.in[(size_t)r * job.ld_in + c] : 0.f;
+      t[i][tx] = v;
+      if (ok && a.x_copy != nullptr) a.x_copy[(size_t)r * job.C + c] = v;
     }
     __syncthreads();
 #pragma unroll
@@ -1145,6 +1151,11 @@ struct Tc05Plan {
   CUtensorMap mW1, mW2x, mW3, mW4, mW4T, mW3T, mW2xT;  // B operands (weights); mW2x / mW3T are A operands (transposed problems)
   std::map<int, Tc05ActMaps> maps;
   // weight-gradient GEMMs run on a side stream, off the dX critical path (fork/join by events; capturable)
+  // Where the next forward's x lives (NULL: already in the stage buffer).  The prologue kernel reads it from there and
+  // fills the stage buffer itself; last_prep / prep_launched let the engine find and re-point that kernel in a graph.
+  const float* x_src = nullptr;
+  PrepArgs last_prep{};
+  bool prep_launched = false;
   cudaStream_t side = nullptr, side2 = nullptr, side3 = nullptr, side4 = nullptr;
   cudaEvent_t ev_fork[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr, ev_join4 = nullptr;
@@ -1312,8 +1323,10 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     {
       PrepArgs pa{};
       int blocks = 0;
-      tr_add(pa.tr, blocks, x, p->xT, B, D, D, p->ldB);
+      const float* src = (p->x_src != nullptr) ? p->x_src : x;
+      tr_add(pa.tr, blocks, src, p->xT, B, D, D, p->ldB);
       pa.tr_blocks = blocks;
+      pa.x_copy = (src != b.x_stage) ? b.x_stage : nullptr;
       if (eps_in == nullptr) {
         pa.eps_out = b.eps; pa.n_eps = (long long)B * Z; pa.st = b.st;
         torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
@@ -1321,6 +1334,8 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
         eps_in = b.eps;
       }
       MDT_CUDA(launch_pdl(prep_kernel, dim3(blocks), dim3(256), 0, s, pa));
+      p->last_prep = pa;
+      p->prep_launched = true;
       TC_NOTE(p, "prep_xT_eps");
     }
     Tc05Epi e1{};

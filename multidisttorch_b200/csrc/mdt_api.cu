@@ -120,7 +120,11 @@ struct mdt_engine {
   bool bucket0_sent = false;
   bool defer_buckets = false;   // compat-mode backward: the caller all-reduces later (mdt_allreduce_grads)
 
-  struct Graph { cudaGraphExec_t exec; long long kernels; };
+  struct Graph {
+    cudaGraphExec_t exec; long long kernels;
+    // tensor-core path: the graph's prologue kernel node, re-pointed at the caller's x before a launch
+    cudaGraph_t graph = nullptr; cudaGraphNode_t prep_node = nullptr; PrepArgs prep{}; dim3 prep_grid{};
+  };
   std::map<std::tuple<int, int, int>, Graph> graphs;
 
   long long launch_count = 0;  // kernels enqueued (a graph launch adds the kernels it holds)
@@ -301,6 +305,7 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
   if (it == e->graphs.end()) {
     cudaGraph_t g = nullptr;
     const long long before = e->launch_count;
+    if (e->tc) e->tc->prep_launched = false;
     MDT_CUDA(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeRelaxed));
     int r = fn();
     cudaError_t ce = cudaStreamEndCapture(e->stream, &g);
@@ -313,9 +318,41 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
     if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
     cudaGraphExec_t ex = nullptr;
     ce = cudaGraphInstantiate(&ex, g, 0);
-    cudaGraphDestroy(g);
-    if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce));
-    it = e->graphs.emplace(key, mdt_engine::Graph{ex, kernels}).first;
+    if (ce != cudaSuccess) { cudaGraphDestroy(g); return set_error(MDT_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce)); }
+    mdt_engine::Graph entry{ex, kernels};
+    if (e->tc && e->tc->prep_launched) {
+      // remember the prologue kernel's node: its x pointer is the one launch parameter that changes between steps
+      size_t nn = 0;
+      cudaGraphGetNodes(g, nullptr, &nn);
+      std::vector<cudaGraphNode_t> nodes(nn);
+      if (nn) cudaGraphGetNodes(g, nodes.data(), &nn);
+      for (size_t i = 0; i < nn; ++i) {
+        cudaGraphNodeType ty;
+        cudaKernelNodeParams kp{};
+        if (cudaGraphNodeGetType(nodes[i], &ty) != cudaSuccess || ty != cudaGraphNodeTypeKernel) continue;
+        if (cudaGraphKernelNodeGetParams(nodes[i], &kp) != cudaSuccess) continue;
+        if (kp.func == reinterpret_cast<void*>(prep_kernel)) {
+          entry.prep_node = nodes[i]; entry.prep = e->tc->last_prep; entry.prep_grid = kp.gridDim;
+          break;
+        }
+      }
+      cudaGetLastError();
+    }
+    if (entry.prep_node) entry.graph = g; else cudaGraphDestroy(g);   // node handles live as long as their graph
+    it = e->graphs.emplace(key, entry).first;
+  }
+  mdt_engine::Graph& G = it->second;
+  if (G.prep_node != nullptr && e->tc) {
+    const float* src = e->tc->x_src ? e->tc->x_src : e->x_stage;
+    if (src != G.prep.tr.job[0].in) {
+      G.prep.tr.job[0].in = src;
+      G.prep.x_copy = (src != e->x_stage) ? e->x_stage : nullptr;
+      void* args[1] = {&G.prep};
+      cudaKernelNodeParams kp{};
+      kp.func = reinterpret_cast<void*>(prep_kernel);
+      kp.gridDim = G.prep_grid; kp.blockDim = dim3(256); kp.sharedMemBytes = 0; kp.kernelParams = args; kp.extra = nullptr;
+      MDT_CUDA(cudaGraphExecKernelNodeSetParams(G.exec, G.prep_node, &kp));
+    }
   }
   MDT_CUDA(cudaGraphLaunch(it->second.exec, e->stream));
   e->launch_count += it->second.kernels;
@@ -495,7 +532,7 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
 void mdt_engine_destroy(mdt_engine* e) {
   if (!e) return;
   cudaStreamSynchronize(e->stream);
-  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
+  for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
   if (e->tc) tc05_destroy(e->tc);
   if (e->comm_stream) { cudaStreamSynchronize(e->comm_stream); cudaStreamDestroy(e->comm_stream); }
   for (auto& ev : e->ev_bucket) if (ev) cudaEventDestroy(ev);
@@ -519,7 +556,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
   for (const void* p : {(const void*)params, (const void*)grads, (const void*)exp_avg, (const void*)exp_avg_sq})
     MDT_CHECK(reinterpret_cast<uintptr_t>(p) % 128 == 0, "flat buffers must be 128-byte aligned");
   e->params = params; e->grads = grads; e->m = exp_avg; e->v = exp_avg_sq;
-  for (auto& kv : e->graphs) cudaGraphExecDestroy(kv.second.exec);
+  for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
   e->graphs.clear();
   if (e->cfg.gemm_mode != MDT_GEMM_FP32) {
     if (e->tc) { tc05_destroy(e->tc); e->tc = nullptr; }
@@ -630,9 +667,16 @@ int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or
   MDT_TRY(check_batch(e, batch));
   MDT_CHECK(x || batch == 0, "x is NULL");
   const float* eps = eps_or_null;
+  if (e->tc) {
+    // tensor-core path: the step's prologue kernel reads x where it lies and fills the stage buffer itself
+    e->tc->x_src = x;
+    x = e->x_stage;
+  }
   MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyDeviceToDevice));
   if (batch == 0) MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));
-  MDT_TRY(train_step_device(e, x, batch, eps));
+  const int rc_step = train_step_device(e, x, batch, eps);
+  if (e->tc) e->tc->x_src = nullptr;
+  MDT_TRY(rc_step);
   if (loss_out) MDT_CUDA(cudaMemcpyAsync(loss_out, e->loss_dev, sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
   return MDT_OK;
 }
