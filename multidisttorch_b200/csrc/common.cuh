@@ -84,8 +84,21 @@ struct StepState {
   unsigned int ticket_reparam;       // "last block done" counters (self-resetting)
   unsigned int ticket_adam;
   unsigned int ticket_loss;
-  unsigned int pad;
+  unsigned int host_seq;             // training steps published to host_mailbox so far
+  unsigned long long* host_mailbox;  // pinned, device-mapped host word: (host_seq << 32) | bits(loss) of the last step
 };
+
+// Called by the one thread that finalises a training step's loss: hands (sequence number, loss) to the host in a
+// single 8-byte store over PCIe, so mdt_train_step_host can poll for it instead of issuing a D2H copy + stream sync.
+__device__ __forceinline__ void publish_loss(StepState* st, float loss) {
+  unsigned long long* mb = st->host_mailbox;
+  if (mb == nullptr) return;
+  const unsigned int seq = st->host_seq + 1u;
+  st->host_seq = seq;
+  // one posted 8-byte store, nothing ordered behind it: no system-scope fence (it would hold the step's last CTA for
+  // a PCIe round trip)
+  *reinterpret_cast<volatile unsigned long long*>(mb) = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(loss);
+}
 
 // ---------------------------------------------------------------- programmatic dependent launch
 // Kernels of a step are chained with PDL: a kernel may be scheduled while its predecessor in the stream is still

@@ -319,7 +319,10 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
     for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) t += __ldcg(a.loss_part_a + i);
     for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) t += __ldcg(a.loss_part_b + i);
     t = block_sum(t, red);
-    if (threadIdx.x == 0) *a.loss_out = t;
+    if (threadIdx.x == 0) {
+      *a.loss_out = t;
+      if (a.st != nullptr) publish_loss(a.st, t);
+    }
   }
 
   const long long n4 = a.n >> 2;

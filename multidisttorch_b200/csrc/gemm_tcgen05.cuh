@@ -902,6 +902,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         adam_next_scalars(st->lr, st->beta1, st->beta2, st->eps, st->b1_pow, st->b2_pow, st->next);
         st->ticket_adam = 0;
         __threadfence();
+        publish_loss(st, tot);
       }
     }
   }

@@ -108,6 +108,8 @@ struct mdt_engine {
   unsigned int* loss_ticket;
   StepState* st;
   float* loss_pinned = nullptr;
+  volatile unsigned long long* mailbox = nullptr;   // loss_pinned + 64 bytes: see publish_loss()
+  unsigned int pub_expected = 0;                    // training steps enqueued so far that publish to the mailbox
   int last_B = 0;  // batch of the activations currently held
 
   Tc05Plan* tc = nullptr;  // tcgen05 path state (tensor maps, transposed shadows); NULL in fp32 mode
@@ -433,6 +435,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   e->last_B = B;
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
+  if (e->tc) ++e->pub_expected;   // every tensor-core training step publishes (sequence, loss) once: publish_loss()
   if (e->gsize == 1 && e->tc && !getenv("MDT_NO_FUSED_ADAM")) {
     // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
     return run_cached(e, /*kind=*/7, B, eps != nullptr, [&]() -> int {
@@ -519,6 +522,18 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   if (r == MDT_OK) {
     cudaError_t ce = cudaMallocHost(&e->loss_pinned, 256);
     if (ce != cudaSuccess) r = set_error(MDT_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(ce));
+  }
+  if (r == MDT_OK && e->cfg.gemm_mode != MDT_GEMM_FP32) {
+    memset(e->loss_pinned, 0, 256);
+    e->mailbox = reinterpret_cast<volatile unsigned long long*>(e->loss_pinned + 16);
+    void* dptr = nullptr;
+    if (cudaHostGetDevicePointer(&dptr, e->loss_pinned + 16, 0) == cudaSuccess && dptr != nullptr) {
+      unsigned long long* mb = static_cast<unsigned long long*>(dptr);
+      if (cudaMemcpy(&e->st->host_mailbox, &mb, sizeof(mb), cudaMemcpyHostToDevice) != cudaSuccess) e->mailbox = nullptr;
+    } else {
+      e->mailbox = nullptr;
+    }
+    cudaGetLastError();
   }
   if (r == MDT_OK) {
     mdt_adam h{1e-3, 0.9, 0.999, 1e-8};
@@ -693,6 +708,42 @@ int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const flo
   MDT_CHECK(x_host || batch == 0, "x_host is NULL");
   const float* x = x_host;
   const float* eps = eps_host_or_null;
+  if (e->tc && e->mailbox != nullptr && batch > 0 && !getenv("MDT_NO_ZEROCOPY")) {
+    // Tensor-core path.  Pinned x is read by the step's prologue kernel straight from host memory (no separate H2D
+    // copy in front of the graph), and the loss comes back through the mailbox the step's last thread writes.
+    cudaPointerAttributes at{};
+    const bool mapped = cudaPointerGetAttributes(&at, x_host) == cudaSuccess && at.type == cudaMemoryTypeHost &&
+                        at.devicePointer != nullptr;
+    cudaGetLastError();
+    if (mapped) {
+      e->tc->x_src = static_cast<const float*>(at.devicePointer);
+      x = e->x_stage;                      // stage_inputs then only handles eps
+    }
+    int rc = stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice);
+    if (rc == MDT_OK) rc = train_step_device(e, x, batch, eps);
+    e->tc->x_src = nullptr;
+    MDT_TRY(rc);
+    const unsigned int expected = e->pub_expected;
+    unsigned long long v = 0;
+    for (unsigned int spins = 0;; ++spins) {
+      v = *e->mailbox;
+      if ((unsigned int)(v >> 32) == expected) break;
+      if ((spins & 255u) == 255u) {
+        const cudaError_t q = cudaStreamQuery(e->stream);
+        if (q == cudaSuccess) {            // stream idle: whatever the mailbox holds now is this step's word
+          v = *e->mailbox;
+          e->pub_expected = (unsigned int)(v >> 32);
+          break;
+        }
+        if (q != cudaErrorNotReady) return set_error(MDT_ERR_CUDA, "training step failed: %s", cudaGetErrorString(q));
+      }
+    }
+    if (loss_host) {
+      const unsigned int bits = (unsigned int)(v & 0xffffffffull);
+      memcpy(loss_host, &bits, sizeof(float));
+    }
+    return MDT_OK;
+  }
   // host buffers never alias the stage, so both copies are issued (H2D, async when pinned)
   MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice));
   if (batch == 0) MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));

@@ -8,16 +8,17 @@ from multidisttorch_b200.engine import VAEEngine
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 128
 eng = VAEEngine(max_batch=B, gemm_mode="tf32x3")
 eng.set_rng(1234)
-pool = torch.rand(64, B, 784, device="cuda")
+NP = int(sys.argv[2]) if len(sys.argv) > 2 else 64
+pool = torch.rand(NP, B, 784, device="cuda")
 for i in range(50):
-    eng.train_step(pool[i % 64], want_loss=False)
+    eng.train_step(pool[i % NP], want_loss=False)
 eng.synchronize()
 for name in ("copy", "staged", "copy", "staged"):
     n = 4000
     eng.synchronize(); t0 = time.perf_counter()
     if name == "copy":
         for i in range(n):
-            eng.train_step(pool[i % 64], want_loss=False)
+            eng.train_step(pool[i % NP], want_loss=False)
     else:
         for i in range(n):
             eng.train_step_staged(B, want_loss=False)
