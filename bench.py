@@ -93,6 +93,9 @@ def algorithmic_bytes(label, B, H, total_params):
         "fc4_bce_fwd": B * H + D * H + D + 3 * B * D,
         "fc3_dX_reparam_bwd": B * H + H * Z + 2 * B * Z + 2 * B * 2 * Z,
         "weights_T": 2 * (D * H + H * Z + 2 * Z * H),
+        # fused CUDA-core latent kernels: fc21|fc22 + reparam + KL + fc3, and their backward
+        "latent_fwd": B * H + 2 * Z * H + 2 * Z + B * 2 * Z + 4 * B * Z + B * 2 * Z + H * Z + H + B * H,
+        "latent_bwd": B * H + H * Z + 2 * B * Z + 2 * B * 2 * Z + 2 * Z * H + 2 * B * H,
         # weight gradient with the Adam update fused in: GEMM operands + gradient write + 3 reads/3 writes of p, m, v
         "fc4_dW_adam": B * D + B * H + D * H + 6 * (D * H + D),
         "fc3_dW_adam": B * H + B * Z + H * Z + 6 * (H * Z + H),

@@ -22,6 +22,7 @@
 #include <map>
 
 #include "common.cuh"
+#include "latent.cuh"
 #include "elementwise.cuh"
 
 namespace mdt {
@@ -1143,6 +1144,7 @@ struct Tc05Plan {
   int bn_skinny;      // BLOCK_N (samples per tile) of the transposed fc21|fc22 and dz GEMMs
   int bn_dw;          // BLOCK_N of the weight-gradient GEMMs (wide tiles: fewer CTAs next to the dX GEMM they overlap)
   int bn_fc4;         // BLOCK_N of the fc4 forward GEMM (narrow tiles spread the BCE epilogue over more SMs)
+  bool simt_latent;   // the latent-side layers (fc21|fc22 + reparam + fc3, and their backward) run as fused CUDA-core kernels
   int bn_dwa;         // BLOCK_N of the Adam-fused weight-gradient GEMMs (narrow: the update's traffic is bound per SM)
   char* slab = nullptr;
   float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws, *ws_dw;
@@ -1185,7 +1187,7 @@ inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* n
   *a = p->bce_partials;
   *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM);
   *b = p->kl_partials;
-  *nb = (B + p->bn_skinny - 1) / p->bn_skinny;
+  *nb = p->simt_latent ? latent_grid(B, latent_pick_sc(B, p->b.sm_count)) : (B + p->bn_skinny - 1) / p->bn_skinny;
 }
 
 inline void tc05_destroy(Tc05Plan* p) {
@@ -1211,6 +1213,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
   p->bn_dw = 64;
   p->bn_dwa = 32;
+  p->simt_latent = getenv("MDT_TC_LATENT") == nullptr;   // MDT_TC_LATENT=1: keep them on the tensor cores (A/B comparisons)
   if (const char* v = getenv("MDT_BN_DWA")) p->bn_dwa = atoi(v);
   if (const char* v = getenv("MDT_BN_FC4")) p->bn_fc4 = atoi(v);          // tuning knobs (16 / 32 / 64)
   if (const char* v = getenv("MDT_BN_H")) p->bn_h = atoi(v);
@@ -1343,6 +1346,16 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
+    if (p->simt_latent) {
+      LatentFwdArgs la{};
+      la.h1 = b.h1; la.H = H; la.W2x = P + b.L.off[W2X]; la.b2x = P + b.L.off[B2X]; la.W3 = P + b.L.off[W3]; la.b3 = P + b.L.off[B3];
+      la.eps_in = eps_in; la.ml = b.ml; la.z = b.z; la.zT = p->zT; la.ldT = p->ldB; la.eps_out = b.eps; la.sd_out = b.sd;
+      la.dml_kl = b.dml_kl; la.kl_partials = p->kl_partials; la.h3 = b.h3; la.h3T = p->h3T; la.B = B; la.Z = Z;
+      la.dbg = tc05_dbg_buffer();
+      if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
+      MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, b.sm_count), s));
+      TC_NOTE(p, "latent_fwd");
+    } else {
     Tc05Epi e2{};
     e2.C = b.ml; e2.ldc = 2 * Z; e2.bias = P + b.L.off[B2X]; e2.eps_in = eps_in;
     e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
@@ -1350,11 +1363,14 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     MDT_TRY(tc05_launch<EPI_REPARAM>(p->bn_skinny, sp, p->mW2x, m->h1B, 2 * Z, B, H, e2, s,
                                       tc05_splits(p, e2, 2 * Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc2x_reparam_fwd");
+    }
   }
-  Tc05Epi e3{};
-  e3.C = b.h3; e3.ldc = H; e3.CT = p->h3T; e3.ldct = p->ldB; e3.bias = P + b.L.off[B3]; e3.act = MDT_ACT_RELU;
-  MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->z, p->mW3, B, H, Z, e3, s));
-  TC_NOTE(p, "fc3_fwd");
+  if (decode_only || !p->simt_latent) {
+    Tc05Epi e3{};
+    e3.C = b.h3; e3.ldc = H; e3.CT = p->h3T; e3.ldct = p->ldB; e3.bias = P + b.L.off[B3]; e3.act = MDT_ACT_RELU;
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->z, p->mW3, B, H, Z, e3, s));
+    TC_NOTE(p, "fc3_fwd");
+  }
   if (fuse_loss && !decode_only) {
     Tc05Epi e4{};
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
@@ -1378,6 +1394,20 @@ inline int tc05_after_external_da4(Tc05Plan* p, cudaStream_t s, int B) {
   tr_add(a, blocks, p->b.da4, p->da4T, B, p->b.D, p->b.D, p->ldB);
   MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
   TC_NOTE(p, "da4_T");
+  return MDT_OK;
+}
+
+// dz -> reparameterisation backward -> fc21|fc22 input gradient as one CUDA-core kernel (latent.cuh)
+inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
+  const Tc05Buffers& b = p->b;
+  LatentBwdArgs la{};
+  la.da3 = b.da3; la.H = b.H; la.W3T = p->W3T; la.W2xT = p->W2xT; la.h1 = b.h1;
+  la.eps = b.eps; la.sd = b.sd; la.dml_kl = b.dml_kl; la.dml = b.dml; la.dmlT = p->dmlT; la.ldT = p->ldB; la.da1T = p->da1T;
+  la.B = B; la.Z = b.Z;
+  la.dbg = tc05_dbg_buffer();
+  if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
+  MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, b.sm_count, /*backward=*/true), s));
+  TC_NOTE(p, "latent_bwd");
   return MDT_OK;
 }
 
@@ -1417,21 +1447,27 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
   MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw, tc05_splits_dw(p, e, H, Z, B, 32)));
   TC_NOTE(p, "fc3_dW");
-  e = Tc05Epi{};
-  e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
-  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
-                                        tc05_splits(p, e, Z, B, H, p->bn_skinny)));
-  TC_NOTE(p, "fc3_dX_reparam_bwd");
-  MDT_TRY(fork_point());                          // dml^T ready
+  if (p->simt_latent) {
+    MDT_TRY(tc05_latent_bwd(p, s, B));
+  } else {
+    e = Tc05Epi{};
+    e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+    MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
+                                          tc05_splits(p, e, Z, B, H, p->bn_skinny)));
+    TC_NOTE(p, "fc3_dX_reparam_bwd");
+  }
+  MDT_TRY(fork_point());                          // dml^T ready (latent_bwd: da1^T too)
   e = Tc05Epi{};
   e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw, tc05_splits_dw(p, e, 2 * Z, H, B, p->bn_dw)));
   TC_NOTE(p, "fc2x_dW");
-  e = Tc05Epi{};
-  e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
-  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
-  TC_NOTE(p, "fc2x_dX");
-  MDT_TRY(fork_point());                          // da1^T ready
+  if (!p->simt_latent) {
+    e = Tc05Epi{};
+    e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+    MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
+    TC_NOTE(p, "fc2x_dX");
+    MDT_TRY(fork_point());                        // da1^T ready
+  }
   e = Tc05Epi{};
   e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, sw, tc05_splits_dw(p, e, H, D, B, p->bn_dw)));
@@ -1508,20 +1544,32 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   TC_NOTE(p, "fc4_dX");
   MDT_TRY(after_main(sa, nullptr));               // E1: W4^T no longer needed, da3^T ready
   MDT_TRY(launch_dw(0, sa));
-  e = Tc05Epi{};
-  e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
-  MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
-                                        tc05_splits(p, e, Z, B, H, p->bn_skinny)));
-  TC_NOTE(p, "fc3_dX_reparam_bwd");
-  MDT_TRY(after_main(sb, nullptr));               // E2: W3^T no longer needed, dml^T ready
-  MDT_TRY(launch_dw(1, sb));
-  e = Tc05Epi{};
-  e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
-  MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
-  TC_NOTE(p, "fc2x_dX");
-  MDT_TRY(after_main(sc, sd));                    // E3: W2x^T no longer needed, da1^T ready
-  MDT_TRY(launch_dw(3, sc));
-  MDT_TRY(launch_dw(2, sd));
+  if (p->simt_latent) {
+    MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3^T and W2x: all three remaining updates wait for it
+    if (fork) {
+      MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
+      for (cudaStream_t t : {sb, sc, sd}) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
+      ++nf;
+    }
+    MDT_TRY(launch_dw(3, sc));
+    MDT_TRY(launch_dw(1, sb));
+    MDT_TRY(launch_dw(2, sd));
+  } else {
+    e = Tc05Epi{};
+    e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+    MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
+                                          tc05_splits(p, e, Z, B, H, p->bn_skinny)));
+    TC_NOTE(p, "fc3_dX_reparam_bwd");
+    MDT_TRY(after_main(sb, nullptr));             // E2: W3^T no longer needed, dml^T ready
+    MDT_TRY(launch_dw(1, sb));
+    e = Tc05Epi{};
+    e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+    MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
+    TC_NOTE(p, "fc2x_dX");
+    MDT_TRY(after_main(sc, sd));                  // E3: W2x^T no longer needed, da1^T ready
+    MDT_TRY(launch_dw(3, sc));
+    MDT_TRY(launch_dw(2, sd));
+  }
   if (fork) {
     cudaStream_t st[4] = {sa, sb, sc, sd};
     cudaEvent_t ev[4] = {p->ev_join, p->ev_join2, p->ev_join3, p->ev_join4};
