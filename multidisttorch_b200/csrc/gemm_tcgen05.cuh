@@ -1542,19 +1542,28 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
-  MDT_TRY(after_main(sa, nullptr));               // E1: W4^T no longer needed, da3^T ready
-  MDT_TRY(launch_dw(0, sa));
   if (p->simt_latent) {
-    MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3^T and W2x: all three remaining updates wait for it
+    // No event between fc4's input-gradient GEMM and latent_bwd: a full (event) dependent next to the programmatic
+    // one costs latent_bwd its early launch.  All four updates start together once latent_bwd is done -- fc4's is
+    // not on the critical path, the last of the other three is.
+    const bool dw4_early = getenv("MDT_DW4_LATE") == nullptr;
+    if (dw4_early) {
+      MDT_TRY(after_main(sa, nullptr));           // E1: W4^T no longer needed, da3^T ready
+      MDT_TRY(launch_dw(0, sa));
+    }
+    MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3^T and W2x^T
     if (fork) {
       MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
-      for (cudaStream_t t : {sb, sc, sd}) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
+      for (cudaStream_t t : {sa, sb, sc, sd}) if (t != sa || !dw4_early) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
       ++nf;
     }
-    MDT_TRY(launch_dw(3, sc));
     MDT_TRY(launch_dw(1, sb));
     MDT_TRY(launch_dw(2, sd));
+    MDT_TRY(launch_dw(3, sc));
+    if (!dw4_early) MDT_TRY(launch_dw(0, sa));
   } else {
+    MDT_TRY(after_main(sa, nullptr));             // E1: W4^T no longer needed, da3^T ready
+    MDT_TRY(launch_dw(0, sa));
     e = Tc05Epi{};
     e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
     MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,

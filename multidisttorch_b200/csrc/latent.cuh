@@ -35,7 +35,7 @@ struct LatentFwdArgs {
   int B, Z, nchunks;
   long long* dbg;                     // optional phase stamps (MDT_TC05_DBG=1), same slot layout as the GEMM kernel's
   int first_live_pass;                // always 1 (a run-time value, so the compiler cannot specialise the two passes)
-  int first_pass;                     // 0: dry run + live pass; 1: live pass only (MDT_LATENT_NODRY=1, for measurements)
+  int first_pass;                     // 1: live pass only; 0: a dry run first (MDT_LATENT_DRY=1, for measurements)
 };
 
 struct LatentBwdArgs {
@@ -228,10 +228,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
     const int m0 = blockIdx.x * SC, ns = min(SC, a.B - m0);
     if ((int)threadIdx.x < ns * Z) e_pre = lat_ldg(a.eps_in + (size_t)m0 * Z + threadIdx.x);
   }
-  // Two passes over the same code.  Pass 0 is a dry run BEFORE the dependency wait: it operates on whatever shared
-  // memory holds and stores nothing, its only purpose is to pull the kernel's instructions into the instruction
-  // caches while the predecessor kernel is still running.  A kernel like this executes a few thousand instructions
-  // exactly once per CTA; cold, they are fetched at ~10 cycles each, which was 3/4 of the kernel's run time.
+  // (The pass loop below can start with a dry run of the same code before the dependency wait -- MDT_LATENT_DRY=1 --
+  // to pull the instructions into the caches early.  Measured: no gain, the kernel is not fetch-bound; left as a knob.)
   float kl = 0.f;
   bool fw_ok = true;
 #pragma unroll 1
@@ -348,7 +346,7 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
   }
   bool fw_ok = true;
 #pragma unroll 1
-  for (int pass = a.first_pass; pass < 2; ++pass) {                // pass 0: dry run that warms the instruction caches (see latent_fwd)
+  for (int pass = a.first_pass; pass < 2; ++pass) {     // pass 0: optional dry run (see latent_fwd)
   const bool live = pass >= a.first_live_pass;
   if (live) {
     pdl_wait();
@@ -453,7 +451,7 @@ inline cudaError_t launch_latent_fwd_z(const LatentFwdArgs& a, int sc, dim3 grid
 inline cudaError_t launch_latent_fwd(LatentFwdArgs a, int sc, cudaStream_t s) {
   a.nchunks = (a.B + sc - 1) / sc;
   a.first_live_pass = 1;
-  a.first_pass = getenv("MDT_LATENT_NODRY") ? 1 : 0;
+  a.first_pass = getenv("MDT_LATENT_DRY") ? 0 : 1;
   const dim3 grid(latent_grid(a.B, sc));
   const size_t smem = (size_t)sc * a.H * sizeof(float);
   return a.Z <= 20 ? launch_latent_fwd_z<5>(a, sc, grid, smem, s) : launch_latent_fwd_z<8>(a, sc, grid, smem, s);
@@ -469,7 +467,7 @@ inline cudaError_t launch_latent_bwd_z(const LatentBwdArgs& a, int sc, dim3 grid
 inline cudaError_t launch_latent_bwd(LatentBwdArgs a, int sc, cudaStream_t s) {
   a.nchunks = (a.B + sc - 1) / sc;
   a.first_live_pass = 1;
-  a.first_pass = getenv("MDT_LATENT_NODRY") ? 1 : 0;
+  a.first_pass = getenv("MDT_LATENT_DRY") ? 0 : 1;
   const dim3 grid(latent_grid(a.B, sc));
   const size_t smem = (size_t)sc * a.H * sizeof(float);
   return a.Z <= 20 ? launch_latent_bwd_z<5>(a, sc, grid, smem, s) : launch_latent_bwd_z<8>(a, sc, grid, smem, s);

@@ -10,7 +10,9 @@ names = ["entry", "setup", "tma_issued", "first_data", "mma_done", "accum_seen",
 labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "dz_reparam_bwd", "fc3_dW", "fc2x_dX", "fc1_dW", "fc2x_dW"]
 if not os.environ.get("MDT_TC_LATENT"):   # the latent-side layers are CUDA-core kernels (no stamps): tcgen05 launches left
     # latent_*: stamps are entry / after wait / rows in smem / dots done / element phase done / (fwd: fc3 done) / exit
-    labels = ["fc1_fwd", "latent_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "latent_bwd", "fc1_dW", "fc3_dW", "fc2x_dW"]
+    labels = ["fc1_fwd", "latent_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "latent_bwd", "fc3_dW", "fc2x_dW", "fc1_dW"]
+    if os.environ.get("MDT_DW4_LATE"):
+        labels = ["fc1_fwd", "latent_fwd", "fc4_bce", "fc4_dX", "latent_bwd", "fc3_dW", "fc2x_dW", "fc1_dW", "fc4_dW"]
 out = (C.c_longlong * 512)()
 for mode in sys.argv[1:] or ["tf32", "tf32x3"]:
     H = int(os.environ.get("H", "400")); B = int(os.environ.get("B", "128"))
