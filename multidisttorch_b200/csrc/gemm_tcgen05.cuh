@@ -1213,7 +1213,12 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
   p->bn_dw = 64;
   p->bn_dwa = 32;
-  p->simt_latent = getenv("MDT_TC_LATENT") == nullptr;   // MDT_TC_LATENT=1: keep them on the tensor cores (A/B comparisons)
+  // The CUDA-core latent kernels win while the step is latency-bound (measured: 90 vs 92 us at H=1024 B=128, 58 vs 70 us
+  // at H=400 B=128); every CTA re-reads the 2Z x H weight rows, so at larger H x B the tensor-core GEMMs take over
+  // (147 vs 143 us at H=400 B=1024, 274 vs 255 us at H=1024 B=1024, 248 vs 219 us at H=4096 B=128).
+  // MDT_TC_LATENT=1 / 0 forces either.
+  p->simt_latent = (long long)b.H * b.Bmax <= 256 * 1024;
+  if (const char* v = getenv("MDT_TC_LATENT")) p->simt_latent = v[0] == '0';
   if (const char* v = getenv("MDT_BN_DWA")) p->bn_dwa = atoi(v);
   if (const char* v = getenv("MDT_BN_FC4")) p->bn_fc4 = atoi(v);          // tuning knobs (16 / 32 / 64)
   if (const char* v = getenv("MDT_BN_H")) p->bn_h = atoi(v);

@@ -8,7 +8,7 @@ from oracle import vae_numpy as O
 lib = _lib.load()
 names = ["entry", "setup", "tma_issued", "first_data", "mma_done", "accum_seen", "drained", "epi_done", "exit"]
 labels = ["fc1_fwd", "fc2x_reparam", "fc3_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "dz_reparam_bwd", "fc3_dW", "fc2x_dX", "fc1_dW", "fc2x_dW"]
-if not os.environ.get("MDT_TC_LATENT"):   # the latent-side layers are CUDA-core kernels (no stamps): tcgen05 launches left
+if os.environ.get("MDT_TC_LATENT", "0") == "0":   # the latent-side layers are CUDA-core kernels (no stamps): tcgen05 launches left
     # latent_*: stamps are entry / after wait / rows in smem / dots done / element phase done / (fwd: fc3 done) / exit
     labels = ["fc1_fwd", "latent_fwd", "fc4_bce", "fc4_dX", "fc4_dW", "latent_bwd", "fc3_dW", "fc2x_dW", "fc1_dW"]
     if os.environ.get("MDT_DW4_LATE"):
