@@ -176,6 +176,35 @@ def test_train_steps_match_reference_golden(E, mode, tag, graph):
     eng.close()
 
 
+@pytest.mark.parametrize("mode", [m for m in MODES if m != "fp32"])
+@pytest.mark.parametrize("env", [{"MDT_TC_LATENT": "1"}, {"MDT_NO_FUSED_ADAM": "1"},
+                                 {"MDT_TC_LATENT": "1", "MDT_NO_FUSED_ADAM": "1"}, {"MDT_LATENT_SC": "1"},
+                                 {"MDT_LATENT_SC": "2"}, {"MDT_DW4_LATE": "1"}],
+                         ids=lambda e: "+".join(f"{k[4:].lower()}{v}" for k, v in e.items()))
+def test_alternative_kernel_paths_match_golden(E, mode, env, monkeypatch):
+    """The step has run-time alternatives the defaults do not take at this size (tensor-core latent layers, the
+    flat Adam kernel, other samples-per-CTA / launch orders): each must meet the same golden vectors."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    g = load("step_b48")
+    tol = TOL[mode]
+    B, n = int(g["B"]), int(g["n_steps"])
+    eng = make_engine(E, mode, B)
+    for t in range(n):
+        x, eps = O.make_batch(batch_seed(t), B)
+        loss = float(eng.train_step(dev(x), dev(eps)).item())
+        assert abs(loss - g["losses"][t]) <= tol["loss"] * abs(g["losses"][t]), (env, t, loss, g["losses"][t])
+        if t == 0:
+            gr = eng.segments_to_numpy(eng.grads)
+            for k in O.SEGMENTS:
+                check_fp(g, "grad0", k, gr[k], tol["grad"], f"{env}/{mode}")
+    pN = eng.segments_to_numpy()
+    for k in O.SEGMENTS:
+        check_fp(g, "paramN", k, pN[k], tol["param"], f"{env}/{mode}")
+    assert eng.state()[0] == n
+    eng.close()
+
+
 @pytest.mark.parametrize("mode", MODES)
 def test_forward_eval_decode_golden(E, mode):
     g = load("eval_b64")
