@@ -101,6 +101,8 @@ def algorithmic_bytes(label, B, H, total_params):
         "fc3_dW_adam": B * H + B * Z + H * Z + 6 * (H * Z + H),
         "fc2x_dW_adam": B * 2 * Z + B * H + 2 * Z * H + 6 * (2 * Z * H + 2 * Z),
         "fc1_dW_adam": B * H + B * D + H * D + 6 * (H * D + H),
+        # fc4's update apart from its GEMM: gradient read + 3 reads / 3 writes of p, m, v + the transposed shadow
+        "fc4_adam": 8 * D * H + 7 * D,
     }
     return t.get(label, 0) * f
 

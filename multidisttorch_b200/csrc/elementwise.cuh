@@ -363,6 +363,114 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
   }
 }
 
+// Adam element update for the fused weight-gradient epilogues and adam_tile_kernel.  Same formula as adam_elem (elementwise.cuh); the
+// square root and the quotient use the branch-free SFU forms (rsqrt / rcp approximations, <= 2 ulp) so that the 32
+// elements a thread owns form independent instruction chains the scheduler can interleave -- with the IEEE forms
+// (slow-path branches) the epilogue is a serial dependency chain on a handful of warps.
+__device__ __forceinline__ void adam_elem_fast(float& p, float g, float& m, float& v, float step_size, float inv_bc2_sqrt,
+                                               float omb1, float b2, float omb2, float eps) {
+  m = m + (g - m) * omb1;
+  v = v * b2 + omb2 * g * g;
+  const float sq = v > 0.f ? v * rsqrtf(v) : 0.f;
+  const float denom = sq * inv_bc2_sqrt + eps;
+  p = p - step_size * __fdividef(m, denom);
+}
+
+
+// Step-wide "last one out" duty of the fused-Adam step.  Every CTA of the kernels that apply this step's update calls
+// this once it no longer needs the Adam scalars; the caller that takes the last of `total` tickets adds up the step's
+// loss partials (fixed order), advances the device-resident optimizer state and publishes the loss.  `scr` = 65 floats
+// of shared memory the CTA no longer uses.  Must be reached by every thread of the CTA.
+__device__ __forceinline__ void adam_step_ticket(StepState* st, int total, const float* part_a, int n_a, const float* part_b,
+                                                 int n_b, float* loss_out, float* scr) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    scr[64] = (atomicAdd(&st->ticket_adam, 1u) == (unsigned)total - 1) ? 1.f : 0.f;
+  }
+  __syncthreads();
+  if (scr[64] != 0.f) {
+    float t = 0.f;
+    for (int i = threadIdx.x; i < n_a; i += blockDim.x) t += __ldcg(part_a + i);
+    for (int i = threadIdx.x; i < n_b; i += blockDim.x) t += __ldcg(part_b + i);
+    t = warp_sum(t);
+    if (lane == 0) scr[warp] = t;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float tot = 0.f;
+      for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += scr[w];
+      if (loss_out != nullptr) *loss_out = tot;
+      publish_loss(st, tot);
+      st->adam_t += 1;
+      st->b1_pow *= st->beta1;
+      st->b2_pow *= st->beta2;
+      adam_next_scalars(st->lr, st->beta1, st->beta2, st->eps, st->b1_pow, st->b2_pow, st->next);
+      st->ticket_adam = 0;
+      __threadfence();
+    }
+  }
+}
+
+// Adam on one weight matrix [R, C] (+ its bias [R]) of the flat buffers, 32 x 32 tiles, also refreshing the transposed
+// shadow pT [C, R] the tensor-core path keeps of that weight.  Used for fc4 in the fused-Adam step: its weight-gradient
+// GEMM starts early and would hold 91 SMs for the update's traffic just when the other three updates need them, so it
+// only writes the gradient and this kernel applies the update on whatever SMs are idle.  Takes part in the step's
+// ticket (adam_step_ticket): it reads the scalars before the last ticket can advance them.
+struct AdamTileArgs {
+  float *p, *m, *v; const float* g;      // weight segment bases, row-major [R, C]
+  float *pb, *mb, *vb; const float* gb;  // bias segment bases, [R]
+  float* pT; int ldpT;                   // transposed shadow (or NULL)
+  int R, C, tiles_c;
+  StepState* st; int total_tickets;
+  const float* part_a; int n_a; const float* part_b; int n_b; float* loss_out;
+};
+
+__global__ void __launch_bounds__(256) adam_tile_kernel(AdamTileArgs a) {
+  __shared__ float t[32][33];
+  __shared__ float scr[65];
+  pdl_wait();
+  pdl_trigger();
+  const float step_size = a.st->next[0], inv_bc2 = __frcp_rn(a.st->next[1]), omb1 = a.st->next[2], b2 = a.st->next[3],
+              omb2 = a.st->next[4], eps = a.st->next[5];
+  const int r0 = ((int)blockIdx.x / a.tiles_c) * 32, c0 = ((int)blockIdx.x % a.tiles_c) * 32;
+  const int tr = threadIdx.x >> 3, tc = (threadIdx.x & 7) * 4;     // thread = (row, 4 consecutive columns)
+  const int r = r0 + tr, c = c0 + tc;
+  if (r < a.R && c < a.C) {                                        // C % 4 == 0: a float4 is inside or outside
+    const size_t o = (size_t)r * a.C + c;
+    float4 p = *reinterpret_cast<const float4*>(a.p + o), m = *reinterpret_cast<const float4*>(a.m + o),
+           v = *reinterpret_cast<const float4*>(a.v + o);
+    const float4 g = __ldg(reinterpret_cast<const float4*>(a.g + o));
+    adam_elem_fast(p.x, g.x, m.x, v.x, step_size, inv_bc2, omb1, b2, omb2, eps);
+    adam_elem_fast(p.y, g.y, m.y, v.y, step_size, inv_bc2, omb1, b2, omb2, eps);
+    adam_elem_fast(p.z, g.z, m.z, v.z, step_size, inv_bc2, omb1, b2, omb2, eps);
+    adam_elem_fast(p.w, g.w, m.w, v.w, step_size, inv_bc2, omb1, b2, omb2, eps);
+    *reinterpret_cast<float4*>(a.p + o) = p;
+    *reinterpret_cast<float4*>(a.m + o) = m;
+    *reinterpret_cast<float4*>(a.v + o) = v;
+    t[tr][tc] = p.x; t[tr][tc + 1] = p.y; t[tr][tc + 2] = p.z; t[tr][tc + 3] = p.w;
+  }
+  if (c0 == 0 && tc == 0 && r < a.R) {                             // first tile column also owns the bias rows
+    float pb = a.pb[r], mb = a.mb[r], vb = a.vb[r];
+    adam_elem_fast(pb, __ldg(a.gb + r), mb, vb, step_size, inv_bc2, omb1, b2, omb2, eps);
+    a.pb[r] = pb; a.mb[r] = mb; a.vb[r] = vb;
+  }
+  if (a.pT != nullptr) {
+    __syncthreads();
+    const int cc = c0 + tr, rr = r0 + tc;                          // thread = (column, 4 consecutive rows)
+    if (cc < a.C) {
+      float* dst = a.pT + (size_t)cc * a.ldpT + rr;
+      if (rr + 3 < a.R && (a.ldpT & 3) == 0) {
+        *reinterpret_cast<float4*>(dst) = make_float4(t[tc][tr], t[tc + 1][tr], t[tc + 2][tr], t[tc + 3][tr]);
+      } else {
+#pragma unroll
+        for (int q = 0; q < 4; ++q) if (rr + q < a.R) dst[q] = t[tc + q][tr];
+      }
+    }
+  }
+  adam_step_ticket(a.st, a.total_tickets, a.part_a, a.n_a, a.part_b, a.n_b, a.loss_out, scr);
+}
+
 // ============================================================================
 // Device-resident data path: x[b, :] = images_u8[idx[b], :] / 255   -- what
 // transforms.ToTensor() + the DataLoader collate produce on the host (ref:vae-hpo.py:135-150),

@@ -225,19 +225,6 @@ __device__ __forceinline__ float fast_dlogit(float r, float x) {
   return p >= 1e-12f ? (r - x) : (r - x) * 1e12f * p;
 }
 
-// Adam element update for the fused weight-gradient epilogue.  Same formula as adam_elem (elementwise.cuh); the
-// square root and the quotient use the branch-free SFU forms (rsqrt / rcp approximations, <= 2 ulp) so that the 32
-// elements a thread owns form independent instruction chains the scheduler can interleave -- with the IEEE forms
-// (slow-path branches) the epilogue is a serial dependency chain on a handful of warps.
-__device__ __forceinline__ void adam_elem_fast(float& p, float g, float& m, float& v, float step_size, float inv_bc2_sqrt,
-                                               float omb1, float b2, float omb2, float eps) {
-  m = m + (g - m) * omb1;
-  v = v * b2 + omb2 * g * g;
-  const float sq = v > 0.f ? v * rsqrtf(v) : 0.f;
-  const float denom = sq * inv_bc2_sqrt + eps;
-  p = p - step_size * __fdividef(m, denom);
-}
-
 // Transposed store of the tile: thread = (tile row, column half); reads float4 from its row, writes four scalars,
 // each of which is coalesced across the warp (consecutive lanes = consecutive m).
 template <int BN>
@@ -876,37 +863,9 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     __syncwarp();
     ptx::tmem_dealloc(tmem_base, kTmemCols);
   }
-  if (kEpi == EPI_GRADW && ep.adam_total_ctas > 0) {
-    // Every CTA of the step's four weight-gradient GEMMs takes a ticket once it no longer needs the Adam scalars; the
-    // last one advances the device-resident optimizer state and adds up the step's loss partials (fixed order).
-    float* scr = reinterpret_cast<float*>(smem);
-    if (threadIdx.x == 0) {
-      __threadfence();
-      scr[64] = (atomicAdd(&ep.adam_st->ticket_adam, 1u) == (unsigned)ep.adam_total_ctas - 1) ? 1.f : 0.f;
-    }
-    __syncthreads();
-    if (scr[64] != 0.f) {
-      float t = 0.f;
-      for (int i = threadIdx.x; i < ep.n_part_a; i += blockDim.x) t += __ldcg(ep.loss_part_a + i);
-      for (int i = threadIdx.x; i < ep.n_part_b; i += blockDim.x) t += __ldcg(ep.loss_part_b + i);
-      t = warp_sum(t);
-      if (lane == 0) scr[warp] = t;
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        float tot = 0.f;
-        for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += scr[w];
-        if (ep.adam_loss_out != nullptr) *ep.adam_loss_out = tot;
-        StepState* st = ep.adam_st;
-        st->adam_t += 1;
-        st->b1_pow *= st->beta1;
-        st->b2_pow *= st->beta2;
-        adam_next_scalars(st->lr, st->beta1, st->beta2, st->eps, st->b1_pow, st->b2_pow, st->next);
-        st->ticket_adam = 0;
-        __threadfence();
-        publish_loss(st, tot);
-      }
-    }
-  }
+  if (kEpi == EPI_GRADW && ep.adam_total_ctas > 0)
+    adam_step_ticket(ep.adam_st, ep.adam_total_ctas, ep.loss_part_a, ep.n_part_a, ep.loss_part_b, ep.n_part_b, ep.adam_loss_out,
+                     reinterpret_cast<float*>(smem));
   if (threadIdx.x == 0) {
     TC_STAMP(8);
     if (ep.dbg != nullptr) {                     // grid-wide: the moment the last CTA left
@@ -1514,8 +1473,13 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     return MDT_OK;
   };
   struct Dw { int seg_w, seg_b, M, N, bn, slot; const CUtensorMap *a, *bm; const float* a_src; float* pT; int ldpT; const char* label; int ns; };
+  // MDT_W4_SPLIT=1: fc4's update runs apart from its weight-gradient GEMM (adam_tile_kernel, see there)
+  // (measured: 60.5 vs 57.4 us/step -- the update's 325 small blocks crowd the SMs the other GEMMs need; kept as a knob)
+  const bool w4_split = getenv("MDT_W4_SPLIT") != nullptr;
+  int bn4 = w4_split ? p->bn_dw : bna;
+  if (const char* v = getenv("MDT_BN_DW4")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn4 = c; }
   Dw dw[4] = {
-      {W4, B4, D, H, bna, 0, &m->da4T, &m->h3Ta, p->da4T, p->W4T, D, "fc4_dW_adam", 1},
+      {W4, B4, D, H, bn4, 0, &m->da4T, bn4 == bna ? &m->h3Ta : &m->h3T, p->da4T, p->W4T, D, w4_split ? "fc4_dW" : "fc4_dW_adam", 1},
       {W3, B3, H, Z, 32, 1, &m->da3T, &m->zT, p->da3T, p->W3T, H, "fc3_dW_adam", 1},
       {W2X, B2X, 2 * Z, H, bna, 2, &m->dmlT, &m->h1Ta, p->dmlT, p->W2xT, 2 * Z, "fc2x_dW_adam", 1},
       {W1, B1, H, D, bna, 3, &m->da1T, &m->xTa, p->da1T, nullptr, 0, "fc1_dW_adam", 1},
@@ -1527,21 +1491,45 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     e = Tc05Epi{};
     const int64_t ow = b.L.off[dw[i].seg_w], ob = b.L.off[dw[i].seg_b];
     e.C = G + ow; e.ldc = dw[i].N; e.a_src = dw[i].a_src; e.lda_src = ldB; e.db = G + ob;
-    e.adam_p = b.params + ow; e.adam_m = b.exp_avg + ow; e.adam_v = b.exp_avg_sq + ow;
-    e.adam_pT = dw[i].pT; e.adam_ldpT = dw[i].ldpT;
-    e.adam_pb = b.params + ob; e.adam_mb = b.exp_avg + ob; e.adam_vb = b.exp_avg_sq + ob;
-    e.adam_st = b.st;
+    const bool fused = !(i == 0 && w4_split);
+    if (fused) {
+      e.adam_p = b.params + ow; e.adam_m = b.exp_avg + ow; e.adam_v = b.exp_avg_sq + ow;
+      e.adam_pT = dw[i].pT; e.adam_ldpT = dw[i].ldpT;
+      e.adam_pb = b.params + ob; e.adam_mb = b.exp_avg + ob; e.adam_vb = b.exp_avg_sq + ob;
+      e.adam_st = b.st;
+    }
     dw[i].ns = tc05_splits_dw(p, e, dw[i].M, dw[i].N, B, dw[i].bn, dw[i].slot);
-    total_ctas += ((dw[i].N + dw[i].bn - 1) / dw[i].bn) * ((dw[i].M + kTcBM - 1) / kTcBM) * dw[i].ns;
+    if (fused) total_ctas += ((dw[i].N + dw[i].bn - 1) / dw[i].bn) * ((dw[i].M + kTcBM - 1) / kTcBM) * dw[i].ns;
+  }
+  AdamTileArgs at{};
+  int at_blocks = 0;
+  if (w4_split) {
+    const int64_t ow = b.L.off[W4], ob = b.L.off[B4];
+    at.p = b.params + ow; at.m = b.exp_avg + ow; at.v = b.exp_avg_sq + ow; at.g = G + ow;
+    at.pb = b.params + ob; at.mb = b.exp_avg + ob; at.vb = b.exp_avg_sq + ob; at.gb = G + ob;
+    at.pT = p->W4T; at.ldpT = D; at.R = D; at.C = H; at.tiles_c = (H + 31) / 32;
+    at.st = b.st;
+    at_blocks = ((D + 31) / 32) * at.tiles_c;
+    total_ctas += at_blocks;
+    at.total_tickets = total_ctas;
+    tc05_loss_partials(p, B, &at.part_a, &at.n_a, &at.part_b, &at.n_b);
+    at.loss_out = b.loss_dev;
   }
   for (int i = 0; i < 4; ++i) {
+    if (i == 0 && w4_split) continue;
     ed[i].adam_total_ctas = total_ctas;
     tc05_loss_partials(p, B, &ed[i].loss_part_a, &ed[i].n_part_a, &ed[i].loss_part_b, &ed[i].n_part_b);
     ed[i].adam_loss_out = b.loss_dev;
   }
+  if (w4_split) at.total_tickets = total_ctas;
   auto launch_dw = [&](int i, cudaStream_t st) -> int {
     MDT_TRY(tc05_launch<EPI_GRADW>(dw[i].bn, sp, *dw[i].a, *dw[i].bm, dw[i].M, dw[i].N, B, ed[i], st, dw[i].ns));
-    return b.note(b.note_ctx, dw[i].label);
+    MDT_TRY(b.note(b.note_ctx, dw[i].label));
+    if (i == 0 && w4_split) {
+      MDT_CUDA(launch_pdl(adam_tile_kernel, dim3(at_blocks), dim3(256), 0, st, at));
+      MDT_TRY(b.note(b.note_ctx, "fc4_adam"));
+    }
+    return MDT_OK;
   };
   Tc05Epi e{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
@@ -1564,7 +1552,10 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     }
     MDT_TRY(launch_dw(1, sb));
     MDT_TRY(launch_dw(2, sd));
-    MDT_TRY(launch_dw(3, sc));
+    // fc1's update is the longest of the three: it stays on the main stream, where it is launched programmatically
+    // behind latent_bwd and has its set-up (barriers, TMEM, descriptor and parameter fetches: ~2.5 us for an
+    // event-launched kernel) done before latent_bwd finishes
+    MDT_TRY(launch_dw(3, getenv("MDT_DW1_SIDE") ? sc : s));
     if (!dw4_early) MDT_TRY(launch_dw(0, sa));
   } else {
     MDT_TRY(after_main(sa, nullptr));             // E1: W4^T no longer needed, da3^T ready
