@@ -126,6 +126,25 @@ __device__ __forceinline__ float to_tf32(float x) {
 __device__ __forceinline__ float tf32_hi(float x) { return __uint_as_float(__float_as_uint(x) & 0xffffe000u); }
 __device__ __forceinline__ void bar_sync_epi() { asm volatile("bar.sync 1, 256;" ::: "memory"); }  // the 8 epilogue warps
 
+// thread-block cluster: barrier over every thread of the cluster, and access to a peer CTA's shared memory
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_map(uint32_t smem_addr, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(smem_addr), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ float4 cluster_ld4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared::cluster.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cluster_st4(uint32_t addr, float4 v) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+
 }  // namespace ptx
 
 // ------------------------------------------------------------------------------------------------
@@ -181,6 +200,7 @@ struct Tc05Epi {
   const float* loss_part_a; int n_part_a; const float* loss_part_b; int n_part_b; float* adam_loss_out;
   // split-K workspace: [tile][split][128*BN] partial tiles + one ticket counter per tile
   float* ws; unsigned int* ws_counters;
+  int cluster;   // split-K CTAs of a tile form a thread-block cluster (1,1,splits): partials are exchanged through DSMEM
   // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
   long long* dbg;
 };
@@ -561,7 +581,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int kb_per_split = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
   const int kb0 = (int)blockIdx.z * kb_per_split;
   const int num_kb = min(kb_per_split, total_kb - kb0);      // >= 1 (the host picks gridDim.z accordingly)
-  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == gridDim.z - 1;
+  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == (ep.cluster ? 0 : gridDim.z - 1);
 #define TC_STAMP(i) do { if (dbg) ep.dbg[i] = clock64(); } while (0)
   if (threadIdx.x == 0) {
     TC_STAMP(0);
@@ -626,6 +646,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
       TC_STAMP(2);
     }
+    if (ep.cluster) { __syncwarp(); ptx::cluster_sync_all(); ptx::cluster_sync_all(); }   // the two exchange barriers (below)
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
@@ -663,6 +684,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       if (!kSplit) ptx::mma_commit(bar_accum);
       TC_STAMP(4);
     }
+    if (ep.cluster) { __syncwarp(); ptx::cluster_sync_all(); ptx::cluster_sync_all(); }
   } else if (kSplit && warp >= 2 + kTcEpiThreads / 32) {
     // ===== TF32X3 drain warps: sum the per-k-block partial accumulators in fp32 registers =====
     const int q = warp & 3;                       // TMEM lane quadrant of this warp
@@ -692,6 +714,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int c = 0; c < BN / 4; ++c)
       *reinterpret_cast<float4*>(T + row * S::TILE_LD + 4 * c) = make_float4(pacc[4 * c], pacc[4 * c + 1], pacc[4 * c + 2], pacc[4 * c + 3]);
     asm volatile("bar.sync 2, 384;" ::: "memory");
+    if (ep.cluster) { ptx::cluster_sync_all(); ptx::cluster_sync_all(); }
   } else {
     // ===== split (TF32X3) + epilogue warps =====
     const int et = threadIdx.x - 64;              // 0..255
@@ -794,7 +817,31 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
     if (et == 0) TC_STAMP(6);
     bool run_epilogue = true;
-    if (gridDim.z > 1) {
+    if (gridDim.z > 1 && ep.cluster) {
+      // Split-K inside a thread-block cluster: the splits of a tile are the CTAs of one cluster.  Every CTA has parked
+      // its partial tile at the same shared-memory offset; after a cluster barrier each CTA sums a 1/splits slice of
+      // the tile over all peers (fixed rank order: deterministic) through distributed shared memory and stores the
+      // slice into rank 0's tile; a second barrier, then rank 0 runs the epilogue.  No workspace round trip through
+      // L2, no fence + ticket chain.
+      constexpr int F4 = kTcBM * BN / 4;
+      const uint32_t ns = gridDim.z, rank = blockIdx.z;
+      const int chunk = (F4 + (int)ns - 1) / (int)ns;
+      const int f_hi = min(F4, ((int)rank + 1) * chunk);
+      ptx::cluster_sync_all();
+      for (int f = (int)rank * chunk + et; f < f_hi; f += kTcEpiThreads) {
+        const uint32_t off = ptx::smem_u32(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4);
+        float4 v[8];
+#pragma unroll
+        for (uint32_t r = 0; r < 8; ++r)
+          v[r] = (r < ns) ? ptx::cluster_ld4(ptx::cluster_map(off, r)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        float4 acc = v[0];
+#pragma unroll
+        for (int r = 1; r < 8; ++r) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
+        ptx::cluster_st4(ptx::cluster_map(off, 0), acc);
+      }
+      ptx::cluster_sync_all();
+      run_epilogue = rank == 0;
+    } else if (gridDim.z > 1) {
       // Deterministic split-K reduction: every split parks its partial tile in the workspace; the CTA that takes the
       // last ticket of the tile adds the partials in split order (independent of arrival order) and runs the epilogue.
       constexpr int F4 = kTcBM * BN / 4;                       // float4 per tile
@@ -1041,17 +1088,45 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   Tc05Epi epd = ep;
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
-  MDT_CUDA(launch_pdl(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(tc_threads(kSplit)), (size_t)S::TOTAL, s, a, b, M, N, K, epd));
+  // split-K: the splits of a tile exchange their partials through distributed shared memory when they fit one cluster
+  static const bool use_clusters = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+  epd.cluster = (nsplit > 1 && nsplit <= 8 && use_clusters) ? 1 : 0;
+  if (epd.cluster) {
+    // a cluster needs its CTAs on SMs of one GPC at the same time: when the tiles do not all fit as co-resident
+    // clusters the launch runs in two waves (measured: fc4 forward, 49 tiles x 3 splits, 8.4 -> 14 us) -- keep the
+    // workspace path then
+    static int max_clusters[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+    if (max_clusters[nsplit] == 0) {
+      cudaLaunchConfig_t cfg{};
+      cfg.gridDim = dim3(1, 1, nsplit); cfg.blockDim = dim3(tc_threads(kSplit)); cfg.dynamicSmemBytes = S::TOTAL;
+      cudaLaunchAttribute at[1];
+      at[0].id = cudaLaunchAttributeClusterDimension;
+      at[0].val.clusterDim.x = 1; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = nsplit;
+      cfg.attrs = at; cfg.numAttrs = 1;
+      int n = 0;
+      if (cudaOccupancyMaxActiveClusters(&n, tc05_gemm_kernel<BN, kSplit, kEpi>, &cfg) != cudaSuccess) { n = -1; cudaGetLastError(); }
+      max_clusters[nsplit] = n > 0 ? n : -1;
+    }
+    if (max_clusters[nsplit] < (int)(grid.x * grid.y)) epd.cluster = 0;
+  }
+  if (epd.cluster)
+    MDT_CUDA(launch_pdl_cluster(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(tc_threads(kSplit)), (size_t)S::TOTAL, s,
+                                (unsigned)nsplit, a, b, M, N, K, epd));
+  else
+    MDT_CUDA(launch_pdl(tc05_gemm_kernel<BN, kSplit, kEpi>, grid, dim3(tc_threads(kSplit)), (size_t)S::TOTAL, s, a, b, M, N, K, epd));
   return MDT_OK;
 }
 
-// Number of K-splits for a GEMM: only when a workspace is given, at least 4 k-blocks (128 K-values) per split, and
+// Number of K-splits for a GEMM: only when a workspace is given, at least min_kb k-blocks (of 32 K-values) per split, and
 // no more CTAs than SMs (one wave).
 inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc05Epi& ep, size_t ws_floats) {
   if (ep.ws == nullptr || ep.ws_counters == nullptr) return 1;
   const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
   const int total_kb = (K + kTcBK - 1) / kTcBK;
-  int want = total_kb / 4;
+  // at least 3 k-blocks per split (4 without the cluster exchange, whose reduction costs ~1.5 us less: measured)
+  static const int min_kb = getenv("MDT_MIN_KB_PER_SPLIT") ? atoi(getenv("MDT_MIN_KB_PER_SPLIT"))
+                                                           : (getenv("MDT_NO_CLUSTER_SPLITK") ? 4 : 3);
+  int want = total_kb / (min_kb > 0 ? min_kb : 4);
   const int cap = sm_count / tiles;
   if (want > cap) want = cap;
   if (want > 8) want = 8;
@@ -1169,7 +1244,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->ldB = (int)round_up(b.Bmax, 4);
   p->bn_h = b.H >= 2048 ? 64 : 32;
   p->bn_d = b.Bmax > 512 ? 64 : 32;
-  p->bn_fc4 = b.Bmax > 512 ? 64 : (b.Bmax > 256 ? 32 : 16);
+  p->bn_fc4 = b.Bmax > 512 ? 64 : 32;   // 32: 25 tiles x 4 splits still fit as co-resident clusters (16: 49 x 3 do not)
   p->bn_dw = 64;
   p->bn_dwa = 32;
   // The CUDA-core latent kernels win while the step is latency-bound (measured: 90 vs 92 us at H=1024 B=128, 58 vs 70 us
