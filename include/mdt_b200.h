@@ -166,6 +166,18 @@ int mdt_engine_workspace(mdt_engine* e, const char* name, float** ptr, int* ld);
  * kernels inside the graph).  Measurement aid; no reference counterpart. */
 int mdt_engine_launch_count(mdt_engine* e, int64_t* kernels);
 
+/* Gradient exchange over NVLink peer memory for a group whose ranks sit on one node (replaces the ncclAllReduce +
+ * optimizer read of ref:vae-hpo.py:72-74 / torch DDP's reducer; mdt_allreduce_grads stays the NCCL form).
+ * mdt_engine_exchange_handle: allocates this rank's exchange region on first use and returns its 64-byte CUDA IPC
+ * handle.  The host side gathers the handles of the group (rank order) and passes all n of them to
+ * mdt_engine_set_peers, which maps the peers' regions.  From then on mdt_train_step / mdt_train_step_host write the
+ * gradient into the exchange region, and one kernel per rank waits for its peers' "ready" flags, sums the n partial
+ * gradients in rank order (own from local memory, the others over NVLink), stores the sum into the bound gradient
+ * buffer and applies Adam.  Errors: MDT_ERR_CUDA when a peer's region cannot be mapped (no peer access) -- the caller
+ * then simply keeps the NCCL path. */
+int mdt_engine_exchange_handle(mdt_engine* e, void* handle64);
+int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n);
+
 /* Measurement aid: run `iters` un-graphed training steps on x with a CUDA event after
  * every kernel and write "label avg_ms\n" lines (one per kernel of the step, in launch
  * order) into `out`.  The steps DO update the parameters.  No reference counterpart

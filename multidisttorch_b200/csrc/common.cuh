@@ -86,6 +86,8 @@ struct StepState {
   unsigned int ticket_loss;
   unsigned int host_seq;             // training steps published to host_mailbox so far
   unsigned long long* host_mailbox;  // pinned, device-mapped host word: (host_seq << 32) | bits(loss) of the last step
+  unsigned int xch_seq;              // peer-memory gradient exchanges completed (never reset: the flags are monotonic)
+  unsigned int xch_error;            // set when a bounded wait on a peer's flag expired
 };
 
 // Called by the one thread that finalises a training step's loss: hands (sequence number, loss) to the host in a

@@ -472,6 +472,108 @@ __global__ void __launch_bounds__(256) adam_tile_kernel(AdamTileArgs a) {
 }
 
 // ============================================================================
+// Gradient all-reduce over NVLink peer memory fused into the Adam kernel (groups of n > 1 ranks on one node).
+//
+// The reference's DDP all-reduces the gradient and then the optimizer reads it again (ref:vae-hpo.py:72-74).  Here
+// every rank's weight-gradient GEMMs write into an exchange buffer that its peers have mapped (CUDA IPC), and ONE
+// kernel per rank does both: it tells its peers "my gradient of exchange #t is complete" (a release store into each
+// peer's flag block), waits for theirs, then for every element loads the n partial gradients -- its own from local
+// memory, the others over NVLink, bypassing L1 -- adds them in rank order (so all ranks get bit-identical sums),
+// stores the sum where DDP would leave it (the caller's gradient buffer) and applies the Adam update.  No NCCL launch,
+// no second pass over the gradient, and the transfer overlaps the update arithmetic element by element.  Before it
+// exits, the kernel's last block tells the peers it has finished reading and waits for the same from them: the exchange
+// buffer may be overwritten by the next step as soon as the kernel is complete.  All waits are bounded (~2 s).
+constexpr int kMaxPeers = 8;
+struct PeerArgs {
+  int n, me;
+  const float* g[kMaxPeers];          // exchange buffers, indexed by group rank (g[me] = this rank's own)
+  unsigned int* flags[kMaxPeers];     // flag blocks: [0..8) "gradient ready" by source rank, [8..16) "done reading"
+  float* g_out;                       // where the summed gradient is stored
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned int* p, unsigned int v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
+  unsigned int v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ bool wait_flag_ge(const unsigned int* p, unsigned int t) {
+  const long long t0 = clock64();
+  while ((int)(ld_acquire_sys(p) - t) < 0) {
+    if (clock64() - t0 > 4000000000LL) return false;
+    __nanosleep(20);
+  }
+  return true;
+}
+
+__global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a, PeerArgs pa) {
+  pdl_wait();
+  pdl_trigger();
+  const float step_size = a.st->next[0], bc2_sqrt = a.st->next[1], omb1 = a.st->next[2], b2 = a.st->next[3],
+              omb2 = a.st->next[4], eps = a.st->next[5];
+  const unsigned int t = a.st->xch_seq + 1u;          // bumped by the last block, after every block has read it
+  const float gs = a.grad_scale;
+  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
+    if (blockIdx.x == 0) {                            // this rank's gradient is complete (the kernel is stream-ordered
+      __threadfence_system();                         // behind its weight-gradient GEMMs): tell peer threadIdx.x
+      st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
+    }
+    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) a.st->xch_error = 1u;
+  }
+  __syncthreads();
+  if (a.loss_out != nullptr && blockIdx.x == 0) {     // block-uniform branch (same duty as in adam_flat_kernel)
+    __shared__ float red[32];
+    float l = 0.f;
+    for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) l += __ldcg(a.loss_part_a + i);
+    for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) l += __ldcg(a.loss_part_b + i);
+    l = block_sum(l, red);
+    if (threadIdx.x == 0) { *a.loss_out = l; publish_loss(a.st, l); }
+  }
+  const long long n4 = a.n >> 2;                      // the flat layout is a multiple of 32 floats: no scalar tail
+  float4* p4 = reinterpret_cast<float4*>(a.p);
+  float4* m4 = reinterpret_cast<float4*>(a.m);
+  float4* v4 = reinterpret_cast<float4*>(a.v);
+  float4* go4 = reinterpret_cast<float4*>(pa.g_out);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 gr[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+      gr[r] = (r < pa.n) ? __ldcg(reinterpret_cast<const float4*>(pa.g[r]) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 p = p4[i], m = m4[i], v = v4[i];
+    float4 g = gr[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) { g.x += gr[r].x; g.y += gr[r].y; g.z += gr[r].z; g.w += gr[r].w; }
+    go4[i] = g;
+    g.x *= gs; g.y *= gs; g.z *= gs; g.w *= gs;
+    adam_elem(p.x, g.x, m.x, v.x, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.y, g.y, m.y, v.y, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.z, g.z, m.z, v.z, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.w, g.w, m.w, v.w, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    p4[i] = p; m4[i] = m; v4[i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int done = atomicAdd(&a.st->ticket_adam, 1u);
+    if (done == gridDim.x - 1) {
+      a.st->adam_t += 1;
+      a.st->b1_pow *= a.st->beta1;
+      a.st->b2_pow *= a.st->beta2;
+      adam_next_scalars(a.st->lr, a.st->beta1, a.st->beta2, a.st->eps, a.st->b1_pow, a.st->b2_pow, a.st->next);
+      a.st->xch_seq = t;
+      a.st->ticket_adam = 0;
+      __threadfence_system();
+      for (int r = 0; r < pa.n; ++r)                  // every block of this rank has finished reading the peers' buffers
+        if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
+      for (int r = 0; r < pa.n; ++r)
+        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) a.st->xch_error = 1u;
+    }
+  }
+}
+
+// ============================================================================
 // Device-resident data path: x[b, :] = images_u8[idx[b], :] / 255   -- what
 // transforms.ToTensor() + the DataLoader collate produce on the host (ref:vae-hpo.py:135-150),
 // gathered straight into the step's stage buffer.  16 pixels per thread (one 16-byte load, four

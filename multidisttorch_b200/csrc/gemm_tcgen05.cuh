@@ -1191,6 +1191,9 @@ struct Tc05Plan {
   // Where the next forward's x lives (NULL: already in the stage buffer).  The prologue kernel reads it from there and
   // fills the stage buffer itself; last_prep / prep_launched let the engine find and re-point that kernel in a graph.
   const float* x_src = nullptr;
+  // Non-NULL while the engine enqueues a peer-memory exchange step: the weight-gradient GEMMs of tc05_backward write
+  // the gradient there (the buffer the group's peers have mapped) instead of into the caller's gradient buffer.
+  float* grads_override = nullptr;
   PrepArgs last_prep{};
   bool prep_launched = false;
   cudaStream_t side = nullptr, side2 = nullptr, side3 = nullptr, side4 = nullptr;
@@ -1455,23 +1458,26 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   const Tc05Buffers& b = p->b;
   const bool sp = b.split3;
   const int D = b.D, H = b.H, Z = b.Z, ldB = p->ldB;
-  float* G = b.grads;
+  float* G = p->grads_override ? p->grads_override : b.grads;
   Tc05ActMaps* m = nullptr;
   MDT_TRY(tc05_act_maps(p, B, &m));
   (void)x;   // x^T was written by this step's forward prologue
   const bool fork = !(b.serial && *b.serial);
-  cudaStream_t sw = fork ? p->side : s;          // stream of the weight-gradient GEMMs
+  // The four weight-gradient GEMMs are independent of each other: each trails on its own side stream (fc1's, the
+  // last and largest, stays on the main stream behind the kernel that produces its operand).
+  cudaStream_t sw = fork ? p->side : s;
+  cudaStream_t sw3 = fork ? p->side2 : s, sw2x = fork ? p->side4 : s;
   int nf = 0;
-  auto fork_point = [&]() -> int {               // everything enqueued on `s` so far is visible to later work on `sw`
+  auto fork_to = [&](cudaStream_t t) -> int {    // everything enqueued on `s` so far is visible to later work on `t`
     if (!fork) return MDT_OK;
     MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
-    MDT_CUDA(cudaStreamWaitEvent(sw, p->ev_fork[nf], 0));
+    MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
     ++nf;
     return MDT_OK;
   };
   Tc05Epi e{};
-  // critical path on `s`: fc4 dX -> dz/reparam -> fc2x dX ; weight gradients trail on `sw`
-  MDT_TRY(fork_point());                          // da4^T, h3^T ready
+  // critical path on `s`: fc4 dX -> dz/reparam -> fc2x dX
+  MDT_TRY(fork_to(sw));                           // da4^T, h3^T ready
   e = Tc05Epi{};
   e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw, tc05_splits_dw(p, e, D, H, B, p->bn_dw)));
@@ -1481,10 +1487,10 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
-  MDT_TRY(fork_point());                          // da3^T ready (z^T since the forward)
+  MDT_TRY(fork_to(sw3));                          // da3^T ready (z^T since the forward)
   e = Tc05Epi{};
   e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
-  MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw, tc05_splits_dw(p, e, H, Z, B, 32)));
+  MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw3, tc05_splits_dw(p, e, H, Z, B, 32, 1)));
   TC_NOTE(p, "fc3_dW");
   if (p->simt_latent) {
     MDT_TRY(tc05_latent_bwd(p, s, B));
@@ -1495,25 +1501,28 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
                                           tc05_splits(p, e, Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc3_dX_reparam_bwd");
   }
-  MDT_TRY(fork_point());                          // dml^T ready (latent_bwd: da1^T too)
+  MDT_TRY(fork_to(sw2x));                         // dml^T ready (latent_bwd: da1^T too)
   e = Tc05Epi{};
   e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw, tc05_splits_dw(p, e, 2 * Z, H, B, p->bn_dw)));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw2x, tc05_splits_dw(p, e, 2 * Z, H, B, p->bn_dw, 2)));
   TC_NOTE(p, "fc2x_dW");
   if (!p->simt_latent) {
     e = Tc05Epi{};
     e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
     MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
     TC_NOTE(p, "fc2x_dX");
-    MDT_TRY(fork_point());                        // da1^T ready
   }
   e = Tc05Epi{};
   e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, sw, tc05_splits_dw(p, e, H, D, B, p->bn_dw)));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, s, tc05_splits_dw(p, e, H, D, B, p->bn_dw, 3)));
   TC_NOTE(p, "fc1_dW");
-  if (fork) {                                     // join: the gradient buffer is complete once `sw` drains
-    MDT_CUDA(cudaEventRecord(p->ev_join, sw));
-    MDT_CUDA(cudaStreamWaitEvent(s, p->ev_join, 0));
+  if (fork) {                                     // join: the gradient buffer is complete once the side streams drain
+    cudaStream_t st[3] = {sw, sw3, sw2x};
+    cudaEvent_t ev[3] = {p->ev_join, p->ev_join2, p->ev_join4};
+    for (int i = 0; i < 3; ++i) {
+      MDT_CUDA(cudaEventRecord(ev[i], st[i]));
+      MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+    }
   }
   return MDT_OK;
 }

@@ -108,6 +108,11 @@ struct mdt_engine {
   unsigned int* loss_ticket;
   StepState* st;
   float* loss_pinned = nullptr;
+  // peer-memory gradient exchange (groups of n > 1 on one node): see adam_allreduce_kernel
+  float* xch = nullptr;                 // own exchange region (cudaMalloc): L.total floats of gradient + 64 flag words
+  void* xch_opened[kMaxPeers] = {};     // peers' regions mapped with cudaIpcOpenMemHandle
+  PeerArgs peers{};
+  bool p2p = false;
   volatile unsigned long long* mailbox = nullptr;   // loss_pinned + 64 bytes: see publish_loss()
   unsigned int pub_expected = 0;                    // training steps enqueued so far that publish to the mailbox
   int last_B = 0;  // batch of the activations currently held
@@ -282,6 +287,19 @@ int enqueue_adam(mdt_engine* e, float grad_scale, bool finalize_loss = false) {
   return MDT_OK;
 }
 
+// Gradient exchange over peer memory + Adam in one kernel (replaces finish_allreduce + enqueue_adam for the step).
+int enqueue_adam_p2p(mdt_engine* e, float grad_scale) {
+  AdamArgs a{};
+  a.p = e->params; a.g = e->grads; a.m = e->m; a.v = e->v; a.n = e->L.total; a.st = e->st; a.grad_scale = grad_scale;
+  tc05_loss_partials(e->tc, e->last_B, &a.loss_part_a, &a.n_part_a, &a.loss_part_b, &a.n_part_b);
+  a.loss_out = e->loss_dev;
+  PeerArgs pa = e->peers;
+  pa.g_out = e->grads;
+  MDT_CUDA(launch_pdl(adam_allreduce_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a, pa));
+  MDT_TRY(note_launch(e, "adam_allreduce_p2p"));
+  return tc05_params_changed(e->tc, e->stream);   // refresh the transposed weight shadows
+}
+
 int enqueue_forward(mdt_engine* e, const float* x, int B, const float* eps_in, bool decode_only) {
   if (e->tc) return tc05_forward(e->tc, e->stream, x, B, eps_in, decode_only, /*fuse_loss=*/false);
   return enqueue_forward_fp32(e, x, B, eps_in, decode_only);
@@ -449,6 +467,18 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
       return enqueue_adam(e, gscale, true);
     });
   }
+  if (e->p2p && e->tc && !e->prof_on) {
+    // group on one node with peer access: gradients are exchanged through NVLink peer memory inside the Adam kernel
+    return run_cached(e, /*kind=*/8, B, eps != nullptr, [&]() -> int {
+      e->tc->grads_override = e->xch;
+      e->defer_buckets = true;                    // no NCCL buckets in this step
+      int rc = enqueue_fwd_loss_bwd(e, x, B, eps);
+      e->defer_buckets = false;
+      e->tc->grads_override = nullptr;
+      MDT_TRY(rc);
+      return enqueue_adam_p2p(e, gscale);
+    });
+  }
   if (getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0') {   // NCCL outside the graphs
     MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
     MDT_TRY(finish_allreduce(e));
@@ -552,10 +582,58 @@ void mdt_engine_destroy(mdt_engine* e) {
   if (e->comm_stream) { cudaStreamSynchronize(e->comm_stream); cudaStreamDestroy(e->comm_stream); }
   for (auto& ev : e->ev_bucket) if (ev) cudaEventDestroy(ev);
   if (e->ev_comm_done) cudaEventDestroy(e->ev_comm_done);
+  for (void* p : e->xch_opened) if (p) cudaIpcCloseMemHandle(p);
+  if (e->xch) cudaFree(e->xch);
   if (e->slab) cudaFree(e->slab);
   if (e->loss_pinned) cudaFreeHost(e->loss_pinned);
   if (e->own_stream) cudaStreamDestroy(e->stream);
   delete e;
+}
+
+int mdt_engine_exchange_handle(mdt_engine* e, void* handle64) {
+  MDT_CHECK(e && handle64, "NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  if (e->xch == nullptr) {
+    const size_t bytes = (size_t)e->L.total * sizeof(float) + 64 * sizeof(unsigned int);
+    MDT_CUDA(cudaMalloc(&e->xch, bytes));
+    MDT_CUDA(cudaMemset(e->xch, 0, bytes));
+    MDT_CUDA(cudaDeviceSynchronize());
+  }
+  cudaIpcMemHandle_t h;
+  MDT_CUDA(cudaIpcGetMemHandle(&h, e->xch));
+  memcpy(handle64, &h, sizeof(h));
+  return MDT_OK;
+}
+
+int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n) {
+  MDT_CHECK(e && handles64, "NULL argument");
+  MDT_CHECK(n == e->gsize && n >= 2 && n <= kMaxPeers, "set_peers: %d handles for a group of %d (2..%d ranks supported)", n, e->gsize, kMaxPeers);
+  MDT_CHECK(e->xch != nullptr, "call mdt_engine_exchange_handle first");
+  MDT_CHECK(e->cfg.gemm_mode != MDT_GEMM_FP32, "the peer-memory exchange is part of the tensor-core path");
+  PeerArgs pa{};
+  pa.n = n; pa.me = e->grank;
+  for (int r = 0; r < n; ++r) {
+    float* base = e->xch;
+    if (r != e->grank) {
+      cudaIpcMemHandle_t h;
+      memcpy(&h, static_cast<const char*>(handles64) + 64 * r, sizeof(h));
+      void* p = nullptr;
+      cudaError_t ce = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+      if (ce != cudaSuccess) {
+        cudaGetLastError();
+        return set_error(MDT_ERR_CUDA, "cudaIpcOpenMemHandle(rank %d): %s (no peer access?)", r, cudaGetErrorString(ce));
+      }
+      e->xch_opened[r] = p;
+      base = static_cast<float*>(p);
+    }
+    pa.g[r] = base;
+    pa.flags[r] = reinterpret_cast<unsigned int*>(base + e->L.total);
+  }
+  e->peers = pa;
+  e->p2p = true;
+  for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
+  e->graphs.clear();
+  return MDT_OK;
 }
 
 int mdt_engine_stream(mdt_engine* e, void** stream) {

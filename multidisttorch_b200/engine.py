@@ -6,6 +6,7 @@ as ONE object that owns four flat fp32 device buffers (params, grads, exp_avg,
 exp_avg_sq) and drives the hand-written sm_100a kernels through ctypes.  torch
 is used for device memory, streams and torch.distributed only."""
 import ctypes as C
+import os
 
 import numpy as np
 import torch
@@ -79,7 +80,31 @@ class VAEEngine:
             s = C.c_void_p()
             check(self.lib.mdt_engine_stream(h, C.byref(s)))
             self.stream = torch.cuda.ExternalStream(s.value, device=self.device)
+            self.p2p = False
+            if self.group_size > 1 and gemm_mode != "fp32" and os.environ.get("MDT_P2P_ALLREDUCE", "1") != "0":
+                self.p2p = self._connect_peers()
         self.set_adam(lr, betas, eps, 0)
+
+    def _connect_peers(self):
+        """Exchange the CUDA IPC handles of the group's gradient-exchange regions (include/mdt_b200.h,
+        mdt_engine_set_peers).  Every rank of the group must agree, so the outcome is all-reduced: if any rank
+        cannot map its peers (ranks on different nodes, no peer access) the whole group stays on NCCL."""
+        mine = (C.c_ubyte * 64)()
+        ok = self.lib.mdt_engine_exchange_handle(self._h, mine) == 0
+        handles = [None] * self.group_size
+        dist.all_gather_object(handles, bytes(mine) if ok else None, group=self.group)
+        ok = ok and all(h is not None for h in handles)
+        if ok:
+            blob = (C.c_ubyte * (64 * self.group_size)).from_buffer_copy(b"".join(handles))
+            ok = self.lib.mdt_engine_set_peers(self._h, blob, self.group_size) == 0
+        flag = torch.tensor([1 if ok else 0], device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
+        if int(flag.item()) == 0:
+            if ok:   # this rank could, a peer could not: recreate without the exchange is not needed, just never use it
+                raise RuntimeError("peer-memory exchange set up on this rank but not on all ranks of the group; "
+                                   "set MDT_P2P_ALLREDUCE=0")
+            return False
+        return True
 
     # ------------------------------------------------------------------ buffers
     def segment(self, buf, name):
