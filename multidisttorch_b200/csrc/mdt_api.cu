@@ -636,6 +636,16 @@ int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n) {
   return MDT_OK;
 }
 
+int mdt_engine_exchange_status(mdt_engine* e, int* enabled, int* timed_out) {
+  MDT_CHECK(e, "NULL engine");
+  StepState h;
+  MDT_CUDA(cudaMemcpyAsync(&h, e->st, sizeof(h), cudaMemcpyDeviceToHost, e->stream));
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  if (enabled) *enabled = e->p2p ? 1 : 0;
+  if (timed_out) *timed_out = (int)h.xch_error;
+  return MDT_OK;
+}
+
 int mdt_engine_stream(mdt_engine* e, void** stream) {
   MDT_CHECK(e && stream, "NULL argument");
   *stream = e->stream;

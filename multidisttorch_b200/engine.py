@@ -85,6 +85,12 @@ class VAEEngine:
                 self.p2p = self._connect_peers()
         self.set_adam(lr, betas, eps, 0)
 
+    def exchange_status(self):
+        """(enabled, timed_out) of the peer-memory gradient exchange (mdt_engine_exchange_status)."""
+        en, to = C.c_int(), C.c_int()
+        check(self.lib.mdt_engine_exchange_status(self._h, C.byref(en), C.byref(to)))
+        return bool(en.value), bool(to.value)
+
     def _connect_peers(self):
         """Exchange the CUDA IPC handles of the group's gradient-exchange regions (include/mdt_b200.h,
         mdt_engine_set_peers).  Every rank of the group must agree, so the outcome is all-reduced: if any rank
