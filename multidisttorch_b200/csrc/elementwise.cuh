@@ -482,7 +482,8 @@ __global__ void __launch_bounds__(256) adam_tile_kernel(AdamTileArgs a) {
 // stores the sum where DDP would leave it (the caller's gradient buffer) and applies the Adam update.  No NCCL launch,
 // no second pass over the gradient, and the transfer overlaps the update arithmetic element by element.  Before it
 // exits, the kernel's last block tells the peers it has finished reading and waits for the same from them: the exchange
-// buffer may be overwritten by the next step as soon as the kernel is complete.  All waits are bounded (~2 s).
+// buffer may be overwritten by the next step as soon as the kernel is complete.  All waits are bounded (~30 s; an
+// expired wait sets StepState.xch_error, reported by mdt_engine_exchange_status).
 constexpr int kMaxPeers = 8;
 struct PeerArgs {
   int n, me;
@@ -502,7 +503,8 @@ __device__ __forceinline__ unsigned int ld_acquire_sys(const unsigned int* p) {
 __device__ __forceinline__ bool wait_flag_ge(const unsigned int* p, unsigned int t) {
   const long long t0 = clock64();
   while ((int)(ld_acquire_sys(p) - t) < 0) {
-    if (clock64() - t0 > 4000000000LL) return false;
+    if (clock64() - t0 > 60000000000LL) return false;   // ~30 s: a peer that is merely slow (graph instantiation,
+                                                         // first-touch) must not be mistaken for a dead one
     __nanosleep(20);
   }
   return true;

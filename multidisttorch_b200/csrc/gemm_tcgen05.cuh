@@ -267,6 +267,25 @@ __device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, f
   }
 }
 
+// The same for the RPP = 1024 / BN tile rows of one epilogue pass (row_lo .. row_lo + RPP): thread = (row, group of 4
+// columns), one float4 read and 4 coalesced scalar stores.  Used when the passes of a tile are shared out among the
+// CTAs of a split-K cluster.
+template <int BN>
+__device__ __forceinline__ void tc05_store_transposed_rows(const float* T, int ldt, float* CT, int ldct, int m0, int n0,
+                                                           int M, int N, int et, int row_lo) {
+  constexpr int RPP = kTcEpiThreads / (BN / 4);
+  const int r = row_lo + et % RPP, c0 = (et / RPP) * 4;
+  const int m = m0 + r;
+  if (m >= M) return;
+  const float4 t = *reinterpret_cast<const float4*>(T + r * ldt + c0);
+  float* tp = CT + (size_t)(n0 + c0) * ldct + m;
+  const int cvalid = N - n0 - c0;
+  if (0 < cvalid) tp[0] = t.x;
+  if (1 < cvalid) tp[(size_t)ldct] = t.y;
+  if (2 < cvalid) tp[(size_t)2 * ldct] = t.z;
+  if (3 < cvalid) tp[(size_t)3 * ldct] = t.w;
+}
+
 // Global inputs of the element-wise epilogues (bias, ReLU mask / BCE target) that do not depend on this kernel's own
 // result: fetched into registers right after the dependency wait, so their L2 latency hides behind the main loop
 // instead of sitting at the head of the epilogue.
@@ -284,7 +303,8 @@ struct Tc05Pre {
 };
 
 template <int BN, int kEpi>
-__device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0, int M, int N, int et, Tc05Pre<BN>& pre) {
+__device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0, int M, int N, int et, Tc05Pre<BN>& pre,
+                                              int it_rank, int it_ns) {
   constexpr int F4R = BN / 4;
   constexpr int RPP = kTcEpiThreads / F4R;
   constexpr int ITERS = kTcBM / RPP;
@@ -304,7 +324,8 @@ __device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0,
     const float fill = (kEpi == EPI_RELU_MASK) ? 0.f : 0.5f;
 #pragma unroll
     for (int i = 0; i < ITERS; ++i)
-      pre.aux[i] = (i < rows_valid) ? __ldg(reinterpret_cast<const float4*>(sp + i * step)) : make_float4(fill, fill, fill, fill);
+      pre.aux[i] = (i < rows_valid && (i % it_ns) == it_rank) ? __ldg(reinterpret_cast<const float4*>(sp + i * step))
+                                                             : make_float4(fill, fill, fill, fill);
   }
   pre.adam_loaded = false;
   if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
@@ -329,7 +350,9 @@ __device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0,
 
 template <int BN, int kEpi>
 __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int ldt, int m0, int n0, int M, int N, int et,
-                                              float* red, const Tc05Pre<BN>& pre) {
+                                              float* red, const Tc05Pre<BN>& pre, int it_rank, int it_ns) {
+  // it_rank / it_ns: in a split-K cluster the tile's epilogue passes (RPP rows each) are shared out among the CTAs --
+  // this CTA holds the summed rows of, and runs, the passes i with i % it_ns == it_rank.  (0, 1) = the whole tile.
   const int lane = et & 31, ew = et >> 5;
   // Element-wise epilogues: 256 threads sweep the tile row by row in float4 units.  A thread always owns the same
   // four columns and rows rbase, rbase+RPP, ...; everything it needs (tile values from shared memory, mask / x
@@ -378,7 +401,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       const size_t cstep = (size_t)RPP * ldc;
 #pragma unroll
       for (int i = 0; i < ITERS; ++i)
-        if (i < rows_valid) *reinterpret_cast<float4*>(cp + i * cstep) = v[i];
+        if (i < rows_valid && (i % it_ns) == it_rank) *reinterpret_cast<float4*>(cp + i * cstep) = v[i];
     }
     float* CTp = CTp0;
     if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
@@ -392,7 +415,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
         float4 pp[CHK], mm[CHK], vv[CHK];
 #pragma unroll
         for (int c = 0; c < CHK; ++c) {
-          const bool ok = i0 + c < rows_valid;
+          const bool ok = i0 + c < rows_valid && ((i0 + c) % it_ns) == it_rank;
           const size_t o = off0 + (size_t)(i0 + c) * ostep;
           if (Tc05Pre<BN>::kAdamRegs && pre.adam_loaded) {
             pp[c] = pre.ap[Tc05Pre<BN>::kAdamRegs ? i0 + c : 0];
@@ -411,7 +434,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
           adam_elem_fast(pp[c].y, g.y, mm[c].y, vv[c].y, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
           adam_elem_fast(pp[c].z, g.z, mm[c].z, vv[c].z, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
           adam_elem_fast(pp[c].w, g.w, mm[c].w, vv[c].w, step_size, bc2_sqrt, omb1, b2, omb2, aeps);
-          if (i0 + c < rows_valid) {
+          if (i0 + c < rows_valid && ((i0 + c) % it_ns) == it_rank) {
             const size_t o = off0 + (size_t)(i0 + c) * ostep;
             *reinterpret_cast<float4*>(ep.adam_p + o) = pp[c];
             *reinterpret_cast<float4*>(ep.adam_m + o) = mm[c];
@@ -427,7 +450,11 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
       ptx::bar_sync_epi();
-      tc05_store_transposed<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et);
+      if (it_ns == 1) {
+        tc05_store_transposed<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et);
+      } else {
+        for (int i = it_rank; i < ITERS; i += it_ns) tc05_store_transposed_rows<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et, i * RPP);
+      }
     }
   } else if (kEpi == EPI_SIGMOID_BCE) {
     const int ldc = ep.ldc;
@@ -443,6 +470,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     const size_t cstep = (size_t)RPP * ldc;
 #pragma unroll
     for (int i = 0; i < ITERS; ++i) {
+      if ((i % it_ns) != it_rank) continue;        // CTA-uniform
       float4 r, g;
       r.x = fast_sigmoid(v[i].x + b.x); r.y = fast_sigmoid(v[i].y + b.y);
       r.z = fast_sigmoid(v[i].z + b.z); r.w = fast_sigmoid(v[i].w + b.w);
@@ -463,12 +491,21 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     part = warp_sum(part);
     if (lane == 0) red[ew] = part;
     ptx::bar_sync_epi();
-    tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
-    // per-tile partial only: the loss itself is not needed by any later kernel of the step, so the fixed-order sum
-    // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here
-    if (et == 0)
-      ep.bce_partials[blockIdx.y * gridDim.x + blockIdx.x] =
-          ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
+    if (it_ns == 1) {
+      tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
+    } else {
+      for (int i = it_rank; i < ITERS; i += it_ns)
+        tc05_store_transposed_rows<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et, i * RPP);
+    }
+    // per-CTA partial only: the loss itself is not needed by any later kernel of the step, so the fixed-order sum
+    // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here.
+    // A tile owns gridDim.z consecutive slots (one per split); without the cluster exchange only slot 0 is used.
+    if (et == 0) {
+      float* slot = ep.bce_partials + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z;
+      slot[it_ns == 1 ? 0 : it_rank] = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
+      if (it_ns == 1)
+        for (unsigned z = 1; z < gridDim.z; ++z) slot[z] = 0.f;
+    }
   } else if (kEpi == EPI_REPARAM || kEpi == EPI_REPARAM_BWD) {
     // These two GEMMs have a skinny output (2Z or Z features), so they run as the TRANSPOSED problem
     // C^T[feature, sample] = W[feature, K] . X[sample, K]^T: the batch becomes the tiled N dimension and the work
@@ -721,8 +758,12 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     const int q = warp & 3;                       // TMEM lane quadrant this warp may read
     const int chalf = (warp - 2) >> 2;            // which half of the accumulator columns this warp drains
     const int row = q * 32 + lane;                // accumulator row held by this thread
+    // split-K cluster: the row-wise epilogues are shared out among the cluster's CTAs by epilogue pass (see below)
+    constexpr bool kDist = kEpi != EPI_REPARAM && kEpi != EPI_REPARAM_BWD;
+    const bool dist = kDist && ep.cluster && gridDim.z > 1;
+    const int it_rank = dist ? (int)blockIdx.z : 0, it_ns = dist ? (int)gridDim.z : 1;
     Tc05Pre<BN> pre;
-    tc05_prefetch<BN, kEpi>(ep, m0, n0, M, N, et, pre);
+    tc05_prefetch<BN, kEpi>(ep, m0, n0, M, N, et, pre, it_rank, it_ns);
     // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), done first: it overlaps the latency of the first TMA loads
     if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
       // one warp per row, lanes stride the batch dimension (coalesced), fixed-shape shuffle tree: deterministic
@@ -819,28 +860,52 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     bool run_epilogue = true;
     if (gridDim.z > 1 && ep.cluster) {
       // Split-K inside a thread-block cluster: the splits of a tile are the CTAs of one cluster.  Every CTA has parked
-      // its partial tile at the same shared-memory offset; after a cluster barrier each CTA sums a 1/splits slice of
-      // the tile over all peers (fixed rank order: deterministic) through distributed shared memory and stores the
-      // slice into rank 0's tile; a second barrier, then rank 0 runs the epilogue.  No workspace round trip through
-      // L2, no fence + ticket chain.
+      // its partial tile at the same shared-memory offset.  After a cluster barrier the partials are summed through
+      // distributed shared memory in fixed rank order (deterministic); a second barrier keeps every CTA's tile alive
+      // until its peers have read it.  No workspace round trip through L2, no fence + ticket chain.
+      //  * row-wise epilogues: CTA r sums, into its own tile, the rows of the epilogue passes i = r, r + splits, ...
+      //    (a pass = the 256 float4 that the 256 epilogue threads handle together) and then runs the epilogue for just
+      //    those passes -- the reduction AND the epilogue (sigmoid/BCE math, stores) are spread over the cluster;
+      //  * reparameterisation epilogues (whole-tile structure): every CTA sums a 1/splits slice into rank 0's tile,
+      //    rank 0 runs the epilogue.
       constexpr int F4 = kTcBM * BN / 4;
+      constexpr int ITERS_E = F4 / kTcEpiThreads;
       const uint32_t ns = gridDim.z, rank = blockIdx.z;
-      const int chunk = (F4 + (int)ns - 1) / (int)ns;
-      const int f_hi = min(F4, ((int)rank + 1) * chunk);
       ptx::cluster_sync_all();
-      for (int f = (int)rank * chunk + et; f < f_hi; f += kTcEpiThreads) {
-        const uint32_t off = ptx::smem_u32(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4);
-        float4 v[8];
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
+      if (kDist) {
+        for (int i = (int)rank; i < ITERS_E; i += (int)ns) {
+          const int f = i * kTcEpiThreads + et;
+          float* const mine = T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4;
+          const uint32_t off = ptx::smem_u32(mine);
+          float4 v[8];
 #pragma unroll
-        for (uint32_t r = 0; r < 8; ++r)
-          v[r] = (r < ns) ? ptx::cluster_ld4(ptx::cluster_map(off, r)) : make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 acc = v[0];
+          for (uint32_t r = 0; r < 8; ++r)
+            v[r] = (r < ns) ? ptx::cluster_ld4(ptx::cluster_map(off, r)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 acc = v[0];
 #pragma unroll
-        for (int r = 1; r < 8; ++r) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
-        ptx::cluster_st4(ptx::cluster_map(off, 0), acc);
+          for (int r = 1; r < 8; ++r) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
+          *reinterpret_cast<float4*>(mine) = acc;    // only this thread reads this element again before the next barrier
+        }
+        // NB the peers read this CTA's ORIGINAL partial of the rows they own, never the rows it just overwrote
+      } else {
+        const int chunk = (F4 + (int)ns - 1) / (int)ns;
+        const int f_hi = min(F4, ((int)rank + 1) * chunk);
+        for (int f = (int)rank * chunk + et; f < f_hi; f += kTcEpiThreads) {
+          const uint32_t off = ptx::smem_u32(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4);
+          float4 v[8];
+#pragma unroll
+          for (uint32_t r = 0; r < 8; ++r)
+            v[r] = (r < ns) ? ptx::cluster_ld4(ptx::cluster_map(off, r)) : make_float4(0.f, 0.f, 0.f, 0.f);
+          float4 acc = v[0];
+#pragma unroll
+          for (int r = 1; r < 8; ++r) { acc.x += v[r].x; acc.y += v[r].y; acc.z += v[r].z; acc.w += v[r].w; }
+          ptx::cluster_st4(ptx::cluster_map(off, 0), acc);
+        }
       }
       ptx::cluster_sync_all();
-      run_epilogue = rank == 0;
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
+      run_epilogue = kDist || rank == 0;
     } else if (gridDim.z > 1) {
       // Deterministic split-K reduction: every split parks its partial tile in the workspace; the CTA that takes the
       // last ticket of the tile adds the partials in split order (independent of arrival order) and runs the epilogue.
@@ -898,7 +963,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       }
     }
     if (run_epilogue) {
-      tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre);
+      tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre, it_rank, it_ns);
       if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[11] = (long long)g; }
     }
     if (et == 0) TC_STAMP(7);
@@ -1131,6 +1196,14 @@ inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc0
   if (want > cap) want = cap;
   if (want > 8) want = 8;
   if (const char* v = getenv("MDT_MAX_SPLITS")) { const int c = atoi(v); if (want > c) want = c; }
+  // Prefer a split count whose clusters are all co-resident (a cluster lives inside one GPC: ~sm_count/8 SMs), as long
+  // as that costs at most one split level -- otherwise the launch falls back to the workspace exchange.
+  if (getenv("MDT_NO_CLUSTER_SPLITK") == nullptr && want >= 2) {
+    const int gpc = sm_count / 8;
+    int w = want;
+    while (w > 1 && tiles > 8 * (gpc / w)) --w;
+    if (w >= 2 && w + 1 >= want) want = w;
+  }
   if (want < 2) return 1;
   const int per = (total_kb + want - 1) / want;
   const int ns = (total_kb + per - 1) / per;                 // every split gets at least one k-block
@@ -1222,7 +1295,14 @@ inline int tc05_params_changed(Tc05Plan* p, cudaStream_t s) { return tc05_weight
 inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* na, const float** b, int* nb) {
   const int D = p->b.D;
   *a = p->bce_partials;
-  *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM);
+  // one slot per (fc4 tile, K-split): same split count as tc05_forward's launch of fc4
+  int ns = 1;
+  if (!getenv("MDT_NO_SPLITK")) {
+    Tc05Epi e{};
+    e.ws = p->ws; e.ws_counters = p->ws_counters;
+    ns = tc05_pick_splits(B, D, p->b.H, p->bn_fc4, p->b.sm_count, e, Tc05Plan::kWsFloats);
+  }
+  *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM) * ns;
   *b = p->kl_partials;
   *nb = p->simt_latent ? latent_grid(B, latent_pick_sc(B, p->b.sm_count)) : (B + p->bn_skinny - 1) / p->bn_skinny;
 }
