@@ -163,6 +163,10 @@ class EngineAdam:
 
     def __init__(self, owner, lr, betas, eps):
         self.owner = owner
+        from . import hpo
+        if hpo.overridden():           # per-trial hyper-parameters from MDT_HPO_* (SURVEY 8f-4), keyed by the trial's group
+            cfg = hpo.trial_config(hpo.group_index(owner.process_group), lr=lr, beta1=betas[0], beta2=betas[1], eps=eps)
+            lr, betas, eps = cfg.lr, cfg.betas, cfg.eps
         self.defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False)
         self.param_groups = [dict(self.defaults, params=list(owner.module.parameters()))]
         owner._adam_h = (lr, betas, eps)

@@ -175,6 +175,8 @@ def setup_ddp_groups(num_groups):
         f"Number of groups {num_groups} requested exceeds number of total processes {world_size} available")
 
     groups = [dist.new_group(ranks=ranks) for ranks in group_ranks(world_size, num_groups)]
+    from . import hpo
+    hpo.register_groups(groups)        # trial id of each group, for the per-trial hyper-parameter surface (hpo.py)
     for gid, grp in enumerate(groups):
         if dist.get_rank(grp) >= 0:
             print(f"Rank {world_rank} is in group {gid}")

@@ -262,13 +262,13 @@ class Trainer:
     """N-step driver mirroring ref:vae-hpo.py:69-74 for one rank (or, with
     several batches per step, one DDP group)."""
 
-    def __init__(self, params: dict, dims: Dims = Dims(), lr=1e-3):
+    def __init__(self, params: dict, dims: Dims = Dims(), lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
         self.dims = dims
         self.p = {k: np.array(v, dtype=F32, copy=True) for k, v in params.items()}
         self.m = {k: np.zeros_like(v) for k, v in self.p.items()}
         self.v = {k: np.zeros_like(v) for k, v in self.p.items()}
         self.t = 0
-        self.lr = lr
+        self.lr, self.b1, self.b2, self.eps = lr, b1, b2, eps
 
     def step(self, batches):
         """batches: list of (x, eps), one per rank of the group.  Returns the
@@ -281,7 +281,7 @@ class Trainer:
         g = grads[0] if len(grads) == 1 else ddp_average(grads)
         self.t += 1
         for k in self.p:
-            adam_update(self.p[k], g[k], self.m[k], self.v[k], self.t, lr=self.lr)
+            adam_update(self.p[k], g[k], self.m[k], self.v[k], self.t, lr=self.lr, b1=self.b1, b2=self.b2, eps=self.eps)
         return losses, g
 
 

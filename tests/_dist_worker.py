@@ -24,6 +24,9 @@ def main():
     res = {"size": size, "rank": rank, "stdout": buf.getvalue(),
            "membership": [int(dist.get_rank(g)) for g in groups],
            "get_comm": list(get_comm_size_and_rank())}
+    from multidisttorch_b200 import hpo
+    res["hpo_group_index"] = [hpo.group_index(g) for g in groups]
+    res["hpo_my_group"] = hpo.my_group_index(groups)
     mine = [g for g in groups if dist.get_rank(g) >= 0]
     if mode == "gather" and mine:
         # what ref:example-subgroup.py:25-33 does, on the group this rank belongs to

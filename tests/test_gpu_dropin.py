@@ -70,3 +70,34 @@ def test_dropin_training_loop_matches_torch_cuda():
         assert abs(a - b) <= 2e-5 * abs(b), (got, want)
     for (n, p), (_, q) in zip(wrapped.module.named_parameters(), plain.named_parameters()):
         assert rel_l2(p.detach().cpu().numpy(), q.detach().cpu().numpy()) < 2e-4, n
+
+
+def test_dropin_adam_takes_per_trial_hyperparameters_from_env(monkeypatch):
+    """with MDT_HPO_* set, the optimizer that stands in for `optim.Adam(model.parameters(), lr=1e-3)`
+    trains with the trial's own lr / betas, and the result equals plain torch trained with those values."""
+    from multidisttorch_b200 import dropin
+    torch.backends.cuda.matmul.allow_tf32 = False
+    monkeypatch.setenv("MDT_HPO_LR", "3e-4")
+    monkeypatch.setenv("MDT_HPO_BETA1", "0.8")
+    xs = [torch.rand(64, 1, 28, 28, generator=torch.Generator().manual_seed(100 + i)).cuda() for i in range(5)]
+    p0 = O.init_params(22)
+    plain = TP.VAEPort().cuda()
+    TP.load_segments(plain, p0)
+    torch.manual_seed(78)
+    want = loop(plain, torch.optim.Adam(plain.parameters(), lr=3e-4, betas=(0.8, 0.999)), xs)
+    assert dropin.install() or dropin._ORIG
+    try:
+        m = TP.VAEPort().cuda()
+        TP.load_segments(m, p0)
+        torch.manual_seed(78)
+        wrapped = torch.nn.parallel.DistributedDataParallel(m, process_group=None)
+        opt = torch.optim.Adam(wrapped.parameters(), lr=1e-3)          # what the script asks for
+        assert isinstance(opt, dropin.EngineAdam)
+        assert opt.defaults["lr"] == 3e-4 and opt.defaults["betas"] == (0.8, 0.999)
+        got = loop(wrapped, opt, xs)
+    finally:
+        dropin.uninstall()
+    for a, b in zip(got, want):
+        assert abs(a - b) <= 2e-5 * abs(b), (got, want)
+    for (n, p), (_, q) in zip(wrapped.module.named_parameters(), plain.named_parameters()):
+        assert rel_l2(p.detach().cpu().numpy(), q.detach().cpu().numpy()) < 2e-4, n
