@@ -81,11 +81,17 @@ class VAEEngine:
             check(self.lib.mdt_engine_stream(h, C.byref(s)))
             self.stream = torch.cuda.ExternalStream(s.value, device=self.device)
             self.p2p = False
-            # one-shot exchange (every rank reads all peers): measured faster than NCCL for groups of 2 and 4
-            # (4x2: 12.8 vs 11.8 M samples/s, 2x4: 11.1 vs 10.9), slower for 8 (1x8: 7.7 vs 9.1) -> NCCL there
+            # One-shot exchange (every rank reads all its peers' gradients).  Measured against NCCL in the same build:
+            #   2 ranks: 3.19 vs 3.03 M samples/s at H=400 (2.6 MB), 2.27 vs 1.94 M at H=4096 (26.7 MB)  -> always
+            #   4 ranks: 11.1 vs 10.9 M at H=400 (7.8 MB read per rank), 1.66 vs 1.83 M at H=4096 (80 MB) -> small only
+            #   8 ranks: 7.7 vs 9.1 M at H=400                                                            -> never
+            mode = os.environ.get("MDT_P2P_ALLREDUCE", "1")
             max_ranks = int(os.environ.get("MDT_P2P_MAX_RANKS", "4"))
-            if (1 < self.group_size <= max_ranks and gemm_mode != "fp32"
-                    and os.environ.get("MDT_P2P_ALLREDUCE", "1") != "0"):
+            peer_bytes = (self.group_size - 1) * self.total * 4
+            want = self.group_size == 2 or (self.group_size <= max_ranks and peer_bytes <= (16 << 20))
+            if mode == "force":
+                want = self.group_size <= 8
+            if self.group_size > 1 and gemm_mode != "fp32" and mode != "0" and want:
                 self.p2p = self._connect_peers()
         self.set_adam(lr, betas, eps, 0)
 
