@@ -150,6 +150,15 @@ int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int 
 int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
                         float* loss_host);
 
+/* The same step in two halves, so that the host can keep the next step's input in flight while it waits for this
+ * step's loss (what a prefetching DataLoader + a deferred loss.item() do for ref:vae-hpo.py:64-73):
+ * mdt_train_step_host_submit enqueues the step and returns a ticket; mdt_train_step_host_wait returns that step's
+ * loss.  x_host (and eps_host) must stay untouched until the matching wait has returned: when they are pinned the
+ * device reads them in place.  Up to 63 steps may be in flight; tickets may be waited on in any order. */
+int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
+                               uint32_t* ticket);
+int mdt_train_step_host_wait(mdt_engine* e, uint32_t ticket, float* loss_host);
+
 /* Forward + loss only (the eval loop), ref:vae-hpo.py:101-105. */
 int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out,
                   float* recon);

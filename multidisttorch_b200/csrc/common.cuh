@@ -85,7 +85,7 @@ struct StepState {
   unsigned int ticket_adam;
   unsigned int ticket_loss;
   unsigned int host_seq;             // training steps published to host_mailbox so far
-  unsigned long long* host_mailbox;  // pinned, device-mapped host word: (host_seq << 32) | bits(loss) of the last step
+  unsigned long long* host_mailbox;  // pinned, device-mapped ring of 64 words: slot seq % 64 = (seq << 32) | bits(loss)
   unsigned int xch_seq;              // peer-memory gradient exchanges completed (never reset: the flags are monotonic)
   unsigned int xch_error;            // set when a bounded wait on a peer's flag expired
 };
@@ -99,7 +99,9 @@ __device__ __forceinline__ void publish_loss(StepState* st, float loss) {
   st->host_seq = seq;
   // one posted 8-byte store, nothing ordered behind it: no system-scope fence (it would hold the step's last CTA for
   // a PCIe round trip)
-  *reinterpret_cast<volatile unsigned long long*>(mb) = ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(loss);
+  // the mailbox is a ring of 64 words indexed by the sequence number, so the host may have several steps in flight
+  *reinterpret_cast<volatile unsigned long long*>(mb + (seq & 63u)) =
+      ((unsigned long long)seq << 32) | (unsigned long long)__float_as_uint(loss);
 }
 
 // ---------------------------------------------------------------- programmatic dependent launch

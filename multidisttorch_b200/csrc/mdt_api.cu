@@ -113,7 +113,9 @@ struct mdt_engine {
   void* xch_opened[kMaxPeers] = {};     // peers' regions mapped with cudaIpcOpenMemHandle
   PeerArgs peers{};
   bool p2p = false;
-  volatile unsigned long long* mailbox = nullptr;   // loss_pinned + 64 bytes: see publish_loss()
+  volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
+  float sync_losses[64] = {};
+  unsigned int sync_seq = 0;                       // losses of submitted steps on configurations without the mailbox
   unsigned int pub_expected = 0;                    // training steps enqueued so far that publish to the mailbox
   int last_B = 0;  // batch of the activations currently held
 
@@ -550,11 +552,11 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
       r = set_error(MDT_ERR_CUDA, "could not create the communication stream/events");
   }
   if (r == MDT_OK) {
-    cudaError_t ce = cudaMallocHost(&e->loss_pinned, 256);
+    cudaError_t ce = cudaMallocHost(&e->loss_pinned, 1024);
     if (ce != cudaSuccess) r = set_error(MDT_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(ce));
   }
   if (r == MDT_OK && e->cfg.gemm_mode != MDT_GEMM_FP32) {
-    memset(e->loss_pinned, 0, 256);
+    memset(e->loss_pinned, 0, 1024);
     e->mailbox = reinterpret_cast<volatile unsigned long long*>(e->loss_pinned + 16);
     void* dptr = nullptr;
     if (cudaHostGetDevicePointer(&dptr, e->loss_pinned + 16, 0) == cudaSuccess && dptr != nullptr) {
@@ -790,15 +792,16 @@ int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int 
   return MDT_OK;
 }
 
-int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
-                        float* loss_host) {
+int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
+                               uint32_t* ticket) {
   MDT_TRY(check_batch(e, batch));
   MDT_CHECK(x_host || batch == 0, "x_host is NULL");
+  MDT_CHECK(ticket, "ticket is NULL");
   const float* x = x_host;
   const float* eps = eps_host_or_null;
   if (e->tc && e->mailbox != nullptr && batch > 0 && !getenv("MDT_NO_ZEROCOPY")) {
     // Tensor-core path.  Pinned x is read by the step's prologue kernel straight from host memory (no separate H2D
-    // copy in front of the graph), and the loss comes back through the mailbox the step's last thread writes.
+    // copy in front of the graph), and the loss comes back through the mailbox ring the step's last thread writes.
     cudaPointerAttributes at{};
     const bool mapped = cudaPointerGetAttributes(&at, x_host) == cudaSuccess && at.type == cudaMemoryTypeHost &&
                         at.devicePointer != nullptr;
@@ -811,35 +814,58 @@ int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const flo
     if (rc == MDT_OK) rc = train_step_device(e, x, batch, eps);
     e->tc->x_src = nullptr;
     MDT_TRY(rc);
-    const unsigned int expected = e->pub_expected;
-    unsigned long long v = 0;
-    for (unsigned int spins = 0;; ++spins) {
-      v = *e->mailbox;
-      if ((unsigned int)(v >> 32) == expected) break;
-      if ((spins & 255u) == 255u) {
-        const cudaError_t q = cudaStreamQuery(e->stream);
-        if (q == cudaSuccess) {            // stream idle: whatever the mailbox holds now is this step's word
-          v = *e->mailbox;
-          e->pub_expected = (unsigned int)(v >> 32);
-          break;
-        }
-        if (q != cudaErrorNotReady) return set_error(MDT_ERR_CUDA, "training step failed: %s", cudaGetErrorString(q));
-      }
-    }
-    if (loss_host) {
-      const unsigned int bits = (unsigned int)(v & 0xffffffffull);
-      memcpy(loss_host, &bits, sizeof(float));
-    }
+    *ticket = e->pub_expected;
     return MDT_OK;
   }
-  // host buffers never alias the stage, so both copies are issued (H2D, async when pinned)
+  // no mailbox (fp32 FFMA path, empty batch, MDT_NO_ZEROCOPY): the step runs to completion here
   MDT_TRY(stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice));
   if (batch == 0) MDT_CUDA(cudaMemsetAsync(e->loss_dev, 0, sizeof(float), e->stream));
   MDT_TRY(train_step_device(e, x, batch, eps));
   MDT_CUDA(cudaMemcpyAsync(e->loss_pinned, e->loss_dev, sizeof(float), cudaMemcpyDeviceToHost, e->stream));
   MDT_CUDA(cudaStreamSynchronize(e->stream));
-  if (loss_host) *loss_host = *e->loss_pinned;
+  e->sync_seq = (e->sync_seq + 1u) | 0x80000000u;      // tickets of this kind have the top bit set
+  e->sync_losses[e->sync_seq & 63u] = *e->loss_pinned;
+  *ticket = e->sync_seq;
   return MDT_OK;
+}
+
+int mdt_train_step_host_wait(mdt_engine* e, uint32_t ticket, float* loss_host) {
+  MDT_CHECK(e, "NULL engine");
+  if (ticket & 0x80000000u) {
+    if (loss_host) *loss_host = e->sync_losses[ticket & 63u];
+    return MDT_OK;
+  }
+  MDT_CHECK(e->mailbox != nullptr, "no step is in flight on this engine");
+  MDT_CHECK(e->pub_expected - ticket < 64u, "ticket %u is more than 63 steps old (latest %u): its mailbox slot has been reused",
+            ticket, e->pub_expected);
+  volatile unsigned long long* slot = e->mailbox + (ticket & 63u);
+  unsigned long long v = 0;
+  for (unsigned int spins = 0;; ++spins) {
+    v = *slot;
+    if ((unsigned int)(v >> 32) == ticket) break;
+    if ((spins & 255u) == 255u) {
+      const cudaError_t q = cudaStreamQuery(e->stream);
+      if (q == cudaSuccess) {              // stream idle: the word must be there by now
+        v = *slot;
+        if ((unsigned int)(v >> 32) == ticket) break;
+        return set_error(MDT_ERR_STATE, "step %u finished without publishing its loss (mailbox holds %u)", ticket,
+                         (unsigned int)(v >> 32));
+      }
+      if (q != cudaErrorNotReady) return set_error(MDT_ERR_CUDA, "training step failed: %s", cudaGetErrorString(q));
+    }
+  }
+  if (loss_host) {
+    const unsigned int bits = (unsigned int)(v & 0xffffffffull);
+    memcpy(loss_host, &bits, sizeof(float));
+  }
+  return MDT_OK;
+}
+
+int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,
+                        float* loss_host) {
+  uint32_t ticket = 0;
+  MDT_TRY(mdt_train_step_host_submit(e, x_host, batch, eps_host_or_null, &ticket));
+  return mdt_train_step_host_wait(e, ticket, loss_host);
 }
 
 int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out, float* recon) {

@@ -227,6 +227,23 @@ class VAEEngine:
         check(self.lib.mdt_train_step_host(self._h, _ptr(x), x.shape[0], _ptr(eps_host), C.byref(out)))
         return float(out.value)
 
+    def submit_host(self, x_host, eps_host=None):
+        """First half of train_step_host: enqueue the step, return a ticket.  ``x_host`` must stay untouched until
+        ``wait_host(ticket)`` has returned (pinned memory is read in place by the device)."""
+        x = self._x2d(x_host)
+        t = C.c_uint32()
+        check(self.lib.mdt_train_step_host_submit(self._h, _ptr(x), x.shape[0], _ptr(eps_host), C.byref(t)))
+        self._inflight = getattr(self, "_inflight", {})
+        self._inflight[t.value] = (x, eps_host)          # keep the buffers alive while the device may read them
+        return t.value
+
+    def wait_host(self, ticket):
+        """Second half: the loss of the step ``submit_host`` returned ``ticket`` for."""
+        out = C.c_float()
+        check(self.lib.mdt_train_step_host_wait(self._h, C.c_uint32(ticket), C.byref(out)))
+        getattr(self, "_inflight", {}).pop(ticket, None)
+        return float(out.value)
+
     def forward(self, x, eps=None):
         x = self._x2d(x)
         B = x.shape[0]

@@ -427,3 +427,28 @@ def test_no_stray_writes_into_layout_padding(E, mode, B):
     for name, buf in (("params", eng.params), ("grads", eng.grads), ("exp_avg", eng.exp_avg), ("exp_avg_sq", eng.exp_avg_sq)):
         assert not buf.cpu().numpy()[gap].any(), name
     eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_submit_wait_pipelined_host_steps_equal_synchronous_ones(E, mode):
+    """mdt_train_step_host_submit / _wait with several steps in flight gives, step for step, the losses and the final
+    parameters of the synchronous mdt_train_step_host loop (tickets waited out of order too)."""
+    B, n = 48, 9
+    xs = [torch.from_numpy(O.make_batch(batch_seed(t), B)[0]).pin_memory() for t in range(n)]
+    a = make_engine(E, mode, B)
+    a.set_rng(99, 0)
+    want = [a.train_step_host(x) for x in xs]
+    b = make_engine(E, mode, B)
+    b.set_rng(99, 0)
+    tickets = [b.submit_host(x) for x in xs[:4]]                 # four in flight
+    got = {}
+    got[1] = b.wait_host(tickets[1])                             # out of order
+    got[0] = b.wait_host(tickets[0])
+    for t in range(4, n):
+        tickets.append(b.submit_host(xs[t]))
+        got[t - 2] = b.wait_host(tickets[t - 2])
+    for t in range(n - 2, n):
+        got[t] = b.wait_host(tickets[t])
+    assert [got[t] for t in range(n)] == want
+    assert torch.equal(a.params, b.params)
+    a.close(); b.close()
