@@ -294,8 +294,9 @@ def run_own(args):
     barrier()
     e2e = {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * D * 4, "d2h_bytes_per_step": 4,
            "ms_per_step": e2e_s * 1e3 / K, "last_loss": loss,
-           "how": "mdt_train_step_host_submit / _wait, one step in flight ahead; x read from pinned host memory by "
-                  "the step's first kernel, loss returned through the device-written mailbox",
+           "how": "mdt_train_step_host_submit / _wait, one step in flight ahead; each step's x goes from pinned host "
+                  "memory to the device inside the timed region (DMA on a copy stream behind the step in flight), each "
+                  "step's loss is read by the host from the device-written mailbox",
            "sync_value": world * B * K / sync_s, "sync_ms_per_step": sync_s * 1e3 / K}
     # ---- per-kernel device time (un-graphed, event after each kernel) -> roofline of the dominant kernel
     roofline = None

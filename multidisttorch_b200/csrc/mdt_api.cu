@@ -114,6 +114,14 @@ struct mdt_engine {
   PeerArgs peers{};
   bool p2p = false;
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
+  // host-buffer steps submitted while the GPU is still busy: x is DMA'd into a small ring of device buffers on a copy
+  // stream (overlapping the step in flight) instead of being read over PCIe by the step's own first kernel
+  static constexpr int kPreSlots = 4;
+  cudaStream_t copy_stream = nullptr;
+  float* x_pre[kPreSlots] = {};
+  cudaEvent_t ev_copied[kPreSlots] = {}, ev_used[kPreSlots] = {};
+  bool pre_used[kPreSlots] = {};
+  unsigned int pre_next = 0;
   float sync_losses[64] = {};
   unsigned int sync_seq = 0;                       // losses of submitted steps on configurations without the mailbox
   unsigned int pub_expected = 0;                    // training steps enqueued so far that publish to the mailbox
@@ -584,6 +592,12 @@ void mdt_engine_destroy(mdt_engine* e) {
   if (e->comm_stream) { cudaStreamSynchronize(e->comm_stream); cudaStreamDestroy(e->comm_stream); }
   for (auto& ev : e->ev_bucket) if (ev) cudaEventDestroy(ev);
   if (e->ev_comm_done) cudaEventDestroy(e->ev_comm_done);
+  if (e->copy_stream) { cudaStreamSynchronize(e->copy_stream); cudaStreamDestroy(e->copy_stream); }
+  for (int k = 0; k < mdt_engine::kPreSlots; ++k) {
+    if (e->x_pre[k]) cudaFree(e->x_pre[k]);
+    if (e->ev_copied[k]) cudaEventDestroy(e->ev_copied[k]);
+    if (e->ev_used[k]) cudaEventDestroy(e->ev_used[k]);
+  }
   for (void* p : e->xch_opened) if (p) cudaIpcCloseMemHandle(p);
   if (e->xch) cudaFree(e->xch);
   if (e->slab) cudaFree(e->slab);
@@ -806,14 +820,39 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
     const bool mapped = cudaPointerGetAttributes(&at, x_host) == cudaSuccess && at.type == cudaMemoryTypeHost &&
                         at.devicePointer != nullptr;
     cudaGetLastError();
+    int slot = -1;
     if (mapped) {
       e->tc->x_src = static_cast<const float*>(at.devicePointer);
       x = e->x_stage;                      // stage_inputs then only handles eps
+      // Is the step submitted last still running?  Then there is compute to hide a DMA behind.
+      const unsigned int last = e->pub_expected;
+      const bool busy = last != 0 && (unsigned int)(e->mailbox[last & 63u] >> 32) != last;
+      if (busy && !getenv("MDT_NO_H2D_PREFETCH")) {
+        if (e->copy_stream == nullptr) {
+          MDT_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+          for (int k = 0; k < mdt_engine::kPreSlots; ++k) {
+            MDT_CUDA(cudaMalloc(&e->x_pre[k], (size_t)e->Bmax * e->D * sizeof(float)));
+            MDT_CUDA(cudaEventCreateWithFlags(&e->ev_copied[k], cudaEventDisableTiming));
+            MDT_CUDA(cudaEventCreateWithFlags(&e->ev_used[k], cudaEventDisableTiming));
+          }
+        }
+        slot = (int)(e->pre_next++ % mdt_engine::kPreSlots);
+        if (e->pre_used[slot]) MDT_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_used[slot], 0));
+        MDT_CUDA(cudaMemcpyAsync(e->x_pre[slot], x_host, (size_t)batch * e->D * sizeof(float), cudaMemcpyHostToDevice,
+                                 e->copy_stream));
+        MDT_CUDA(cudaEventRecord(e->ev_copied[slot], e->copy_stream));
+        MDT_CUDA(cudaStreamWaitEvent(e->stream, e->ev_copied[slot], 0));
+        e->tc->x_src = e->x_pre[slot];
+      }
     }
     int rc = stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice);
     if (rc == MDT_OK) rc = train_step_device(e, x, batch, eps);
     e->tc->x_src = nullptr;
     MDT_TRY(rc);
+    if (slot >= 0) {                       // the slot is free again once this step (its prologue, really) has run
+      MDT_CUDA(cudaEventRecord(e->ev_used[slot], e->stream));
+      e->pre_used[slot] = true;
+    }
     *ticket = e->pub_expected;
     return MDT_OK;
   }
