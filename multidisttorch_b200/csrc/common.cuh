@@ -95,7 +95,8 @@ struct StepState {
 __device__ __forceinline__ void publish_loss(StepState* st, float loss) {
   unsigned long long* mb = st->host_mailbox;
   if (mb == nullptr) return;
-  const unsigned int seq = st->host_seq + 1u;
+  const unsigned int seq = (st->host_seq + 1u) & 0x7fffffffu;   // 31 bits: the host keeps the top bit for tickets of
+                                                                  // steps that did not go through the mailbox
   st->host_seq = seq;
   // one posted 8-byte store, nothing ordered behind it: no system-scope fence (it would hold the step's last CTA for
   // a PCIe round trip)

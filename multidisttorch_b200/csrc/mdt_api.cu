@@ -463,7 +463,8 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   e->last_B = B;
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
-  if (e->tc) ++e->pub_expected;   // every tensor-core training step publishes (sequence, loss) once: publish_loss()
+  if (e->tc) e->pub_expected = (e->pub_expected + 1u) & 0x7fffffffu;   // every tensor-core training step publishes
+                                                                         // (sequence, loss) once: publish_loss()
   if (e->gsize == 1 && e->tc && !getenv("MDT_NO_FUSED_ADAM")) {
     // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
     return run_cached(e, /*kind=*/7, B, eps != nullptr, [&]() -> int {
@@ -875,7 +876,7 @@ int mdt_train_step_host_wait(mdt_engine* e, uint32_t ticket, float* loss_host) {
     return MDT_OK;
   }
   MDT_CHECK(e->mailbox != nullptr, "no step is in flight on this engine");
-  MDT_CHECK(e->pub_expected - ticket < 64u, "ticket %u is more than 63 steps old (latest %u): its mailbox slot has been reused",
+  MDT_CHECK(((e->pub_expected - ticket) & 0x7fffffffu) < 64u, "ticket %u is more than 63 steps old (latest %u): its mailbox slot has been reused",
             ticket, e->pub_expected);
   volatile unsigned long long* slot = e->mailbox + (ticket & 63u);
   unsigned long long v = 0;
