@@ -143,6 +143,10 @@ int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or
  * mdt_train_step on each engine; it exists to take the per-call host overhead out of the HPO driver's loop.
  * Replaces: nothing in the reference (it runs one trial per rank, ref:vae-hpo.py:200-202). */
 int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch);
+/* (new, no reference counterpart) Size this engine's kernels -- K-split counts, CTAs per launch -- for 1/n_sharing of
+ * the GPU's SMs, for callers that run several trials on one GPU themselves (own threads / streams).  Default 1.
+ * mdt_train_step_many applies max(n_trials, this value) for the duration of its call. */
+int mdt_engine_set_sm_share(mdt_engine* e, int n_sharing);
 
 /* Same, with HOST buffers: copies x (and eps) host->device, runs the step, copies
  * the loss back and synchronises (the `loss.item()` of ref:vae-hpo.py:73).

@@ -41,6 +41,7 @@ _PROTOS = {
     "mdt_train_step": (C.c_int, [_P, _P, C.c_int, _P, _P]),
     "mdt_train_step_many": (C.c_int, [C.POINTER(_P), C.POINTER(_P), C.c_int, C.c_int]),
     "mdt_train_step_host": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_float)]),
+    "mdt_engine_set_sm_share": (C.c_int, [_P, C.c_int]),
     "mdt_train_step_host_submit": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_uint32)]),
     "mdt_train_step_host_wait": (C.c_int, [_P, C.c_uint32, C.POINTER(C.c_float)]),
     "mdt_eval_step": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),

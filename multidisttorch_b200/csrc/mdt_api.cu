@@ -113,6 +113,7 @@ struct mdt_engine {
   void* xch_opened[kMaxPeers] = {};     // peers' regions mapped with cudaIpcOpenMemHandle
   PeerArgs peers{};
   bool p2p = false;
+  int sm_share_pending = 1;
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
   // host-buffer steps submitted while the GPU is still busy: x is DMA'd into a small ring of device buffers on a copy
   // stream (overlapping the step in flight) instead of being read over PCIe by the step's own first kernel
@@ -463,24 +464,25 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   e->last_B = B;
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
+  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1);   // graphs are per (eps given, SM share)
   if (e->tc) e->pub_expected = (e->pub_expected + 1u) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
   if (e->gsize == 1 && e->tc && !getenv("MDT_NO_FUSED_ADAM")) {
     // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
-    return run_cached(e, /*kind=*/7, B, eps != nullptr, [&]() -> int {
+    return run_cached(e, /*kind=*/7, B, fl, [&]() -> int {
       MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
       return tc05_backward_fused_adam(e->tc, e->stream, B);
     });
   }
   if (e->gsize == 1) {
-    return run_cached(e, /*kind=*/0, B, eps != nullptr, [&]() -> int {
+    return run_cached(e, /*kind=*/0, B, fl, [&]() -> int {
       MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
       return enqueue_adam(e, gscale, true);
     });
   }
   if (e->p2p && e->tc && !e->prof_on) {
     // group on one node with peer access: gradients are exchanged through NVLink peer memory inside the Adam kernel
-    return run_cached(e, /*kind=*/8, B, eps != nullptr, [&]() -> int {
+    return run_cached(e, /*kind=*/8, B, fl, [&]() -> int {
       e->tc->grads_override = e->xch;
       e->defer_buckets = true;                    // no NCCL buckets in this step
       int rc = enqueue_fwd_loss_bwd(e, x, B, eps);
@@ -491,12 +493,12 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
     });
   }
   if (getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0') {   // NCCL outside the graphs
-    MDT_TRY(run_cached(e, /*kind=*/1, B, eps != nullptr, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
+    MDT_TRY(run_cached(e, /*kind=*/1, B, fl, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
     MDT_TRY(finish_allreduce(e));
-    return run_cached(e, /*kind=*/2, B, 0, [&]() -> int { return enqueue_adam(e, gscale, true); });
+    return run_cached(e, /*kind=*/2, B, fl & ~1, [&]() -> int { return enqueue_adam(e, gscale, true); });
   }
   // one graph for the whole step, the group's NCCL all-reduces included (bucket 0 overlaps the rest of backward)
-  return run_cached(e, /*kind=*/6, B, eps != nullptr, [&]() -> int {
+  return run_cached(e, /*kind=*/6, B, fl, [&]() -> int {
     MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
     MDT_TRY(finish_allreduce(e));
     return enqueue_adam(e, gscale, true);
@@ -663,6 +665,14 @@ int mdt_engine_exchange_status(mdt_engine* e, int* enabled, int* timed_out) {
   return MDT_OK;
 }
 
+int mdt_engine_set_sm_share(mdt_engine* e, int n_sharing) {
+  MDT_CHECK(e, "NULL engine");
+  MDT_CHECK(n_sharing >= 1 && n_sharing <= 16, "n_sharing %d outside [1, 16]", n_sharing);
+  if (e->tc) e->tc->sm_share = n_sharing;
+  e->sm_share_pending = n_sharing;      // applied when the tensor-core plan is (re)built by mdt_engine_bind_buffers
+  return MDT_OK;
+}
+
 int mdt_engine_stream(mdt_engine* e, void** stream) {
   MDT_CHECK(e && stream, "NULL argument");
   *stream = e->stream;
@@ -689,6 +699,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
     b.bucket_ready = (e->gsize > 1) ? bucket_ready_cb : nullptr;
     b.split3 = (e->cfg.gemm_mode == MDT_GEMM_TF32X3);
     MDT_TRY(tc05_create(&b, e->stream, &e->tc));
+    e->tc->sm_share = e->sm_share_pending;
   }
   e->bound = true;
   return MDT_OK;
@@ -803,8 +814,18 @@ int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or
 
 int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch) {
   MDT_CHECK(engines && xs && n_trials >= 0, "bad argument");
-  for (int i = 0; i < n_trials; ++i) MDT_TRY(mdt_train_step(engines[i], xs[i], batch, nullptr, nullptr));
-  return MDT_OK;
+  // the trials share the GPU: each one's kernels are sized for 1/n of the SMs (Tc05Plan::sm_share)
+  const int share = n_trials < 1 ? 1 : (n_trials > 16 ? 16 : n_trials);
+  int rc = MDT_OK;
+  for (int i = 0; i < n_trials && rc == MDT_OK; ++i) {
+    mdt_engine* e = engines[i];
+    MDT_CHECK(e != nullptr, "engines[%d] is NULL", i);
+    const int keep = e->tc ? e->tc->sm_share : 1;
+    if (e->tc && share > keep) e->tc->sm_share = share;
+    rc = mdt_train_step(e, xs[i], batch, nullptr, nullptr);
+    if (e->tc) e->tc->sm_share = keep;
+  }
+  return rc;
 }
 
 int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, const float* eps_host_or_null,

@@ -95,6 +95,10 @@ class VAEEngine:
                 self.p2p = self._connect_peers()
         self.set_adam(lr, betas, eps, 0)
 
+    def set_sm_share(self, n_sharing):
+        """Size this engine's kernels for 1/n_sharing of the SMs (several trials on one GPU; mdt_engine_set_sm_share)."""
+        check(self.lib.mdt_engine_set_sm_share(self._h, int(n_sharing)))
+
     def exchange_status(self):
         """(enabled, timed_out) of the peer-memory gradient exchange (mdt_engine_exchange_status)."""
         en, to = C.c_int(), C.c_int()

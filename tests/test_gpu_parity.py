@@ -340,7 +340,8 @@ def test_hidden_4096_one_step_vs_oracle(E, mode):
 
 def test_many_trials_on_one_gpu_equal_sequential_trials(E):
     """T independent trials stepped concurrently (own engine/stream/graph each) end bit-identical to the
-    same trials stepped one after another."""
+    same trials stepped one after another.  train_step_many sizes every trial's kernels for 1/T of the SMs, so the
+    sequential twins get the same share (set_sm_share) -- same K-split counts, same summation order."""
     B, T = 128, 3
     xs = [dev(O.make_batch(50 + t, B)[0]) for t in range(T)]
     seq, con = [], []
@@ -350,6 +351,7 @@ def test_many_trials_on_one_gpu_equal_sequential_trials(E):
             e.load_segments(O.init_params(300 + t))
             e.set_rng(300 + t, 0)
             group.append(e)
+        seq[-1].set_sm_share(T)
     for step in range(4):
         for t in range(T):
             seq[t].train_step(xs[(t + step) % T], None, want_loss=False)
