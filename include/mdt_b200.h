@@ -193,6 +193,8 @@ int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n);
 /* *enabled: 1 once mdt_engine_set_peers succeeded; *timed_out: 1 if a bounded wait on a peer's flag ever expired (a
  * peer died or never launched its step: the gradients of that step are then not trustworthy).  Synchronises. */
 int mdt_engine_exchange_status(mdt_engine* e, int* enabled, int* timed_out);
+/* Back to the NCCL exchange (e.g. when another rank of the group could not map its peers: all ranks must agree). */
+int mdt_engine_disable_peers(mdt_engine* e);
 
 /* Measurement aid: run `iters` un-graphed training steps on x with a CUDA event after
  * every kernel and write "label avg_ms\n" lines (one per kernel of the step, in launch

@@ -50,6 +50,7 @@ _PROTOS = {
     "mdt_engine_launch_count": (C.c_int, [_P, C.POINTER(C.c_int64)]),
     "mdt_engine_exchange_handle": (C.c_int, [_P, _P]),
     "mdt_engine_set_peers": (C.c_int, [_P, _P, C.c_int]),
+    "mdt_engine_disable_peers": (C.c_int, [_P]),
     "mdt_engine_exchange_status": (C.c_int, [_P, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     "mdt_engine_profile_step": (C.c_int, [_P, _P, C.c_int, C.c_int, C.c_char_p, C.c_size_t]),
     "mdt_adam_flat": (C.c_int, [_P, _P, _P, _P, C.c_size_t, C.POINTER(mdt_adam), C.c_int64, C.c_float, _P]),

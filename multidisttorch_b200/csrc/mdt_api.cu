@@ -655,6 +655,16 @@ int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n) {
   return MDT_OK;
 }
 
+int mdt_engine_disable_peers(mdt_engine* e) {
+  MDT_CHECK(e, "NULL engine");
+  if (!e->p2p) return MDT_OK;
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  e->p2p = false;
+  for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
+  e->graphs.clear();
+  return MDT_OK;
+}
+
 int mdt_engine_exchange_status(mdt_engine* e, int* enabled, int* timed_out) {
   MDT_CHECK(e, "NULL engine");
   StepState h;

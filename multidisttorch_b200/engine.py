@@ -120,9 +120,8 @@ class VAEEngine:
         flag = torch.tensor([1 if ok else 0], device=self.device)
         dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=self.group)
         if int(flag.item()) == 0:
-            if ok:   # this rank could, a peer could not: recreate without the exchange is not needed, just never use it
-                raise RuntimeError("peer-memory exchange set up on this rank but not on all ranks of the group; "
-                                   "set MDT_P2P_ALLREDUCE=0")
+            if ok:   # this rank could map its peers, another rank of the group could not: everybody stays on NCCL
+                check(self.lib.mdt_engine_disable_peers(self._h))
             return False
         return True
 
