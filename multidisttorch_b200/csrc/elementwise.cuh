@@ -488,7 +488,9 @@ constexpr int kMaxPeers = 8;
 struct PeerArgs {
   int n, me;
   const float* g[kMaxPeers];          // exchange buffers, indexed by group rank (g[me] = this rank's own)
-  unsigned int* flags[kMaxPeers];     // flag blocks: [0..8) "gradient ready" by source rank, [8..16) "done reading"
+  float* red[kMaxPeers];              // second half of every exchange region: reduced slices (two-shot form)
+  unsigned int* flags[kMaxPeers];     // flag blocks: [0..8) "gradient ready" by source rank, [8..16) "done reading",
+                                      // [16..24) "reduced slice ready"
   float* g_out;                       // where the summed gradient is stored
 };
 
@@ -568,6 +570,105 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a
       a.st->ticket_adam = 0;
       __threadfence_system();
       for (int r = 0; r < pa.n; ++r)                  // every block of this rank has finished reading the peers' buffers
+        if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
+      for (int r = 0; r < pa.n; ++r)
+        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) a.st->xch_error = 1u;
+    }
+  }
+}
+
+// Two-shot form for groups of 3+ ranks.  In the one-shot kernel every rank reads all of every peer's gradient:
+// (n-1) x M bytes over NVLink per rank.  Here rank r first sums only slice r (1/n of the buffer) over all ranks into the
+// second half of its exchange region (p2p_reduce_slice_kernel: (n-1)/n x M bytes read), and the Adam kernel then gathers
+// the n reduced slices from their owners (another (n-1)/n x M): 2(n-1)/n x M in total -- the reduce-scatter + all-gather
+// volume -- with the all-gather half still fused into the optimizer pass.  Same flags, same bounded waits, sums in rank
+// order inside every slice (bit-identical on all ranks).
+__global__ void __launch_bounds__(kAdamThreads) p2p_reduce_slice_kernel(PeerArgs pa, long long n4, StepState* st) {
+  pdl_wait();
+  pdl_trigger();
+  const unsigned int t = st->xch_seq + 1u;            // bumped by the Adam kernel that follows
+  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
+    if (blockIdx.x == 0) {
+      __threadfence_system();
+      st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
+    }
+    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) st->xch_error = 1u;
+  }
+  __syncthreads();
+  const long long s4 = (n4 + pa.n - 1) / pa.n;        // float4 per slice
+  const long long lo = (long long)pa.me * s4, hi = (lo + s4 < n4) ? lo + s4 : n4;
+  float4* out = reinterpret_cast<float4*>(pa.red[pa.me]);
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi; i += (long long)gridDim.x * blockDim.x) {
+    float4 gr[kMaxPeers];
+#pragma unroll
+    for (int r = 0; r < kMaxPeers; ++r)
+      gr[r] = (r < pa.n) ? __ldcg(reinterpret_cast<const float4*>(pa.g[r]) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 g = gr[0];
+#pragma unroll
+    for (int r = 1; r < kMaxPeers; ++r) { g.x += gr[r].x; g.y += gr[r].y; g.z += gr[r].z; g.w += gr[r].w; }
+    out[i] = g;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&st->ticket_loss, 1u) == gridDim.x - 1) {     // last block: this rank's slice is complete
+      st->ticket_loss = 0;
+      __threadfence_system();
+      for (int r = 0; r < pa.n; ++r)
+        if (r != pa.me) st_release_sys(pa.flags[r] + 2 * kMaxPeers + pa.me, t);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kAdamThreads) adam_allgather_kernel(AdamArgs a, PeerArgs pa) {
+  pdl_wait();
+  pdl_trigger();
+  const float step_size = a.st->next[0], bc2_sqrt = a.st->next[1], omb1 = a.st->next[2], b2 = a.st->next[3],
+              omb2 = a.st->next[4], eps = a.st->next[5];
+  const unsigned int t = a.st->xch_seq + 1u;
+  const float gs = a.grad_scale;
+  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me)
+    if (!wait_flag_ge(pa.flags[pa.me] + 2 * kMaxPeers + threadIdx.x, t)) a.st->xch_error = 1u;
+  __syncthreads();
+  if (a.loss_out != nullptr && blockIdx.x == 0) {
+    __shared__ float red[32];
+    float l = 0.f;
+    for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) l += __ldcg(a.loss_part_a + i);
+    for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) l += __ldcg(a.loss_part_b + i);
+    l = block_sum(l, red);
+    if (threadIdx.x == 0) { *a.loss_out = l; publish_loss(a.st, l); }
+  }
+  const long long n4 = a.n >> 2;
+  const long long s4 = (n4 + pa.n - 1) / pa.n;
+  float4* p4 = reinterpret_cast<float4*>(a.p);
+  float4* m4 = reinterpret_cast<float4*>(a.m);
+  float4* v4 = reinterpret_cast<float4*>(a.v);
+  float4* go4 = reinterpret_cast<float4*>(pa.g_out);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const int owner = (int)(i / s4);
+    float4 g = __ldcg(reinterpret_cast<const float4*>(pa.red[owner]) + i);
+    float4 p = p4[i], m = m4[i], v = v4[i];
+    go4[i] = g;
+    g.x *= gs; g.y *= gs; g.z *= gs; g.w *= gs;
+    adam_elem(p.x, g.x, m.x, v.x, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.y, g.y, m.y, v.y, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.z, g.z, m.z, v.z, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    adam_elem(p.w, g.w, m.w, v.w, step_size, bc2_sqrt, omb1, b2, omb2, eps);
+    p4[i] = p; m4[i] = m; v4[i] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned int done = atomicAdd(&a.st->ticket_adam, 1u);
+    if (done == gridDim.x - 1) {
+      a.st->adam_t += 1;
+      a.st->b1_pow *= a.st->beta1;
+      a.st->b2_pow *= a.st->beta2;
+      adam_next_scalars(a.st->lr, a.st->beta1, a.st->beta2, a.st->eps, a.st->b1_pow, a.st->b2_pow, a.st->next);
+      a.st->xch_seq = t;
+      a.st->ticket_adam = 0;
+      __threadfence_system();
+      for (int r = 0; r < pa.n; ++r)                  // this rank has finished reading gradients and reduced slices
         if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
       for (int r = 0; r < pa.n; ++r)
         if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) a.st->xch_error = 1u;

@@ -81,14 +81,14 @@ class VAEEngine:
             check(self.lib.mdt_engine_stream(h, C.byref(s)))
             self.stream = torch.cuda.ExternalStream(s.value, device=self.device)
             self.p2p = False
-            # One-shot exchange (every rank reads all its peers' gradients).  Measured against NCCL in the same build:
-            #   2 ranks: 3.19 vs 3.03 M samples/s at H=400 (2.6 MB), 2.27 vs 1.94 M at H=4096 (26.7 MB)  -> always
-            #   4 ranks: 11.1 vs 10.9 M at H=400 (7.8 MB read per rank), 1.66 vs 1.83 M at H=4096 (80 MB) -> small only
-            #   8 ranks: 7.7 vs 9.1 M at H=400                                                            -> never
+            # Gradient exchange over NVLink peer memory inside the Adam kernel (one-shot, or two-shot when a rank would
+            # read more than 16 MB from its peers) against NCCL in the same build, samples/s:
+            #   2 ranks: 3.19 vs 3.03 M at H=400 (2.6 MB of gradient), 2.27 vs 1.94 M at H=4096 (26.7 MB)
+            #   4 ranks: 11.1 vs 10.9 M at H=400 (2x4 layout), 1.85 vs 1.83 M at H=4096 (two-shot)
+            #   8 ranks: one-shot 7.7 vs 9.1 M at H=400; two-shot not measured on 8 -> NCCL unless forced
             mode = os.environ.get("MDT_P2P_ALLREDUCE", "1")
             max_ranks = int(os.environ.get("MDT_P2P_MAX_RANKS", "4"))
-            peer_bytes = (self.group_size - 1) * self.total * 4
-            want = self.group_size == 2 or (self.group_size <= max_ranks and peer_bytes <= (16 << 20))
+            want = self.group_size <= max_ranks
             if mode == "force":
                 want = self.group_size <= 8
             if self.group_size > 1 and gemm_mode != "fp32" and mode != "0" and want:

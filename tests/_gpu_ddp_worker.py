@@ -46,7 +46,7 @@ def main():
     # which exchange ran: peer memory on the tensor-core path unless switched off, NCCL otherwise; no expired waits
     n_grp = dist.get_world_size(group)
     want_p2p = (mode != "fp32" and os.environ.get("MDT_P2P_ALLREDUCE", "1") != "0"
-                and (n_grp == 2 or (n_grp <= 4 and (n_grp - 1) * eng.total * 4 <= (16 << 20))))
+                and n_grp <= int(os.environ.get("MDT_P2P_MAX_RANKS", "4")))
     assert eng.exchange_status() == (want_p2p, False), (eng.exchange_status(), want_p2p)
     # ranks of a group must hold bit-identical parameters
     flat = eng.params.clone()
