@@ -1651,11 +1651,13 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   const bool w4_split = getenv("MDT_W4_SPLIT") != nullptr;
   int bn4 = w4_split ? p->bn_dw : bna;
   if (const char* v = getenv("MDT_BN_DW4")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn4 = c; }
+  int bn1 = bna;
+  if (const char* v = getenv("MDT_BN_DW1")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn1 = c; }
   Dw dw[4] = {
       {W4, B4, D, H, bn4, 0, &m->da4T, bn4 == bna ? &m->h3Ta : &m->h3T, p->da4T, p->W4T, D, w4_split ? "fc4_dW" : "fc4_dW_adam", 1},
       {W3, B3, H, Z, 32, 1, &m->da3T, &m->zT, p->da3T, p->W3T, H, "fc3_dW_adam", 1},
       {W2X, B2X, 2 * Z, H, bna, 2, &m->dmlT, &m->h1Ta, p->dmlT, p->W2xT, 2 * Z, "fc2x_dW_adam", 1},
-      {W1, B1, H, D, bna, 3, &m->da1T, &m->xTa, p->da1T, nullptr, 0, "fc1_dW_adam", 1},
+      {W1, B1, H, D, bn1, 3, &m->da1T, bn1 == bna ? &m->xTa : &m->xT, p->da1T, nullptr, 0, "fc1_dW_adam", 1},
   };
   Tc05Epi ed[4];
   int total_ctas = 0;
