@@ -114,6 +114,8 @@ struct mdt_engine {
   PeerArgs peers{};
   bool p2p = false;
   int sm_share_pending = 1;
+  // diagnostic switches, read from the environment once when the engine is created
+  bool opt_fused_adam = true, opt_nccl_in_graph = true, opt_zerocopy = true, opt_h2d_prefetch = true;
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
   // host-buffer steps submitted while the GPU is still busy: x is DMA'd into a small ring of device buffers on a copy
   // stream (overlapping the step in flight) instead of being read over PCIe by the step's own first kernel
@@ -483,7 +485,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
   const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1);   // graphs are per (eps given, SM share)
   if (e->tc) e->pub_expected = (e->pub_expected + 1u) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
-  if (e->gsize == 1 && e->tc && !getenv("MDT_NO_FUSED_ADAM")) {
+  if (e->gsize == 1 && e->tc && e->opt_fused_adam) {
     // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
     return run_cached(e, /*kind=*/7, B, fl, [&]() -> int {
       MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
@@ -508,7 +510,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
       return enqueue_adam_p2p(e, gscale);
     });
   }
-  if (getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0') {   // NCCL outside the graphs
+  if (!e->opt_nccl_in_graph) {   // MDT_NCCL_GRAPH=0: NCCL outside the graphs
     MDT_TRY(run_cached(e, /*kind=*/1, B, fl, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
     MDT_TRY(finish_allreduce(e));
     return run_cached(e, /*kind=*/2, B, fl & ~1, [&]() -> int { return enqueue_adam(e, gscale, true); });
@@ -561,6 +563,10 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   cudaGetDevice(&e->device);
   e->comm = reinterpret_cast<ncclComm_t>(nccl_comm);
   e->gsize = group_size; e->grank = group_rank;
+  e->opt_fused_adam = getenv("MDT_NO_FUSED_ADAM") == nullptr;
+  e->opt_nccl_in_graph = !(getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0');
+  e->opt_zerocopy = getenv("MDT_NO_ZEROCOPY") == nullptr;
+  e->opt_h2d_prefetch = getenv("MDT_NO_H2D_PREFETCH") == nullptr;
   if (stream) {
     e->stream = reinterpret_cast<cudaStream_t>(stream);
   } else {
@@ -862,7 +868,7 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
   MDT_CHECK(ticket, "ticket is NULL");
   const float* x = x_host;
   const float* eps = eps_host_or_null;
-  if (e->tc && e->mailbox != nullptr && batch > 0 && !getenv("MDT_NO_ZEROCOPY")) {
+  if (e->tc && e->mailbox != nullptr && batch > 0 && e->opt_zerocopy) {
     // Tensor-core path.  Pinned x is read by the step's prologue kernel straight from host memory (no separate H2D
     // copy in front of the graph), and the loss comes back through the mailbox ring the step's last thread writes.
     cudaPointerAttributes at{};
@@ -876,7 +882,7 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
       // Is the step submitted last still running?  Then there is compute to hide a DMA behind.
       const unsigned int last = e->pub_expected;
       const bool busy = last != 0 && (unsigned int)(e->mailbox[last & 63u] >> 32) != last;
-      if (busy && !getenv("MDT_NO_H2D_PREFETCH")) {
+      if (busy && e->opt_h2d_prefetch) {
         if (e->copy_stream == nullptr) {
           MDT_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
           for (int k = 0; k < mdt_engine::kPreSlots; ++k) {
