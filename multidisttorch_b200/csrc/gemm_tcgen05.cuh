@@ -100,6 +100,27 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
+// Same with the A operand in tensor memory (TS form): A[m][k] = lane m, column (a_tmem & 0xffff) + k, one tf32 per column.
+__device__ __forceinline__ void mma_tf32_ts(uint32_t tmem_d, uint32_t a_tmem, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// 32 lanes x 16 consecutive 32-bit columns: thread t of the warp writes lane (base_lane + t).
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const float* v) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(__float_as_uint(v[0])), "r"(__float_as_uint(v[1])), "r"(__float_as_uint(v[2])),
+        "r"(__float_as_uint(v[3])), "r"(__float_as_uint(v[4])), "r"(__float_as_uint(v[5])), "r"(__float_as_uint(v[6])),
+        "r"(__float_as_uint(v[7])), "r"(__float_as_uint(v[8])), "r"(__float_as_uint(v[9])), "r"(__float_as_uint(v[10])),
+        "r"(__float_as_uint(v[11])), "r"(__float_as_uint(v[12])), "r"(__float_as_uint(v[13])), "r"(__float_as_uint(v[14])),
+        "r"(__float_as_uint(v[15]))
+      : "memory");
+}
+__device__ __forceinline__ void tmem_wait_st() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // mbarrier arrive once every tcgen05 op issued so far by this thread has completed.
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
@@ -200,6 +221,8 @@ struct Tc05Epi {
   const float* loss_part_a; int n_part_a; const float* loss_part_b; int n_part_b; float* adam_loss_out;
   // split-K workspace: [tile][split][128*BN] partial tiles + one ticket counter per tile
   float* ws; unsigned int* ws_counters;
+  int a_tmem;    // TF32X3: the split warps put hi / lo of the A tile into tensor memory (MMA TS form) instead of
+                 // writing lo next to it in shared memory -- the MMAs then read only B from shared memory
   int cluster;   // split-K CTAs of a tile form a thread-block cluster (1,1,splits): partials are exchanged through DSMEM
   // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
   long long* dbg;
@@ -634,7 +657,9 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5));
   float* red = reinterpret_cast<float*>(smem + S::BAR_OFF + 8 * (3 * S::STAGES + 5) + 16);  // 8 floats (one per epilogue warp)
   constexpr int kDrainWarps = kTcDrainThreads / 32;                 // TF32X3: one drain warp per TMEM lane quadrant
-  constexpr int kTmemCols = kSplit ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
+  constexpr int kTmemAccCols = kSplit ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
+  constexpr int kTmemABase = kTmemAccCols;              // TS form: A stages follow the accumulators
+  const int kTmemCols = (kSplit && ep.a_tmem) ? 512 : kTmemAccCols;   // power of two >= 2 BN + 4 * 64
 
   if (threadIdx.x == 0) {
     ptx::prefetch_tmap(&tmap_a);
@@ -706,7 +731,13 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 #pragma unroll
         for (int k = 0; k < kTcBK / 8; ++k) {
           const uint64_t koff = (uint64_t)((k * 8 * 4) >> 4);   // 32 bytes per UMMA_K=8 step, in 16-byte units
-          if (kSplit) {
+          if (kSplit && ep.a_tmem) {
+            const uint64_t b_lo = umma_desc_sw128(sa + S::HB + S::A_BYTES);
+            const uint32_t ta_hi = tmem_base + (uint32_t)(kTmemABase + s * 64 + k * 8), ta_lo = ta_hi + 32u;
+            ptx::mma_tf32_ts(td, ta_lo, b_hi + koff, idesc, k ? 1u : 0u);
+            ptx::mma_tf32_ts(td, ta_hi, b_lo + koff, idesc, 1u);
+            ptx::mma_tf32_ts(td, ta_hi, b_hi + koff, idesc, 1u);
+          } else if (kSplit) {
             const uint64_t a_lo = umma_desc_sw128(sa + S::HB), b_lo = umma_desc_sw128(sa + S::HB + S::A_BYTES);
             ptx::mma_tf32(td, a_lo + koff, b_hi + koff, idesc, k ? 1u : 0u);
             ptx::mma_tf32(td, a_hi + koff, b_lo + koff, idesc, 1u);
@@ -816,6 +847,35 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         ptx::mbar_wait(bar_full + 8 * s, ph);
         float4* hi = reinterpret_cast<float4*>(smem + s * S::STAGE);
         float4* lo = reinterpret_cast<float4*>(smem + s * S::STAGE + S::HB);
+        if (ep.a_tmem) {
+          // A tile -> tensor memory.  Thread = accumulator-style (lane quadrant q, row q*32+lane); the two warps of a
+          // quadrant take 16 of the 32 K-columns each.  Row r of the SWIZZLE_128B tile: 16-byte chunk j sits at
+          // r*128 + ((j ^ (r & 7)) << 4).  hi is written explicitly truncated, lo = a - hi (exact).
+          const uint8_t* arow = smem + s * S::STAGE + row * 128;
+          float vh[16], vl[16];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = 4 * chalf + j;
+            const float4 v = *reinterpret_cast<const float4*>(arow + ((chunk ^ (row & 7)) << 4));
+            vh[4 * j + 0] = ptx::tf32_hi(v.x); vh[4 * j + 1] = ptx::tf32_hi(v.y);
+            vh[4 * j + 2] = ptx::tf32_hi(v.z); vh[4 * j + 3] = ptx::tf32_hi(v.w);
+            vl[4 * j + 0] = v.x - vh[4 * j + 0]; vl[4 * j + 1] = v.y - vh[4 * j + 1];
+            vl[4 * j + 2] = v.z - vh[4 * j + 2]; vl[4 * j + 3] = v.w - vh[4 * j + 3];
+          }
+          const uint32_t ta = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(kTmemABase + s * 64 + 16 * chalf);
+          ptx::tmem_st16(ta, vh);
+          ptx::tmem_st16(ta + 32u, vl);
+          // B tile: lo next to hi in shared memory, as before
+          for (int c = S::A_BYTES / 16 + et; c < S::HB / 16; c += kTcEpiThreads) {
+            const float4 v = hi[c];
+            float4 l;
+            l.x = v.x - ptx::tf32_hi(v.x); l.y = v.y - ptx::tf32_hi(v.y);
+            l.z = v.z - ptx::tf32_hi(v.z); l.w = v.w - ptx::tf32_hi(v.w);
+            lo[c] = l;
+          }
+          ptx::tmem_wait_st();
+          ptx::tc_fence_before();
+        } else
 #pragma unroll 4
         for (int c = et; c < S::HB / 16; c += kTcEpiThreads) {
           // The tensor core reads only sign, exponent and the top 10 mantissa bits of an fp32 word (it truncates),
@@ -1154,7 +1214,12 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   // split-K: the splits of a tile exchange their partials through distributed shared memory when they fit one cluster
-  static const bool use_clusters = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+  const bool use_clusters = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+  // MDT_A_TMEM=1: TF32X3 with the A operand in tensor memory (see Tc05Epi::a_tmem).  Correct, and measured equal in
+  // speed to the shared-memory form (57.4 vs 57.5 us/step): the ~1000-cycle k-block is not bound by the MMAs'
+  // shared-memory reads of A.  Off by default; read per launch (launches happen at graph capture).
+  const char* at = getenv("MDT_A_TMEM");
+  epd.a_tmem = (kSplit && at != nullptr && at[0] == '1') ? 1 : 0;
   epd.cluster = (nsplit > 1 && nsplit <= 8 && use_clusters) ? 1 : 0;
   if (epd.cluster) {
     // a cluster needs its CTAs on SMs of one GPC at the same time: when the tiles do not all fit as co-resident
@@ -1189,7 +1254,7 @@ inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc0
   const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
   const int total_kb = (K + kTcBK - 1) / kTcBK;
   // at least 3 k-blocks per split (4 without the cluster exchange, whose reduction costs ~1.5 us less: measured)
-  static const int min_kb = getenv("MDT_MIN_KB_PER_SPLIT") ? atoi(getenv("MDT_MIN_KB_PER_SPLIT"))
+  const int min_kb = getenv("MDT_MIN_KB_PER_SPLIT") ? atoi(getenv("MDT_MIN_KB_PER_SPLIT"))
                                                            : (getenv("MDT_NO_CLUSTER_SPLITK") ? 4 : 3);
   int want = total_kb / (min_kb > 0 ? min_kb : 4);
   const int cap = sm_count / tiles;

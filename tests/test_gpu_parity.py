@@ -179,7 +179,8 @@ def test_train_steps_match_reference_golden(E, mode, tag, graph):
 @pytest.mark.parametrize("mode", [m for m in MODES if m != "fp32"])
 @pytest.mark.parametrize("env", [{"MDT_TC_LATENT": "1"}, {"MDT_NO_FUSED_ADAM": "1"},
                                  {"MDT_TC_LATENT": "1", "MDT_NO_FUSED_ADAM": "1"}, {"MDT_LATENT_SC": "1"},
-                                 {"MDT_LATENT_SC": "2"}, {"MDT_DW4_LATE": "1"}, {"MDT_W4_SPLIT": "1"}],
+                                 {"MDT_LATENT_SC": "2"}, {"MDT_DW4_LATE": "1"}, {"MDT_W4_SPLIT": "1"}, {"MDT_A_TMEM": "1"},
+                                 {"MDT_NO_CLUSTER_SPLITK": "1"}],
                          ids=lambda e: "+".join(f"{k[4:].lower()}{v}" for k, v in e.items()))
 def test_alternative_kernel_paths_match_golden(E, mode, env, monkeypatch):
     """The step has run-time alternatives the defaults do not take at this size (tensor-core latent layers, the
