@@ -101,9 +101,9 @@ class EpsInjector:
         self.torch.randn_like = self._orig
 
 
-def put_fp(out, prefix, seg_dict):
+def put_fp(out, prefix, seg_dict, stride=61):
     for k, v in seg_dict.items():
-        fp = O.fingerprint(v)
+        fp = O.fingerprint(v, stride)
         out[f"{prefix}.{k}.sum"] = fp["sum"]
         out[f"{prefix}.{k}.l2"] = fp["l2"]
         out[f"{prefix}.{k}.sample"] = fp["sample"]
@@ -119,18 +119,31 @@ def batch_seed(step, rank=0):
     return DATA_SEED + 1000 * rank + step
 
 
-def run_single(B, n_steps, tag):
+def widen(ref_model, torch, H):
+    """BASELINE config 5 ("widened hidden dim 4096"): the reference's VAE with its five nn.Linear
+    re-sized to hidden width H.  forward / loss / autograd stay the reference's own code."""
+    if H == 400:
+        return ref_model
+    nn = torch.nn
+    ref_model.fc1, ref_model.fc21, ref_model.fc22 = nn.Linear(784, H), nn.Linear(H, 20), nn.Linear(H, 20)
+    ref_model.fc3, ref_model.fc4 = nn.Linear(20, H), nn.Linear(H, 784)
+    return ref_model
+
+
+def run_single(B, n_steps, tag, H=400, stride=61):
     """One rank, no DDP: ref:vae-hpo.py:69-74 verbatim."""
     torch, ref = load_reference()
     torch.set_num_threads(8)
-    dims = O.Dims()
+    dims = O.Dims(H=H)
     p0 = O.init_params(PARAM_SEED, dims)
-    model = ref.VAE()
+    model = widen(ref.VAE(), torch, H)
     model.load_state_dict(ref_state_from_oracle(p0, torch))
     opt = torch.optim.Adam(model.parameters(), lr=1e-3)
     orc = O.Trainer(p0, dims)
-    out = {"B": B, "n_steps": n_steps}
+    out = {"B": B, "n_steps": n_steps, "H": H, "stride": stride}
     losses = []
+    _put = put_fp
+    put_fp_l = lambda o, pre, d: _put(o, pre, d, stride)
     with EpsInjector(torch) as inj:
         for t in range(n_steps):
             x, eps = O.make_batch(batch_seed(t), B, dims)
@@ -142,10 +155,10 @@ def run_single(B, n_steps, tag):
             loss.backward()
             losses.append(loss.item())
             if t == 0:
-                put_fp(out, "step0", {"recon": recon.detach().numpy(), "mu": mu.detach().numpy(),
+                put_fp_l(out, "step0", {"recon": recon.detach().numpy(), "mu": mu.detach().numpy(),
                                       "logvar": logvar.detach().numpy()})
                 g_ref = oracle_from_ref(dict(model.named_parameters()), attr=lambda q: q.grad)
-                put_fp(out, "grad0", g_ref)
+                put_fp_l(out, "grad0", g_ref)
             opt.step()
             # oracle in lock-step, full-tensor check
             lo, go = orc.step([(x, eps)])
@@ -155,14 +168,16 @@ def run_single(B, n_steps, tag):
                     assert rel_l2(go[k], g_ref[k]) < 2e-5, (tag, "grad", k, rel_l2(go[k], g_ref[k]))
     pN = oracle_from_ref(dict(model.named_parameters()))
     for k in pN:
-        assert rel_l2(orc.p[k], pN[k]) < 1e-5, (tag, "param", k, rel_l2(orc.p[k], pN[k]))
-    put_fp(out, "paramN", pN)
+        # H=4096: K=4096 dot products differ between numpy's and torch's fp32 summation order by ~1e-6, and the
+        # first Adam steps (update ~ lr * sign(g)) amplify that ~50x (measured 6.9e-5 on W1 after 3 steps)
+        assert rel_l2(orc.p[k], pN[k]) < (1e-5 if H == 400 else 2e-4), (tag, "param", k, rel_l2(orc.p[k], pN[k]))
+    put_fp_l(out, "paramN", pN)
     st = opt.state_dict()["state"]
     names = [n for n, _ in model.named_parameters()]
     mN = oracle_from_ref({n: st[i]["exp_avg"] for i, n in enumerate(names)})
     vN = oracle_from_ref({n: st[i]["exp_avg_sq"] for i, n in enumerate(names)})
-    put_fp(out, "mN", mN)
-    put_fp(out, "vN", vN)
+    put_fp_l(out, "mN", mN)
+    put_fp_l(out, "vN", vN)
     out["losses"] = np.array(losses, dtype=np.float64)
     np.savez_compressed(os.path.join(GOLD, f"{tag}.npz"), **out)
     print(f"[golden] {tag}: losses {losses[0]:.4f} .. {losses[-1]:.4f}")
@@ -225,6 +240,57 @@ def run_loss_edge(tag):
                         loss=np.float64(L.item()), d_recon=tr.grad.numpy(), d_mu=tm.grad.numpy(),
                         d_logvar=tl.grad.numpy())
     print(f"[golden] {tag}: loss {L.item():.6e}")
+
+
+EDGE_LOGITS = np.array([-120.0, -104.0, -103.0, -100.0, -95.0, -90.0, -88.0, -87.0, -60.0, -30.0, -17.0, -1e-3, 0.0, 8.0, 15.0,
+                        16.0, 16.6, 16.7, 17.0, 17.5, 20.0, 50.0, 90.0, 120.0], dtype=np.float32)
+
+
+def edge_setup(p0, x):
+    """fc4 rows 0..n-1 get zero weights and a bias equal to a corner logit, so recon[:, j] = sigmoid(EDGE_LOGITS[j])
+    for every sample; samples 0/1/2 carry targets 0 / 1 / 0.25 there.  Shared with tests/test_gpu_parity.py."""
+    n = len(EDGE_LOGITS)
+    p0["W4"][:n, :] = 0.0
+    p0["b4"][:n] = EDGE_LOGITS
+    x[0, :n], x[1, :n], x[2, :n] = 0.0, 1.0, 0.25
+    return p0, x
+
+
+def run_step_edge(tag, B=8):
+    """One full training step of the reference whose fc4 logits sit on the BCE clamp / sigmoid saturation
+    corners (ref:vae-hpo.py:40, 50): the known answer for the step's FUSED sigmoid+BCE epilogue."""
+    torch, ref = load_reference()
+    torch.set_num_threads(8)
+    dims = O.Dims()
+    x, eps = O.make_batch(batch_seed(0), B, dims)
+    p0, x = edge_setup(O.init_params(PARAM_SEED, dims), x)
+    model = ref.VAE()
+    model.load_state_dict(ref_state_from_oracle(p0, torch))
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    out = {"B": B, "n_steps": 1}
+    with EpsInjector(torch) as inj:
+        data = torch.from_numpy(x).view(B, 1, 28, 28)
+        inj.queue.append(torch.from_numpy(eps))
+        opt.zero_grad()
+        recon, mu, logvar = model(data)
+        recon.retain_grad()
+        loss = ref.loss_function(recon, data, mu, logvar)
+        loss.backward()
+        n = len(EDGE_LOGITS)
+        out["recon_edge"] = recon.detach().numpy()[:3, :n].copy()
+        out["d_recon_edge"] = recon.grad.numpy()[:3, :n].copy()
+        g_ref = oracle_from_ref(dict(model.named_parameters()), attr=lambda q: q.grad)
+        put_fp(out, "grad0", g_ref)
+        out["grad0.b4.edge"] = g_ref["b4"][:n].copy()
+        opt.step()
+    lo, go = O.Trainer(p0, dims).step([(x, eps)])
+    assert abs(lo[0] - loss.item()) <= 2e-6 * abs(loss.item()), (lo[0], loss.item())
+    for k in g_ref:
+        assert rel_l2(go[k], g_ref[k]) < 2e-5, (tag, k, rel_l2(go[k], g_ref[k]))
+    put_fp(out, "paramN", oracle_from_ref(dict(model.named_parameters())))
+    out["losses"] = np.array([loss.item()], dtype=np.float64)
+    np.savez_compressed(os.path.join(GOLD, f"{tag}.npz"), **out)
+    print(f"[golden] {tag}: loss {loss.item():.4f}; recon at the corners", out["recon_edge"][0])
 
 
 # ----------------------------------------------------------------------------
@@ -384,13 +450,19 @@ def main():
         run_single(128, 10, "step_b128")
         run_single(48, 3, "step_b48")
         run_single(1, 2, "step_b1")
+        run_single(512, 3, "step_b512")                          # BASELINE config 4's group batch on one rank
+        run_single(128, 3, "step_h4096_b128", H=4096, stride=997)   # BASELINE config 5's width
     if "eval" in todo:
         run_eval(64, "eval_b64")
     if "edge" in todo:
         run_loss_edge("loss_edge")
+        run_step_edge("step_edge_b8")
     if "ddp" in todo:
         run_ddp(2, 1, 5, 32, "ddp_1x2_b32", 29610)
         run_ddp(4, 2, 3, 16, "ddp_2x2_b16", 29620)
+        run_ddp(4, 1, 3, 32, "ddp_1x4_b32", 29650)
+        run_ddp(8, 1, 3, 16, "ddp_1x8_b16", 29660)
+        run_ddp(8, 2, 3, 128, "ddp_2x4_b128", 29670)             # BASELINE config 4: 2 trials x 4 ranks, 512/group
     if "api" in todo:
         run_api(29640)
     # print0 format known answer (from the ddp leg)

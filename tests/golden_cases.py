@@ -28,17 +28,10 @@ def rel_l2(a, b):
 
 def check_fp(gold, prefix, name, arr, tol, what=""):
     """Compare a full tensor against a golden fingerprint: strided sample
-    (relative L2), float64 sum and l2 norm."""
-    arr = np.asarray(arr, np.float32).reshape(-1)
-    smp = gold[f"{prefix}.{name}.sample"]
-    assert smp.shape == arr[::STRIDE].shape, (what, prefix, name, smp.shape, arr[::STRIDE].shape)
-    # error of the sampled elements relative to the tensor's RMS scale (a lone sampled element of a
-    # tiny tensor can be far below the RMS, which would make a pure sample-relative figure noisy)
-    scale = max(float(np.linalg.norm(smp.astype(np.float64))),
-                float(gold[f"{prefix}.{name}.l2"]) * np.sqrt(smp.size / arr.size), 1e-30)
-    e = float(np.linalg.norm(arr[::STRIDE].astype(np.float64) - smp.astype(np.float64))) / scale
+    (relative L2 against the tensor's RMS scale), float64 sum and l2 norm."""
+    from multidisttorch_b200.synth import fingerprint_error
+    e, e_l2, e_sum = fingerprint_error(gold, prefix, name, arr)
     assert e <= tol, f"{what} {prefix}.{name}: sample relL2 {e:.3e} > {tol:.1e}"
-    l2 = float(np.sqrt((arr.astype(np.float64) ** 2).sum()))
-    assert abs(l2 - float(gold[f"{prefix}.{name}.l2"])) <= tol * max(l2, 1e-30) * 4, (what, prefix, name, "l2")
-    s = float(arr.sum(dtype=np.float64))
-    assert abs(s - float(gold[f"{prefix}.{name}.sum"])) <= tol * l2 * np.sqrt(arr.size) , (what, prefix, name, "sum")
+    assert e_l2 <= 4 * tol, (what, prefix, name, "l2", e_l2)
+    assert e_sum <= tol, (what, prefix, name, "sum", e_sum)
+    return e

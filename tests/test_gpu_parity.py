@@ -37,9 +37,9 @@ def E():
     return engine
 
 
-def make_engine(E, mode, B, **kw):
-    eng = E.VAEEngine(max_batch=max(B, 1), gemm_mode=mode, **kw)
-    eng.load_segments(O.init_params(PARAM_SEED))
+def make_engine(E, mode, B, H=400, **kw):
+    eng = E.VAEEngine(hidden=H, max_batch=max(B, 1), gemm_mode=mode, **kw)
+    eng.load_segments(O.init_params(PARAM_SEED, O.Dims(H=H)))
     return eng
 
 
@@ -149,15 +149,20 @@ def test_linear_vs_oracle(E, mode, M, N, K, act):
 # ------------------------------------------------------------------ engine vs golden
 
 @pytest.mark.parametrize("mode", MODES)
-@pytest.mark.parametrize("tag", ["step_b128", "step_b48", "step_b1"])
+@pytest.mark.parametrize("tag", ["step_b128", "step_b48", "step_b1", "step_b512", "step_h4096_b128"])
 @pytest.mark.parametrize("graph", [True, False])
 def test_train_steps_match_reference_golden(E, mode, tag, graph):
+    """step_b512 = BASELINE config 4's group batch on one rank; step_h4096_b128 = config 5's width (the reference's
+    VAE with its five nn.Linear re-sized, oracle/make_golden.py:widen)."""
     g = load(tag)
     tol = TOL[mode]
     B, n = int(g["B"]), int(g["n_steps"])
-    eng = make_engine(E, mode, B, use_graph=graph)
+    H = int(g["H"]) if "H" in g else 400
+    if H != 400 and (not graph or mode == "fp32"):
+        pytest.skip("the wide case runs once per tensor-core mode (graph on); fp32 FFMA at H=4096 is covered by test_hidden_4096")
+    eng = make_engine(E, mode, B, H=H, use_graph=graph)
     for t in range(n):
-        x, eps = O.make_batch(batch_seed(t), B)
+        x, eps = O.make_batch(batch_seed(t), B, O.Dims(H=H))
         loss = eng.train_step(dev(x), dev(eps))
         got = float(loss.item())
         assert abs(got - g["losses"][t]) <= tol["loss"] * abs(g["losses"][t]), (tag, t, got, g["losses"][t])
@@ -173,6 +178,39 @@ def test_train_steps_match_reference_golden(E, mode, tag, graph):
         check_fp(g, "mN", k, mN[k], tol["mom"], f"{tag}/{mode}")
         check_fp(g, "vN", k, vN[k], 2 * tol["mom"], f"{tag}/{mode}")
     assert eng.state()[0] == n
+    eng.close()
+
+
+@pytest.mark.parametrize("mode", MODES)
+def test_fused_bce_epilogue_on_reference_corners(E, mode):
+    """The training step computes sigmoid + BCE + d(logits) inside fc4's GEMM epilogue with SFU approximations
+    (gemm_tcgen05.cuh fast_sigmoid / fast_bce_term / fast_dlogit), not with the stand-alone loss kernel.  Here fc4's
+    logits are pinned to the clamp / saturation corners of F.binary_cross_entropy and torch.sigmoid (|a| up to 120:
+    r = 0, denormal r, r = 1 - 2^-24, r = 1) and the step is compared with what the reference produced there
+    (oracle/make_golden.py:run_step_edge)."""
+    from oracle.make_golden import EDGE_LOGITS, edge_setup
+    g = load("step_edge_b8")
+    tol = TOL[mode]
+    B, n = int(g["B"]), len(EDGE_LOGITS)
+    x, eps = O.make_batch(batch_seed(0), B)
+    p0, x = edge_setup(O.init_params(PARAM_SEED), x)
+    eng = E.VAEEngine(max_batch=B, gemm_mode=mode)
+    eng.load_segments(p0)
+    loss = float(eng.train_step(dev(x), dev(eps)).item())
+    assert abs(loss - g["losses"][0]) <= tol["loss"] * abs(g["losses"][0]), (loss, g["losses"][0])
+    recon = eng.workspace("recon", B).cpu().numpy()[:3, :n]
+    # recon at the corners: exact zeros and ones where the reference has them, 4 ulp elsewhere (denormals included)
+    want = g["recon_edge"]
+    assert np.array_equal(recon == 0, want == 0) and np.array_equal(recon == 1, want == 1), (recon, want)
+    np.testing.assert_allclose(recon, want, rtol=1e-6, atol=1e-44)
+    gr = eng.segments_to_numpy(eng.grads)
+    # d loss / d fc4.bias at the pinned logits = sum over the batch of d(logits): exercises fast_dlogit's clamp branch
+    np.testing.assert_allclose(gr["b4"][:n], g["grad0.b4.edge"], rtol=2e-5, atol=1e-30)
+    for k in O.SEGMENTS:
+        check_fp(g, "grad0", k, gr[k], tol["grad"], f"edge/{mode}")
+    pN = eng.segments_to_numpy()
+    for k in O.SEGMENTS:
+        check_fp(g, "paramN", k, pN[k], tol["param"], f"edge/{mode}")
     eng.close()
 
 

@@ -13,15 +13,19 @@ TOL_PARAM = 1e-5
 TOL_LOSS = 2e-6
 
 
-@pytest.mark.parametrize("tag", ["step_b128", "step_b48", "step_b1"])
+@pytest.mark.parametrize("tag", ["step_b128", "step_b48", "step_b1", "step_b512", "step_h4096_b128"])
 def test_train_steps_match_reference(tag):
     g = load(tag)
     B, n = int(g["B"]), int(g["n_steps"])
-    tr = O.Trainer(O.init_params(PARAM_SEED))
+    dims = O.Dims(H=int(g["H"]) if "H" in g else 400)
+    # K = 4096 dot products: numpy's and torch's summation orders differ by ~1e-6, which Adam's first steps
+    # amplify to 6.9e-5 on W1 (measured by oracle/make_golden.py)
+    TOL_PARAM = 1e-5 if dims.H == 400 else 2e-4
+    tr = O.Trainer(O.init_params(PARAM_SEED, dims), dims)
     for t in range(n):
-        x, eps = O.make_batch(batch_seed(t), B)
+        x, eps = O.make_batch(batch_seed(t), B, dims)
         if t == 0:
-            L, grads, act = O.loss_and_grads(tr.p, x, eps)
+            L, grads, act = O.loss_and_grads(tr.p, x, eps, dims)
             for k_ref, k in (("recon", "recon"), ("mu", "mu"), ("logvar", "lv")):
                 check_fp(g, "step0", k_ref, act[k], TOL_ACT, tag)
             for k in O.SEGMENTS:
@@ -30,8 +34,8 @@ def test_train_steps_match_reference(tag):
         assert abs(losses[0] - g["losses"][t]) <= TOL_LOSS * abs(g["losses"][t]), (tag, t)
     for k in O.SEGMENTS:
         check_fp(g, "paramN", k, tr.p[k], TOL_PARAM, tag)
-        check_fp(g, "mN", k, tr.m[k], TOL_GRAD, tag)
-        check_fp(g, "vN", k, tr.v[k], 2 * TOL_GRAD, tag)
+        check_fp(g, "mN", k, tr.m[k], max(TOL_GRAD, TOL_PARAM), tag)
+        check_fp(g, "vN", k, tr.v[k], 2 * max(TOL_GRAD, TOL_PARAM), tag)
 
 
 def test_eval_forward_and_decode():
@@ -62,7 +66,21 @@ def test_loss_clamp_and_saturation_corners():
     np.testing.assert_allclose(dl, g["d_logvar"], rtol=2e-6, atol=1.2e-7)  # |0.5(e^lv-1)| cancels near lv=0
 
 
-@pytest.mark.parametrize("tag", ["ddp_1x2_b32", "ddp_2x2_b16"])
+def test_step_with_logits_on_the_bce_corners():
+    from oracle.make_golden import EDGE_LOGITS, edge_setup
+    g = load("step_edge_b8")
+    B, n = int(g["B"]), len(EDGE_LOGITS)
+    x, eps = O.make_batch(batch_seed(0), B)
+    p0, x = edge_setup(O.init_params(PARAM_SEED), x)
+    L, grads, act = O.loss_and_grads(p0, x, eps)
+    assert abs(L - g["losses"][0]) <= TOL_LOSS * abs(g["losses"][0])
+    np.testing.assert_allclose(act["recon"][:3, :n], g["recon_edge"], rtol=1e-6, atol=1e-44)
+    np.testing.assert_allclose(grads["b4"][:n], g["grad0.b4.edge"], rtol=2e-5, atol=1e-30)
+    for k in O.SEGMENTS:
+        check_fp(g, "grad0", k, grads[k], TOL_GRAD, "edge")
+
+
+@pytest.mark.parametrize("tag", ["ddp_1x2_b32", "ddp_2x2_b16", "ddp_1x4_b32", "ddp_1x8_b16", "ddp_2x4_b128"])
 def test_ddp_groups_match_reference(tag):
     g = load(tag)
     world, ng, B, n = (int(g[k]) for k in ("world", "ngroups", "B", "n_steps"))
