@@ -9,17 +9,22 @@ backward, group all-reduce, Adam) of one trial on one batch of synthetic
 MNIST-shaped data.  Workload at N GPUs: BASELINE config 3 -- N concurrent
 single-GPU trials (the Nx1 group layout), VAE 784-400-20, batch 128 per GPU;
 weak scaling, no data-path collective.  For N>1 (torchrun, one rank per GPU) the
-other group layouts (N/2 x 2 ... 1 x N, gradient all-reduce inside each group)
-are timed after the headline and reported under "layouts".
+run first replays the reference's own DDP golden vectors on the matching
+sub-worlds (`ddp_parity`; a mismatch makes the run exit non-zero), then times the
+headline, then the other group layouts (N/2 x 2 ... 1 x N, gradient exchange
+inside each group; `layouts`), the DDP-size all-reduce bus bandwidth (`allreduce`,
+BASELINE metric #2) and, at N = 8, BASELINE config 5 (`config5`).
 
 One JSON line on stdout (rank 0).  `value` = samples/s with inputs resident in
-HBM; `e2e` = the same steps through the host-buffer C-ABI call (H2D copy of every
-batch + D2H read of the loss inside the timed region).
+HBM (median of --repeats timed regions); `e2e` = the same steps through the
+host-buffer C-ABI call (H2D copy of every batch + D2H read of the loss inside the
+timed region).
 """
 from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import statistics
 import subprocess
@@ -36,32 +41,42 @@ UNIT = "samples/s"
 D, Z = 784, 20
 POOL_BATCHES = 512          # 512 x 128 x 784 x 4 B = 205 MB of inputs, larger than the 126 MB L2
 HOST_POOL_BATCHES = 64
+MIN_TIMED_STEPS = 200       # at least 200 timed steps per timed region
+DDP_SIZES = {"bucket0_fc4": 1257536, "bucket1_rest": 1353760, "flat_H400": 2611296, "flat_H4096": 26709216}
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20000)
+    ap.add_argument("--steps", type=int, default=2000)
     ap.add_argument("--warmup", type=int, default=50)
+    ap.add_argument("--repeats", type=int, default=5, help="timed regions per figure; the median is reported")
     ap.add_argument("--impl", default="own", choices=["own", "reference"])
     ap.add_argument("--batch", type=int, default=128, help="per-GPU batch")
     ap.add_argument("--hidden", type=int, default=400)
-    ap.add_argument("--gemm-mode", default=os.environ.get("MDT_GEMM", "tf32x3"), choices=["fp32", "tf32", "tf32x3"],
+    ap.add_argument("--gemm-mode", default=os.environ.get("MDT_GEMM", "tf32x3"), choices=["fp32", "tf32", "tf32x3", "bf16"],
                     help="tf32x3 (default): 3-pass split-TF32 on tcgen05 with fp32 promotion, fp32-grade parity; "
-                         "fp32: FFMA reference path; tf32: single-pass tensor-core")
+                         "fp32: FFMA reference path; tf32: single-pass tensor-core; bf16: bf16 operands, fp32 accumulate")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-layouts", action="store_true")
     ap.add_argument("--no-modes", action="store_true")
+    ap.add_argument("--no-parity", action="store_true")
+    ap.add_argument("--no-eager", action="store_true", help="skip the torch-CUDA eager run of the reference step")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
     ap.add_argument("--ref-worker", default="", help=argparse.SUPPRESS)
-    ap.add_argument("--ref-groups", type=int, default=0, help=argparse.SUPPRESS)
+    ap.add_argument("--eager-worker", default="", help=argparse.SUPPRESS)
     return ap.parse_args()
 
 
 def workload_name(n, batch, hidden):
     return (f"BASELINE config 3: VAE-HPO {n} concurrent single-GPU trial(s) ({n}x1 group layout), VAE {D}-{hidden}-{Z}, "
             f"batch {batch}/GPU, Adam lr=1e-3, synthetic MNIST-shaped data")
+
+
+def config_of(n, batch, hidden):
+    """The SAME dict in both arms (the driver compares them); arm-specific facts go under `arm`."""
+    return {"workload": workload_name(n, batch, hidden), "layout": f"{n}x1", "batch_per_gpu": batch, "hidden": hidden}
 
 
 # --------------------------------------------------------------------------------------------
@@ -86,6 +101,7 @@ def algorithmic_bytes(label, B, H, total_params):
         "fc1_dW": B * H + B * D + H * D,
         "bias_grads": B * (D + 2 * H + 2 * Z) + (D + 2 * H + 2 * Z),
         "adam_flat": 7 * total_params,
+        "sgd_flat": 5 * total_params,
         # tcgen05 path (fused epilogues): operands read once + results written once; the transposed duplicates the
         # K-major design adds are overhead, not algorithmic bytes
         "prep_xT_eps": 2 * B * D + B * Z,
@@ -108,7 +124,7 @@ def algorithmic_bytes(label, B, H, total_params):
 
 
 def step_flops(B, H):
-    return 2 * B * (5 * D * H + 9 * Z * H)      # SURVEY §8(d)
+    return 2 * B * (5 * D * H + 9 * Z * H)      # SURVEY section 8(d)
 
 
 def step_bytes(B, H, a=4):
@@ -120,8 +136,8 @@ def load_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
         j = json.load(open(p))
-        return float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
-    return 6650.0, "fallback (B200_PROFILING.md, MEASURED_PEAKS.json absent)"
+        return j, float(j["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return {}, 6650.0, "fallback (B200_PROFILING.md, MEASURED_PEAKS.json absent)"
 
 
 # --------------------------------------------------------------------------------------------
@@ -194,113 +210,279 @@ class ClockSampler:
 # --------------------------------------------------------------------------------------------
 # this repo's arm
 # --------------------------------------------------------------------------------------------
+class Ctx:
+    """Rank / device / collectives of this process."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+        self.torch, self.dist = torch, dist
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local = int(os.environ.get("LOCAL_RANK", str(self.rank)))
+        if self.world != args.gpus:
+            raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={self.world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py (own arm) needs a CUDA device: there is no CPU fallback")
+        torch.cuda.set_device(self.local)
+        self.device = torch.device("cuda", self.local)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("cpu:gloo,cuda:nccl", init_method="env://", device_id=self.device)
+
+    def barrier(self):
+        if self.world > 1:
+            self.dist.barrier(device_ids=[self.local])
+        self.torch.cuda.synchronize()
+
+    def reduce(self, v, op):
+        if self.world == 1:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device=self.device)
+        self.dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    def max(self, v):
+        return self.reduce(v, self.dist.ReduceOp.MAX)
+
+    def min(self, v):
+        return self.reduce(v, self.dist.ReduceOp.MIN)
+
+    def sum(self, v):
+        return self.reduce(v, self.dist.ReduceOp.SUM)
+
+
+def timed_regions(ctx, eng, enqueue, steps, warm, repeats):
+    """`repeats` timed regions of max(steps, MIN_TIMED_STEPS rounded up to a multiple of steps) steps each, every region
+    bracketed by barrier + synchronize on both sides and timed with CUDA events on the engine's stream (max over
+    ranks).  Returns (median ms per step, all ms per step, kernels launched in the timed regions, steps per region)."""
+    torch = ctx.torch
+    blocks = max(1, math.ceil(MIN_TIMED_STEPS / steps))
+    n = blocks * steps
+    enqueue(0, warm)
+    per_step, launches = [], 0
+    cursor = warm
+    for _ in range(repeats):
+        ctx.barrier()
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = eng.launch_count()
+        ev0.record(eng.stream)
+        enqueue(cursor, n)
+        ev1.record(eng.stream)
+        eng.synchronize()
+        ctx.barrier()
+        launches += eng.launch_count() - n0
+        per_step.append(ctx.max(ev0.elapsed_time(ev1)) / n)
+        cursor += n
+    return statistics.median(per_step), per_step, launches, n
+
+
+def ddp_parity(ctx, args, gemm_modes):
+    """Replay the reference's real DDP runs (tests/golden/ddp_*.npz, produced by oracle/make_golden.py from the
+    reference's own utils + DistributedDataParallel over gloo) on the matching sub-worlds, for every gradient
+    exchange the engine has.  Checks per-step losses, final parameters and bit-identical parameters across the ranks
+    of a group.  Returns (report, ok)."""
+    import numpy as np
+    torch, dist = ctx.torch, ctx.dist
+    from multidisttorch_b200 import synth
+    from multidisttorch_b200.engine import VAEEngine
+    cases = [("ddp_1x2_b32", 2)]
+    if ctx.world >= 4:
+        cases += [("ddp_2x2_b16", 4), ("ddp_1x4_b32", 4)]
+    if ctx.world >= 8:
+        cases += [("ddp_1x8_b16", 8), ("ddp_2x4_b128", 8)]
+    # stated tolerances (relative): loss / parameters after the golden's steps
+    TOL = {"tf32x3": (1e-5, 5e-4), "bf16": (2e-3, 1e-1)}
+    report, ok = {}, True
+    for tag, w in cases:
+        g = dict(np.load(os.path.join(ROOT, "tests", "golden", f"{tag}.npz"), allow_pickle=False))
+        ng, B, n_steps = int(g["ngroups"]), int(g["B"]), int(g["n_steps"])
+        k = w // ng
+        groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]   # every rank creates every group
+        entry = {}
+        for mode in gemm_modes:
+            for xch in ("p2p", "p2p_two_shot", "nccl"):
+                res = torch.zeros(3, dtype=torch.float64, device=ctx.device)      # [failed, max loss err, max param err]
+                if ctx.rank < w:
+                    gid = ctx.rank // k
+                    grank = ctx.rank % k
+                    try:
+                        eng = VAEEngine(max_batch=B, gemm_mode=mode, group=groups[gid], exchange=xch)
+                        if xch != "nccl" and not eng.p2p:
+                            raise RuntimeError("peer memory could not be mapped")
+                        eng.load_segments(synth.init_params(synth.PARAM_SEED + gid if grank == 0 else 999 + ctx.rank))
+                        eng.broadcast_params()
+                        for t in range(n_steps):
+                            x, eps = synth.make_batch(synth.batch_seed(t, ctx.rank), B)
+                            loss = float(eng.train_step(torch.from_numpy(x).to(ctx.device), torch.from_numpy(eps).to(ctx.device)).item())
+                            want = float(g[f"losses.rank{ctx.rank}"][t])
+                            res[1] = max(float(res[1]), abs(loss - want) / abs(want))
+                        p = eng.segments_to_numpy()
+                        for name in synth.SEGMENTS:
+                            e, e_l2, e_sum = synth.fingerprint_error(g, f"g{gid}.paramN", name, p[name])
+                            res[2] = max(float(res[2]), e, e_l2 / 4, e_sum)
+                        flat = eng.params.clone()
+                        gathered = [torch.empty_like(flat) for _ in range(k)]
+                        dist.all_gather(gathered, flat, group=groups[gid])
+                        same = all(torch.equal(gathered[0], t_) for t_ in gathered)
+                        timed_out = eng.exchange_status()[1]
+                        if not same or timed_out or not (res[1] <= TOL[mode][0]) or not (res[2] <= TOL[mode][1]):
+                            res[0] = 1
+                        eng.close()
+                    except Exception as exc:       # keep every rank in the collective below
+                        print(f"[bench ddp_parity] rank {ctx.rank} {tag}/{mode}/{xch}: {exc}", file=sys.stderr)
+                        res[0] = 1
+                dist.all_reduce(res, op=dist.ReduceOp.MAX)
+                failed = bool(res[0].item())
+                ok = ok and not failed
+                entry[f"{mode}/{xch}"] = {"status": "FAIL" if failed else "ok", "max_loss_rel": float(f"{res[1].item():.3g}"),
+                                          "max_param_rel": float(f"{res[2].item():.3g}")}
+        report[tag.replace("ddp_", "")] = entry
+    report["tolerance"] = {m: {"loss_rel": TOL[m][0], "param_rel": TOL[m][1]} for m in gemm_modes}
+    report["checks"] = ("per-step loss of every rank and final parameters of every group vs the reference's DDP run; "
+                        "parameters bit-identical across the ranks of a group; no expired peer wait")
+    return report, ok
+
+
+def allreduce_section(ctx, args):
+    """BASELINE metric #2 at the DDP message sizes: NCCL on the subgroup communicator (mdt_allreduce_bench) and the
+    repo's own peer-memory exchange + Adam kernel(s) (mdt_engine_exchange_bench), all groups of a layout concurrently.
+    busbw = (S / t) * 2(n-1)/n against 900 GB/s per direction."""
+    import ctypes as C
+    torch, dist = ctx.torch, ctx.dist
+    from multidisttorch_b200 import _lib
+    from multidisttorch_b200.engine import VAEEngine, nccl_comm_ptr
+    lib = _lib.load()
+    out = {}
+    k = 2
+    while k <= ctx.world:
+        ng = ctx.world // k
+        groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]
+        mine = groups[ctx.rank // k]
+        comm = nccl_comm_ptr(mine, ctx.device)
+        entry = {}
+        buf = torch.ones(max(DDP_SIZES.values()) // 4, dtype=torch.float32, device=ctx.device)
+        for name, nbytes in DDP_SIZES.items():
+            sec = C.c_double()
+            ctx.barrier()
+            _lib.check(lib.mdt_allreduce_bench(C.c_void_p(comm), C.c_void_p(buf.data_ptr()), nbytes, 20,
+                                               C.c_void_p(torch.cuda.current_stream().cuda_stream), C.byref(sec)))
+            t = ctx.max(sec.value)
+            entry[f"nccl/{name}"] = {"bytes": nbytes, "us": round(t * 1e6, 2), "busbw_GBps": round(nbytes / t * 2 * (k - 1) / k / 1e9, 2)}
+        for H, name in ((400, "flat_H400"), (4096, "flat_H4096")):
+            for xch in ("p2p", "p2p_two_shot"):
+                eng = VAEEngine(hidden=H, max_batch=8, gemm_mode="tf32x3", group=mine, exchange=xch)
+                if eng.p2p:
+                    ctx.barrier()
+                    t = ctx.max(eng.exchange_bench(20))
+                    nbytes = eng.total * 4
+                    entry[f"{xch}+adam/{name}"] = {"bytes": nbytes, "us": round(t * 1e6, 2),
+                                                   "busbw_GBps": round(nbytes / t * 2 * (k - 1) / k / 1e9, 2)}
+                eng.close()
+        out[f"{ng}x{k}"] = entry
+        k *= 2
+    out["note"] = ("fp32 SUM, in place, all groups of a layout concurrently, max over ranks; '+adam' rows time the fused peer-memory "
+                   "exchange + optimizer pass (28 B/element of optimizer traffic included), so their bus GB/s is a lower bound")
+    return out
+
+
 def run_own(args):
-    import torch
-    import torch.distributed as dist
+    ctx = Ctx(args)
+    torch, dist = ctx.torch, ctx.dist
+    rank, world, device = ctx.rank, ctx.world, ctx.device
+    from multidisttorch_b200 import synth
     from multidisttorch_b200.engine import VAEEngine, train_step_many
-
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", str(rank)))
-    if world != args.gpus:
-        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py (own arm) needs a CUDA device: there is no CPU fallback")
-    torch.cuda.set_device(local)
-    device = torch.device("cuda", local)
-    if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        dist.init_process_group("nccl", init_method="env://", device_id=device)
-
-    def barrier():
-        if world > 1:
-            dist.barrier(device_ids=[local])
-        torch.cuda.synchronize()
-
-    def max_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return float(t.item())
-
-    def sum_over_ranks(v):
-        if world == 1:
-            return v
-        t = torch.tensor([v], dtype=torch.float64, device=device)
-        dist.all_reduce(t, op=dist.ReduceOp.SUM)
-        return float(t.item())
 
     B, H, K = args.batch, args.hidden, args.steps
     W = max(args.warmup, 3)
-    from oracle import vae_numpy as O        # deterministic parameter init shared with tests (not a compute path)
-    dims = O.Dims(H=H)
+    R = max(args.repeats, 1)
+    graph = not args.no_graph
+
+    # ---- parity first: golden replay of the reference's DDP runs on this box's GPUs
+    parity, parity_ok = None, True
+    if world > 1 and not args.no_parity:
+        parity, parity_ok = ddp_parity(ctx, args, ["tf32x3"] + (["bf16"] if _has_bf16() else []))
 
     g = torch.Generator(device="cpu").manual_seed(4321 + rank)
     host_pool = torch.rand(HOST_POOL_BATCHES, B, D, generator=g).pin_memory()
     gd = torch.Generator(device=device).manual_seed(4321 + rank)
     pool = torch.rand(POOL_BATCHES, B, D, generator=gd, device=device)
 
-    def timed_run(eng, steps, warm):
-        for i in range(warm):
-            eng.train_step(pool[i % POOL_BATCHES], None, want_loss=False)
-        barrier()
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        n0 = eng.launch_count()
-        ev0.record(eng.stream)
-        for i in range(steps):
-            eng.train_step(pool[i % POOL_BATCHES], None, want_loss=False)
-        ev1.record(eng.stream)
-        eng.synchronize()
-        barrier()
-        return max_over_ranks(ev0.elapsed_time(ev1)), eng.launch_count() - n0
+    def new_engine(mode, hidden=H, batch=B, group=None, seed=None, **kw):
+        e = VAEEngine(hidden=hidden, max_batch=batch, gemm_mode=mode, use_graph=graph, group=group, **kw)
+        e.load_segments(synth.init_params(1234 + rank if seed is None else seed, H=hidden))
+        e.set_rng(1234 + rank, 0)
+        if group is not None:
+            e.broadcast_params()
+        return e
 
-    eng = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph)
-    eng.load_segments(O.init_params(1234 + rank, dims))
-    eng.set_rng(1234 + rank, 0)
+    def pool_enqueue(eng, p=pool):
+        return lambda first, n: eng.train_steps(p, first % p.shape[0], n)
 
-    clocks = ClockSampler(local) if rank == 0 else None
+    eng = new_engine(args.gemm_mode)
+    clocks = ClockSampler(ctx.local) if rank == 0 else None
     if clocks:
         clocks.mark()
-    ms, launches = timed_run(eng, K, W)
+    ms_step, all_ms, launches, n_region = timed_regions(ctx, eng, pool_enqueue(eng), K, W, R)
     if clocks:
         clocks.mark()
     clk = clocks.stop() if clocks else None
-    value = world * B * K / (ms * 1e-3)
+    value = world * B / (ms_step * 1e-3)
+
+    # the same steps enqueued one C-ABI call per step (mdt_train_step with the caller's pointer), for comparison
+    def per_call(first, n):
+        for i in range(n):
+            eng.train_step(pool[(first + i) % POOL_BATCHES], None, want_loss=False)
+    ms_call, _, _, _ = timed_regions(ctx, eng, per_call, K, W, max(R // 2, 1))
 
     # ---- e2e: host buffers through the C-ABI, copies inside the timed region.  Every step reads its x from pinned
     # host memory and hands its loss back to the host.  Two ways a caller drives it: (1) train_step_host, the
     # reference's loop literally (loss.item() before the next batch is touched) -> "sync_value"; (2) submit / wait with
     # one step in flight ahead (a prefetching loader + reading the previous step's loss) -> "value", the headline.
-    for i in range(W):
-        eng.train_step_host(host_pool[i % HOST_POOL_BATCHES])
-    barrier()
-    t0 = time.perf_counter()
-    loss = 0.0
-    for i in range(K):
-        loss = eng.train_step_host(host_pool[i % HOST_POOL_BATCHES])
-    torch.cuda.synchronize()
-    sync_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
-    t0 = time.perf_counter()
-    prev = eng.submit_host(host_pool[0])
-    for i in range(1, K):
-        cur = eng.submit_host(host_pool[i % HOST_POOL_BATCHES])
-        loss = eng.wait_host(prev)
-        prev = cur
-    loss = eng.wait_host(prev)
-    torch.cuda.synchronize()
-    e2e_s = max_over_ranks(time.perf_counter() - t0)
-    barrier()
-    e2e = {"value": world * B * K / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * D * 4, "d2h_bytes_per_step": 4,
-           "ms_per_step": e2e_s * 1e3 / K, "last_loss": loss,
+    n_e2e = max(K, MIN_TIMED_STEPS)
+
+    def e2e_sync(n):
+        loss = 0.0
+        for i in range(n):
+            loss = eng.train_step_host(host_pool[i % HOST_POOL_BATCHES])
+        return loss
+
+    def e2e_pipelined(n):
+        prev = eng.submit_host(host_pool[0])
+        loss = 0.0
+        for i in range(1, n):
+            cur = eng.submit_host(host_pool[i % HOST_POOL_BATCHES])
+            loss = eng.wait_host(prev)
+            prev = cur
+        return eng.wait_host(prev) if n > 0 else loss
+
+    def wall(fn, n):
+        ts = []
+        loss = 0.0
+        for _ in range(max(R // 2, 3)):
+            ctx.barrier()
+            t0 = time.perf_counter()
+            loss = fn(n)
+            torch.cuda.synchronize()
+            ts.append(ctx.max(time.perf_counter() - t0) / n)
+        ctx.barrier()
+        return statistics.median(ts), loss
+
+    e2e_sync(W)
+    e2e_pipelined(max(W, 8))               # warm the submit / wait path itself (copy stream, staging ring, mailbox)
+    sync_s, _ = wall(e2e_sync, n_e2e)
+    e2e_s, loss = wall(e2e_pipelined, n_e2e)
+    e2e = {"value": world * B / e2e_s, "unit": UNIT, "h2d_bytes_per_step": B * D * 4, "d2h_bytes_per_step": 4,
+           "ms_per_step": e2e_s * 1e3, "last_loss": loss, "steps_per_region": n_e2e,
            "how": "mdt_train_step_host_submit / _wait, one step in flight ahead; each step's x goes from pinned host "
                   "memory to the device inside the timed region (DMA on a copy stream behind the step in flight), each "
-                  "step's loss is read by the host from the device-written mailbox",
-           "sync_value": world * B * K / sync_s, "sync_ms_per_step": sync_s * 1e3 / K}
+                  "step's loss is read by the host from the device-written mailbox; wall clock, max over ranks, median of regions",
+           "sync_value": world * B / sync_s, "sync_ms_per_step": sync_s * 1e3}
+
     # ---- per-kernel device time (un-graphed, event after each kernel) -> roofline of the dominant kernel
     roofline = None
     kernels = None
+    peaks, peak, peak_src = load_peaks()
     if rank == 0:
         prof = eng.profile_step(pool[0], iters=30)
         null_ms = next((t for n, t in prof if n == "_null"), 0.0)      # launch + event overhead of an empty kernel
@@ -309,7 +491,6 @@ def run_own(args):
         kernels = [{"kernel": n, "avg_us": round(t * 1e3, 3), "share": round(t / tot, 4),
                     "alg_bytes": algorithmic_bytes(n, B, H, eng.total)} for n, t in prof]
         name, t_ms = max(prof, key=lambda r: r[1])
-        peak, peak_src = load_peaks()
         ab = algorithmic_bytes(name, B, H, eng.total)
         ach = ab / (t_ms * 1e-3) / 1e9
         traffic = None
@@ -322,150 +503,463 @@ def run_own(args):
                     "how": "CUDA events on the engine stream around every kernel of 30 un-graphed steps, minus the interval "
                            "of an empty kernel (launch + event overhead); side-stream overlap disabled while timing",
                     "step": {"alg_bytes": step_bytes(B, H), "flops": step_flops(B, H),
-                             "achieved_GBps": round(step_bytes(B, H) / (ms * 1e-3 / K) / 1e9, 2),
-                             "frac_of_hbm_peak": round(step_bytes(B, H) / (ms * 1e-3 / K) / 1e9 / peak, 5)}}
+                             "achieved_GBps": round(step_bytes(B, H) / (ms_step * 1e-3) / 1e9, 2),
+                             "frac_of_hbm_peak": round(step_bytes(B, H) / (ms_step * 1e-3) / 1e9 / peak, 5)}}
+    eng.close()
+
+    short = min(K, 1000)
     # ---- the other GEMM modes, for reference (short runs)
     modes = {args.gemm_mode: round(value, 1)}
     if world == 1 and not args.no_modes:
-        for m in ("fp32", "tf32", "tf32x3"):
-            if m in modes:
+        for m in ("fp32", "tf32", "tf32x3", "bf16"):
+            if m in modes or (m == "bf16" and not _has_bf16()):
                 continue
-            em = VAEEngine(hidden=H, max_batch=B, gemm_mode=m, use_graph=not args.no_graph)
-            em.load_segments(O.init_params(1234 + rank, dims))
-            em.set_rng(1234 + rank, 0)
-            msm, _ = timed_run(em, min(K, 2000), W)
-            modes[m] = round(world * B * min(K, 2000) / (msm * 1e-3), 1)
+            em = new_engine(m)
+            msm, _, _, _ = timed_regions(ctx, em, pool_enqueue(em), short, W, 3)
+            modes[m] = round(world * B / (msm * 1e-3), 1)
             em.close()
-    # ---- SURVEY section 8f-3 (next row): several independent trials per GPU, each its own engine, stream and CUDA graph,
-    #      stepped round-robin from this process; the kernels of different trials overlap on idle SMs
+    # ---- SURVEY section 8f-3 (next row): several independent trials per GPU
     multi_trial = None
     if world == 1 and not args.no_modes:
         multi_trial = {"1": round(value, 1)}
         for T in (2, 4, 8):
-            engs = []
-            for t in range(T):
-                et_ = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph)
-                et_.load_segments(O.init_params(2000 + t, dims))
-                et_.set_rng(2000 + t, 0)
-                engs.append(et_)
-            Km = min(K, 2000)
+            engs = [new_engine(args.gemm_mode, seed=2000 + t) for t in range(T)]
+            Km = max(short, MIN_TIMED_STEPS)
             for i in range(W):
                 train_step_many(engs, [pool[(i * T + t) % POOL_BATCHES] for t in range(T)])
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            for i in range(Km):
-                train_step_many(engs, [pool[(i * T + t) % POOL_BATCHES] for t in range(T)])
-            torch.cuda.synchronize()
-            dt = time.perf_counter() - t0
-            multi_trial[str(T)] = round(T * B * Km / dt, 1)
+            ts = []
+            for _ in range(3):
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()
+                for i in range(Km):
+                    train_step_many(engs, [pool[(i * T + t) % POOL_BATCHES] for t in range(T)])
+                torch.cuda.synchronize()
+                ts.append(time.perf_counter() - t0)
+            multi_trial[str(T)] = round(T * B * Km / statistics.median(ts), 1)
             for e_ in engs:
                 e_.close()
-    eng.close()
 
-    # ---- other group layouts (gradient all-reduce inside each group)
+    # ---- other group layouts (gradient exchange inside each group), BASELINE configs 4 and 5, metric #2
     layouts = {f"{world}x1": round(value, 1)}
+    layouts_bf16, exchanges, allreduce, config5 = None, None, None, None
     if world > 1 and not args.no_layouts:
+        exchanges = {}
+        if _has_bf16():
+            layouts_bf16 = {}
         k = 2
         while k <= world:
             ng = world // k
             groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]
             mine = groups[rank // k]
-            e2 = VAEEngine(hidden=H, max_batch=B, gemm_mode=args.gemm_mode, use_graph=not args.no_graph, group=mine)
-            e2.load_segments(O.init_params(1234 + rank // k, dims))
-            e2.set_rng(1234 + rank, 0)
-            e2.broadcast_params()
-            ms2, _ = timed_run(e2, K, W)
-            layouts[f"{ng}x{k}"] = round(world * B * K / (ms2 * 1e-3), 1)
+            best = None
+            per = {}
+            for xch in ("p2p", "p2p_two_shot", "nccl"):
+                e2 = new_engine(args.gemm_mode, group=mine, seed=1234 + rank // k, exchange=xch)
+                if xch == "nccl" or e2.p2p:
+                    ms2, _, _, _ = timed_regions(ctx, e2, pool_enqueue(e2), short, W, 3)
+                    per[xch] = round(world * B / (ms2 * 1e-3), 1)
+                e2.close()
+            e2 = new_engine(args.gemm_mode, group=mine, seed=1234 + rank // k)      # the shipped (automatic) choice
+            ms2, _, _, _ = timed_regions(ctx, e2, pool_enqueue(e2), short, W, 3)
             e2.close()
+            layouts[f"{ng}x{k}"] = round(world * B / (ms2 * 1e-3), 1)
+            exchanges[f"{ng}x{k}"] = per
+            if layouts_bf16 is not None:          # BASELINE config 4 names bf16 GEMMs (2 trials x 4-GPU groups at N = 8)
+                e3 = new_engine("bf16", group=mine, seed=1234 + rank // k)
+                ms3, _, _, _ = timed_regions(ctx, e3, pool_enqueue(e3), short, W, 3)
+                e3.close()
+                layouts_bf16[f"{ng}x{k}"] = round(world * B / (ms3 * 1e-3), 1)
             k *= 2
+        allreduce = allreduce_section(ctx, args)
+        if world == 8:
+            config5 = run_config5(ctx, args, new_engine, peaks)
 
-    total_launches = sum_over_ranks(launches)
+    total_launches = ctx.sum(launches)
+
+    # ---- comparison lines at N = 1: the unchanged reference step on torch-CUDA eager, and the drop-in's compat path
+    eager, compat = None, None
+    if not args.no_eager:
+        eager = run_eager(ctx, args, B, H)
+    if world == 1 and not args.no_modes:
+        compat = run_compat(ctx, args, B, H, pool)
 
     cpu_baseline = None
-    if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cpu_baseline = run_reference(1, B, H, steps=None, warmup=5, seconds=args.cpu_seconds)["cpu_baseline"]
+    if not args.no_cpu_baseline:
+        # rank 0 times the reference's CPU path on the host cores while the other ranks sleep on a store key (a NCCL
+        # barrier would keep their host threads spinning on the cores being measured)
+        if rank == 0:
+            cpu_baseline = run_reference(world, B, H, steps=None, warmup=5, seconds=args.cpu_seconds)["cpu_baseline"]
+        if world > 1:
+            store = dist.distributed_c10d._get_default_store()
+            if rank == 0:
+                store.set("mdt_cpu_baseline_done", "1")
+            else:
+                from datetime import timedelta
+                store.wait(["mdt_cpu_baseline_done"], timedelta(seconds=900))
 
     if rank == 0:
         out = {
             "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
-            "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-            "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(world, B, H), "layout": f"{world}x1", "batch_per_gpu": B, "hidden": H,
-                       "gemm_mode": args.gemm_mode, "cuda_graph": not args.no_graph,
-                       "l2": f"inputs cycle through a {POOL_BATCHES}-batch device pool ({POOL_BATCHES * B * D * 4 / 1e6:.0f} MB > 126 MB L2); "
-                             "parameters and optimizer state are step-to-step resident by the nature of training",
-                       "eps": "Philox in-kernel (torch-CUDA-compatible stream)"},
-            "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches), "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "layouts": layouts, "modes": modes,
-            "trials_per_gpu": multi_trial, "kernels": kernels,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.gemm_mode != "bf16" else "bf16", "gemm": args.gemm_mode, "data": "synthetic",
+            "config": config_of(world, B, H),
+            "arm": {"gemm_mode": args.gemm_mode,
+                    "gemm_note": "tf32x3 = three tcgen05 kind::tf32 passes (hi*hi + hi*lo + lo*hi) with fp32 promotion: fp32-grade products, fp32 storage",
+                    "cuda_graph": graph,
+                    "api": "mdt_train_steps: graphs of 8 steps each, the batch index advances in device memory",
+                    "l2": f"inputs cycle through a {POOL_BATCHES}-batch device pool ({POOL_BATCHES * B * D * 4 / 1e6:.0f} MB > 126 MB L2); "
+                          "parameters and optimizer state are step-to-step resident by the nature of training",
+                    "eps": "Philox in-kernel (torch-CUDA-compatible stream)"},
+            "timing": {"repeats": R, "steps_per_region": n_region, "ms_per_step_regions": [round(t, 6) for t in all_ms],
+                       "statistic": "median over regions of (CUDA-event time, max over ranks) / steps",
+                       "one_call_per_step_ms": ms_call, "one_call_per_step_value": round(world * B / (ms_call * 1e-3), 1)},
+            "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches),
+            "gpu_launches_per_step": round(total_launches / (world * R * n_region), 2), "roofline": roofline,
+            "cpu_baseline": cpu_baseline, "ddp_parity": parity, "layouts": layouts, "layouts_bf16": layouts_bf16,
+            "exchanges": exchanges, "allreduce": allreduce, "config5": config5, "modes": modes,
+            "trials_per_gpu": multi_trial, "torch_cuda_eager": eager, "compat_mode": compat, "kernels": kernels,
         }
         emit(out)
+    if world > 1:
+        dist.barrier(device_ids=[ctx.local])
+        dist.destroy_process_group()
+    if not parity_ok:
+        raise SystemExit("ddp_parity FAILED (see the JSON line)")
+
+
+def _has_bf16():
+    from multidisttorch_b200 import _lib
+    return "bf16" in _lib.MDT_GEMM
+
+
+def run_config5(ctx, args, new_engine, peaks):
+    """BASELINE config 5: ONE 8-GPU DDP group, hidden width 4096, per-rank batch 128 / 1024 / 8192."""
+    torch, dist = ctx.torch, ctx.dist
+    H5 = 4096
+    out = {}
+    world = ctx.world
+    group = dist.new_group(ranks=list(range(world)))
+    P = 2 * D * H5 + 3 * Z * H5 + 2 * H5 + 2 * Z + D
+    for Bc in (128, 1024, 8192):
+        nb = max(2, min(16, (256 << 20) // (Bc * D * 4)))
+        gd = torch.Generator(device=ctx.device).manual_seed(99 + ctx.rank)
+        pool5 = torch.rand(nb, Bc, D, generator=gd, device=ctx.device)
+        entry = {}
+        modes = ["tf32x3"] + (["bf16"] if _has_bf16() else [])
+        for mode in modes:
+            for xch in ("auto", "nccl"):
+                e5 = new_engine(mode, hidden=H5, batch=Bc, group=group, seed=77, exchange=xch)
+                steps = 40 if Bc <= 1024 else 12
+                enq = lambda first, n, e=e5: e.train_steps(pool5, first % nb, n)
+                enq(0, 5)
+                ts = []
+                for _ in range(3):
+                    ctx.barrier()
+                    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    ev0.record(e5.stream)
+                    enq(0, steps)
+                    ev1.record(e5.stream)
+                    e5.synchronize()
+                    ctx.barrier()
+                    ts.append(ctx.max(ev0.elapsed_time(ev1)) / steps)
+                ms = statistics.median(ts)
+                used = "nccl" if xch == "nccl" or not e5.p2p else "peer memory (automatic one-/two-shot choice)"
+                a = 2 if mode == "bf16" else 4
+                flops = step_flops(Bc, H5)
+                entry[f"{mode}/{xch}"] = {"samples_per_s": round(world * Bc / (ms * 1e-3), 1), "us_per_step": round(ms * 1e3, 1),
+                                          "exchange": used, "gradient_bytes": 4 * P,
+                                          "hbm_roofline_frac": round(step_bytes(Bc, H5, a) / (ms * 1e-3) / 1e9 / float(peaks.get("hbm_gbs", 6650.0)), 4),
+                                          "tflops": round(flops / (ms * 1e-3) / 1e12, 2)}
+                e5.close()
+        out[f"B{Bc}"] = entry
+        del pool5
+    out["note"] = ("1x8 layout, H=4096, Adam; samples/s whole box; hbm_roofline_frac = SURVEY 8(d) step bytes / time / measured HBM peak; "
+                   "tflops = 2*B*(5DH+9ZH) / time per GPU")
+    return out
+
+
+# --------------------------------------------------------------------------------------------
+# the unchanged reference step on torch-CUDA eager (+ NCCL), SURVEY section 8(d) "beat this" line
+# --------------------------------------------------------------------------------------------
+def load_ref_model():
+    """(module with VAE / loss_function, kind): the reference's own vae-hpo.py when oracle/_ref (or /root/reference)
+    holds it, else the torch port."""
+    try:
+        from oracle import ref_loader
+        m = ref_loader.load_vae_hpo()
+        if m is not None:
+            return m, "reference"
+    except Exception as exc:       # e.g. torchvision missing
+        print(f"[bench] reference module not loadable ({exc}); using the torch port", file=sys.stderr)
+    from oracle import torch_port as TP
+
+    class _Port:
+        VAE = TP.VAEPort
+        loss_function = staticmethod(TP.loss_port)
+    return _Port, "port"
+
+
+def eager_worker(args):
+    """One GPU rank: ref:vae-hpo.py:129-131 + 67-74 on torch CUDA (TF32 off), synthetic device-resident batches."""
+    spec = json.loads(args.eager_worker)
+    import torch
+    import torch.distributed as dist
+    ref, kind = load_ref_model()
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.backends.cudnn.allow_tf32 = False
+    dev = torch.device("cuda")
+    rank, world = spec["rank"], spec["world"]
+    group = None
+    if world > 1:
+        dist.init_process_group("nccl", init_method=f"tcp://127.0.0.1:{spec['port']}", rank=rank, world_size=world,
+                                device_id=torch.device("cuda", 0))
+    torch.manual_seed(1234 + rank)
+    model = ref.VAE().to(dev)
+    if world > 1:
+        k = spec["group_size"]
+        groups = [dist.new_group(ranks=list(range(k * g, k * g + k))) for g in range(world // k)]
+        group = groups[rank // k]
+        model = torch.nn.parallel.DistributedDataParallel(model, process_group=group)
+    opt = torch.optim.Adam(model.parameters(), lr=1e-3)
+    g = torch.Generator(device=dev).manual_seed(4321 + rank)
+    batches = [torch.rand(spec["batch"], 1, 28, 28, generator=g, device=dev) for _ in range(64)]
+
+    def step(x):
+        opt.zero_grad()
+        recon, mu, logvar = model(x)
+        loss = ref.loss_function(recon, x, mu, logvar)
+        loss.backward()
+        v = loss.item()
+        opt.step()
+        return v
+
+    for i in range(spec["warmup"]):
+        step(batches[i % 64])
+    ts = []
+    for _ in range(3):
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        t0 = time.perf_counter()
+        for i in range(spec["steps"]):
+            step(batches[i % 64])
+        torch.cuda.synchronize()
+        ts.append((time.perf_counter() - t0) / spec["steps"])
+    with open(os.path.join(spec["out"], f"rank{rank}.json"), "w") as f:
+        json.dump({"s_per_step": statistics.median(ts), "kind": kind}, f)
     if world > 1:
         dist.destroy_process_group()
 
 
+def run_eager(ctx, args, B, H):
+    """Every rank of this bench launches one worker on its own GPU (CUDA_VISIBLE_DEVICES = its local rank: the reference
+    uses the bare "cuda" device).  Layouts: Nx1 and, for N > 1, 1xN (one DDP group over NCCL)."""
+    if H != 400:
+        return None          # the reference's VAE is 784-400-20
+    out_dir = None
+    res = {}
+    for gsize in ([1] if ctx.world == 1 else [1, ctx.world]):
+        if ctx.rank == 0:
+            out_dir = tempfile.mkdtemp(prefix="mdt_eager_")
+        if ctx.world > 1:
+            box = [out_dir]
+            ctx.dist.broadcast_object_list(box, src=0)
+            out_dir = box[0]
+        import zlib
+        port = 23000 + (zlib.crc32(str(out_dir).encode()) % 20000)      # same on every rank (out_dir was broadcast)
+        spec = {"rank": ctx.rank, "world": ctx.world if gsize > 1 else 1, "group_size": gsize, "batch": B, "warmup": 20,
+                "steps": 200, "out": out_dir, "port": port}
+        if gsize == 1:
+            spec["rank"] = 0
+            spec["out"] = tempfile.mkdtemp(prefix="mdt_eager_r_")
+        env = dict(os.environ)
+        for k in list(env):
+            if k.startswith("TORCHELASTIC") or k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK",
+                                                     "GROUP_WORLD_SIZE", "ROLE_RANK", "ROLE_WORLD_SIZE", "ROLE_NAME",
+                                                     "MASTER_ADDR", "MASTER_PORT"):
+                env.pop(k)
+        env.update(CUDA_VISIBLE_DEVICES=str(ctx.local), MDT_DROPIN="0", NVIDIA_TF32_OVERRIDE="0",
+                   PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
+        p = subprocess.run([sys.executable, os.path.abspath(__file__), "--eager-worker", json.dumps(spec)], env=env,
+                           stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True, timeout=600)
+        s_step, kind = float("nan"), "?"
+        if p.returncode == 0:
+            j = json.load(open(os.path.join(spec["out"], f"rank{spec['rank']}.json")))
+            s_step, kind = j["s_per_step"], j["kind"]
+        else:
+            print(f"[bench eager] worker failed on rank {ctx.rank}:\n{p.stderr[-1500:]}", file=sys.stderr)
+        worst = ctx.max(s_step if s_step == s_step else 1e9)
+        layout = f"{ctx.world}x1" if gsize == 1 else f"1x{ctx.world}"
+        res[layout] = {"value": round(ctx.world * B / worst, 1), "ms_per_step": round(worst * 1e3, 4)} if worst < 1e8 else {"error": "worker failed"}
+        res["kind"] = kind
+    res["what"] = ("the reference's own step (VAE, loss_function, torch DDP over NCCL, optim.Adam, loss.item() every step) on these "
+                   "GPUs through torch eager, TF32 off, device-resident synthetic batches; wall clock, max over ranks, median of 3 x 200 steps")
+    return res
+
+
+def run_compat(ctx, args, B, H, pool):
+    """The path the UNCHANGED vae-hpo.py takes through the drop-in: engine forward -> the script's own loss_function in
+    torch -> mdt_backward -> mdt_allreduce_grads -> flat Adam kernel (no fused loss, no fused Adam)."""
+    if H != 400:
+        return None
+    torch = ctx.torch
+    from multidisttorch_b200 import dropin
+    ref, kind = load_ref_model()
+    installed = dropin.install()
+    try:
+        torch.manual_seed(1234)
+        model = ref.VAE().to(ctx.device)
+        wrapped = torch.nn.parallel.DistributedDataParallel(model, process_group=None)
+        if not isinstance(wrapped, dropin.EngineModule):
+            return {"error": "the drop-in did not take the model"}
+        opt = torch.optim.Adam(wrapped.parameters(), lr=1e-3)
+        xs = [pool[i].view(B, 1, 28, 28) for i in range(64)]
+
+        def step(x):
+            opt.zero_grad()
+            recon, mu, logvar = wrapped(x)
+            loss = ref.loss_function(recon, x, mu, logvar)
+            loss.backward()
+            v = loss.item()
+            opt.step()
+            return v
+
+        wrapped.train()
+        for i in range(20):
+            step(xs[i % 64])
+        ts = []
+        for _ in range(3):
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for i in range(200):
+                step(xs[i % 64])
+            torch.cuda.synchronize()
+            ts.append((time.perf_counter() - t0) / 200)
+        s = statistics.median(ts)
+        wrapped.engine.close()
+        return {"value": round(B / s, 1), "ms_per_step": round(s * 1e3, 4), "model": kind,
+                "what": "unchanged-script path: DistributedDataParallel / optim.Adam replaced by the drop-in, the script's own "
+                        "loss_function + loss.item() in torch; wall clock, median of 3 x 200 steps"}
+    finally:
+        if installed:
+            dropin.uninstall()
+
+
 # --------------------------------------------------------------------------------------------
-# reference arm: the reference's CPU/gloo path (torch port, oracle/torch_port.py) on the host cores
+# reference arm: the reference's CPU/gloo path on the host cores
 # --------------------------------------------------------------------------------------------
 def ref_worker(args):
-    """One CPU rank: utils-style bootstrap, DDP over gloo, Adam -- ref:vae-hpo.py:122-131 + 69-74."""
+    """One CPU rank: utils-style bootstrap, DDP over gloo, Adam -- ref:vae-hpo.py:122-131 + 69-74.  Runs the reference's
+    OWN modules (utils.setup_ddp / setup_ddp_groups, VAE, loss_function) when oracle/_ref or /root/reference holds
+    them; the torch port otherwise."""
     import torch
     import torch.distributed as dist
     from oracle import torch_port as TP
-    from utils import setup_ddp, setup_ddp_groups          # this repo's drop-in utils (gloo leg)
 
     spec = json.loads(args.ref_worker)
     torch.set_num_threads(spec["threads"])
-    size, rank = setup_ddp()
-    groups = setup_ddp_groups(spec["ngroups"])
+    ref, kind = load_ref_model()
+    if kind == "reference" and spec["hidden"] == 400:
+        size, rank = ref.setup_ddp()
+        groups = ref.setup_ddp_groups(spec["ngroups"])
+        make_model = ref.VAE
+        loss_fn = ref.loss_function
+    else:
+        kind = "port"
+        from utils import setup_ddp, setup_ddp_groups          # this repo's drop-in utils (gloo leg)
+        size, rank = setup_ddp()
+        groups = setup_ddp_groups(spec["ngroups"])
+        make_model = lambda: TP.VAEPort(D, spec["hidden"], Z)
+        loss_fn = TP.loss_port
     group = next(gr for gr in groups if dist.get_rank(gr) >= 0)
     torch.manual_seed(1234 + rank)
-    model = TP.VAEPort(D, spec["hidden"], Z)
-    model = torch.nn.parallel.DistributedDataParallel(model, process_group=group)
+    model = torch.nn.parallel.DistributedDataParallel(make_model(), process_group=group)
     opt = torch.optim.Adam(model.parameters(), lr=1e-3)
     g = torch.Generator().manual_seed(4321 + rank)
     batches = [torch.rand(spec["batch"], 1, 28, 28, generator=g) for _ in range(16)]
-    n, dt = TP.timed_steps(model, opt, batches, spec["warmup"], spec["steps"], spec["seconds"], barrier=dist.barrier)
+
+    def step(x):                    # ref:vae-hpo.py:69-74
+        opt.zero_grad()
+        recon, mu, logvar = model(x)
+        loss = loss_fn(recon, x, mu, logvar)
+        loss.backward()
+        v = loss.item()
+        opt.step()
+        return v
+
+    for i in range(spec["warmup"]):
+        step(batches[i % 16])
+    dist.barrier()
+    t0 = time.perf_counter()
+    done = 0
+    while True:
+        step(batches[done % 16])
+        done += 1
+        if spec["steps"] is not None and done >= spec["steps"]:
+            break
+        if spec["steps"] is None and time.perf_counter() - t0 >= spec["seconds"]:
+            break
+    dist.barrier()
+    dt = time.perf_counter() - t0
     with open(os.path.join(spec["out"], f"rank{rank}.json"), "w") as f:
-        json.dump({"steps": n, "seconds": dt}, f)
+        json.dump({"steps": done, "seconds": dt, "kind": kind}, f)
     dist.destroy_process_group()
+
+
+_LAUNCHER_VARS = ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE", "ROLE_RANK",
+                  "ROLE_WORLD_SIZE", "ROLE_NAME", "SLURM_NPROCS", "SLURM_PROCID", "SLURM_NODELIST", "LSB_HOSTS",
+                  "LSB_MCPU_HOSTS", "OMP_NUM_THREADS", "MASTER_ADDR", "MASTER_PORT")
 
 
 def run_reference(n, B, H, steps, warmup, seconds):
     cores = os.cpu_count() or 1
     threads = max(cores // n, 1)
     out = tempfile.mkdtemp(prefix="mdt_ref_")
-    port = 20000 + (os.getpid() % 20000)
+    import socket
+    with socket.socket(socket.AF_INET, socket.SOCK_STREAM) as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
     spec = {"threads": threads, "ngroups": n, "hidden": H, "batch": B, "warmup": warmup, "steps": steps,
             "seconds": seconds, "out": out}
     procs = []
     for r in range(n):
         env = dict(os.environ)
-        for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "SLURM_NPROCS", "SLURM_PROCID", "SLURM_NODELIST", "LSB_HOSTS",
-                  "LSB_MCPU_HOSTS", "TORCHELASTIC_RUN_ID"):
-            env.pop(k, None)
+        # nothing of the launcher that started THIS process may leak into the CPU workers: with torchrun's
+        # TORCHELASTIC_USE_AGENT_STORE=True a worker would wait for a TCPStore on the new port that nobody serves
+        for k in list(env):
+            if k.startswith("TORCHELASTIC") or k.startswith("TORCH_NCCL") or k in _LAUNCHER_VARS:
+                env.pop(k)
         env.update(OMPI_COMM_WORLD_SIZE=str(n), OMPI_COMM_WORLD_RANK=str(r), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
                    DDP_BACKEND="gloo", CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS=str(threads), MDT_DROPIN="0",
                    PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
         procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--ref-worker", json.dumps(spec)],
                                       env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE, text=True))
+    limit = 120 + (seconds or 0) * 4 + (steps or 0) * 2
     for p in procs:
-        _, err = p.communicate(timeout=1800)
+        try:
+            _, err = p.communicate(timeout=limit)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise RuntimeError(f"reference worker did not finish within {limit:.0f} s")
         if p.returncode != 0:
             raise RuntimeError(f"reference worker failed:\n{err[-2000:]}")
     res = [json.load(open(os.path.join(out, f"rank{r}.json"))) for r in range(n)]
     n_steps = min(r["steps"] for r in res)
     dt = max(r["seconds"] for r in res)
+    kind = res[0]["kind"]
     value = n * B * n_steps / dt
     cpu_model = ""
     try:
         cpu_model = next(l.split(":", 1)[1].strip() for l in open("/proc/cpuinfo") if l.startswith("model name"))
     except Exception:
         pass
-    sample = (f"{n_steps} training steps of batch {B} per rank on {n} CPU rank(s) x {threads} thread(s) (torch {_torch_version()} CPU, "
+    what = ("the reference's own utils.setup_ddp/_groups, VAE, loss_function" if kind == "reference"
+            else "torch port of the reference step (oracle/torch_port.py)")
+    sample = (f"{n_steps} training steps of batch {B} per rank on {n} CPU rank(s) x {threads} thread(s) ({what}; torch {_torch_version()} CPU, "
               f"DDP over gloo, {n}x1 layout), {dt:.1f} s; same synthetic U[0,1) data shape as the GPU arm")
     return {"value": value, "steps": n_steps, "seconds": dt,
-            "cpu_baseline": {"value": round(value, 1), "unit": UNIT, "cores": threads * n, "kind": "port", "sample": sample,
+            "cpu_baseline": {"value": round(value, 1), "unit": UNIT, "cores": threads * n, "kind": kind, "sample": sample,
                              "host_cores": cores, "cpu_model": cpu_model, "ms_per_step": dt * 1e3 / n_steps}}
 
 
@@ -480,17 +974,17 @@ def run_reference_arm(args):
         return          # under torchrun only rank 0 runs the CPU arm; the others exit 0 without work
     n, B, H = args.gpus, args.batch, args.hidden
     W = max(min(args.warmup, 20), 3)
-    # bounded sample: at most ~60 s of CPU work, and never more steps than asked for
+    # bounded sample: at most ~45 s of CPU work, and never more steps than asked for
     probe = run_reference(n, B, H, steps=20, warmup=3, seconds=None)
     per_step = probe["seconds"] / probe["steps"]
-    K = max(min(args.steps, int(60.0 / per_step)), 10)
+    K = max(min(args.steps, int(45.0 / per_step)), 10)
     r = run_reference(n, B, H, steps=K, warmup=W, seconds=None)
     out = {
         "impl": "reference", "metric": METRIC, "value": round(r["value"], 1), "unit": UNIT, "n_gpus": n, "steps": r["steps"],
         "warmup": W, "ms_per_step": r["seconds"] * 1e3 / r["steps"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(n, B, H), "layout": f"{n}x1", "batch_per_gpu": B, "hidden": H,
-                   "device": "host CPU cores (no GPU)", "requested_steps": args.steps},
+        "config": config_of(n, B, H),
+        "arm": {"device": "host CPU cores (no GPU)", "requested_steps": args.steps},
         "cpu_baseline": r["cpu_baseline"],
         "e2e": {"value": round(r["value"], 1), "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -520,6 +1014,8 @@ def main():
     args = parse_args()
     if args.ref_worker:
         return ref_worker(args)
+    if args.eager_worker:
+        return eager_worker(args)
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_own(args)

@@ -34,7 +34,7 @@
 extern "C" {
 #endif
 
-#define MDT_VERSION 100 /* 0.1.0 */
+#define MDT_VERSION 200 /* 0.2.0 */
 #define MDT_NUM_SEGMENTS 8
 
 typedef enum mdt_status {
@@ -52,6 +52,14 @@ typedef enum mdt_gemm_mode {
   MDT_GEMM_TF32X3 = 2  /* 3-pass split-TF32 on tcgen05 (fp32-grade accuracy) */
 } mdt_gemm_mode;
 
+/* How a trial group of n > 1 ranks sums its gradients (the DDP reducer of ref:vae-hpo.py:130). */
+typedef enum mdt_exchange {
+  MDT_EXCHANGE_AUTO = 0,         /* peer memory when mdt_engine_set_peers was called (one- or two-shot by size), else NCCL */
+  MDT_EXCHANGE_NCCL = 1,         /* ncclAllReduce on the subgroup communicator even if peers are mapped */
+  MDT_EXCHANGE_P2P_ONE_SHOT = 2, /* every rank reads every peer's whole gradient inside the optimizer kernel */
+  MDT_EXCHANGE_P2P_TWO_SHOT = 3  /* reduce own slice, gather the reduced slices inside the optimizer kernel */
+} mdt_exchange;
+
 typedef enum mdt_act { MDT_ACT_NONE = 0, MDT_ACT_RELU = 1, MDT_ACT_SIGMOID = 2 } mdt_act;
 
 /* Model/trial configuration: VAE(in_dim - hidden - latent), ref:vae-hpo.py:20-27. */
@@ -62,8 +70,26 @@ typedef struct mdt_cfg {
   int32_t max_batch;  /* largest per-rank batch any call will pass */
   int32_t gemm_mode;  /* mdt_gemm_mode */
   int32_t use_graph;  /* 1: capture each (batch size) step into a CUDA graph */
-  int32_t reserved[2];
+  int32_t exchange;   /* mdt_exchange; 0 = automatic */
+  int32_t reserved;   /* 0 */
 } mdt_cfg;
+
+/* SGD hyper-parameters as torch.optim.SGD keeps them (BASELINE north_star (c): "fused per-trial Adam/SGD update"). */
+typedef struct mdt_sgd {
+  double lr, momentum, dampening, weight_decay;
+  int32_t nesterov;
+  int32_t reserved;
+} mdt_sgd;
+
+/* Where mdt_train_steps finds its batches: a device-resident pool of fp32 batches, or a device-resident uint8 image
+ * table plus the sampler's index order (ref:vae-hpo.py:135-150: datasets.MNIST + ToTensor + DistributedSampler). */
+typedef struct mdt_batch_source {
+  const float* x_pool;      /* [n_batches][batch][in_dim] fp32, or NULL to use images_u8 */
+  const uint8_t* images_u8; /* [n_images][in_dim] uint8; x = value / 255 as transforms.ToTensor() does */
+  const int64_t* indices;   /* [n_batches * batch] device int64 sample indices, batch-major */
+  int64_t n_batches;        /* step i of a call reads batch (first_batch + i) % n_batches */
+  int64_t n_images;
+} mdt_batch_source;
 
 /* Adam hyper-parameters as the Python doubles torch.optim.Adam keeps
  * (ref:vae-hpo.py:131: lr=1e-3, defaults beta=(0.9,0.999), eps=1e-8). */
@@ -107,6 +133,10 @@ int mdt_engine_broadcast_params(mdt_engine* e);
  * Replaces: optim.Adam(..., lr=1e-3) state and the CUDA default generator. */
 int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_steps);
 int mdt_engine_set_rng(mdt_engine* e, uint64_t philox_seed, uint64_t philox_offset);
+/* optim.SGD(model.parameters(), lr, momentum, dampening, weight_decay, nesterov) + .step() in place of Adam
+ * (north_star (c); the reference itself only instantiates Adam, ref:vae-hpo.py:131).  exp_avg holds the momentum
+ * buffer, exp_avg_sq is unused.  The update runs as one flat kernel after the gradient exchange (NCCL for groups). */
+int mdt_engine_set_sgd(mdt_engine* e, const mdt_sgd* h, int64_t completed_steps);
 int mdt_engine_get_state(mdt_engine* e, int64_t* completed_steps, uint64_t* philox_offset); /* syncs */
 
 /* Stage buffer the step reads x from ([max_batch, D] fp32).  Writing the batch here
@@ -136,6 +166,15 @@ int mdt_adam_step(mdt_engine* e, float grad_scale);
  *   forward -> BCE+KLD loss -> backward -> group all-reduce -> Adam.
  * `loss_out` (device, may be NULL) receives the summed loss of this rank's batch. */
 int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out);
+
+/* The inner loop of train(), ref:vae-hpo.py:67-74, for `n_steps` consecutive batches of a device-resident source:
+ * step i trains on batch (first_batch + i) % src->n_batches.  The steps are enqueued as CUDA graphs of several steps
+ * each (the batch index lives in device memory and advances by itself, so the graphs are launched unmodified); with
+ * images_u8 the gather + /255 of mdt_gather_u8 happens inside each step's first kernel.  `losses_out` (device,
+ * n_steps floats, or NULL; n_steps <= 4096 when given) receives the per-step losses; the host mailbox of
+ * mdt_train_step_host_wait is fed as well.  Asynchronous. */
+int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64_t first_batch, int n_steps,
+                    float* losses_out);
 
 /* SURVEY section 8f-3 (several independent trials on one GPU): one step of each of `n_trials` engines, every engine on
  * its own stream / CUDA graph so their kernels overlap on idle SMs.  xs[i] is trial i's device batch; eps comes from
@@ -191,10 +230,16 @@ int mdt_engine_launch_count(mdt_engine* e, int64_t* kernels);
 int mdt_engine_exchange_handle(mdt_engine* e, void* handle64);
 int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n);
 /* *enabled: 1 once mdt_engine_set_peers succeeded; *timed_out: 1 if a bounded wait on a peer's flag ever expired (a
- * peer died or never launched its step: the gradients of that step are then not trustworthy).  Synchronises. */
+ * peer died or never launched its step).  The step in which that happens is skipped (parameters and moments
+ * untouched, NaN loss) and every later mdt_train_step* / mdt_forward call on the engine returns MDT_ERR_STATE: the
+ * kernels raise a host-visible flag, so no synchronisation is needed to notice.  This call synchronises. */
 int mdt_engine_exchange_status(mdt_engine* e, int* enabled, int* timed_out);
 /* Back to the NCCL exchange (e.g. when another rank of the group could not map its peers: all ranks must agree). */
 int mdt_engine_disable_peers(mdt_engine* e);
+/* Measurement aid for BASELINE's "subgroup allreduce bus GB/s" on the repo's own exchange: runs the group's gradient
+ * exchange + optimizer kernel(s) `iters` times on the flat gradient (every rank of the group must call it together,
+ * peers mapped) and returns the average seconds per exchange.  The parameters ARE updated (use a scratch engine). */
+int mdt_engine_exchange_bench(mdt_engine* e, int iters, double* seconds);
 
 /* Measurement aid: run `iters` un-graphed training steps on x with a CUDA event after
  * every kernel and write "label avg_ms\n" lines (one per kernel of the step, in launch

@@ -8,16 +8,27 @@ LIB_PATH = os.path.join(_HERE, "csrc", "libmdt_b200.so")
 
 MDT_GEMM = {"fp32": 0, "tf32": 1, "tf32x3": 2}
 MDT_ACT = {"none": 0, "relu": 1, "sigmoid": 2}
+MDT_EXCHANGE = {"auto": 0, "nccl": 1, "p2p": 2, "p2p_two_shot": 3}
 SEGMENTS = ("W1", "b1", "W2x", "b2x", "W3", "b3", "W4", "b4")
 
 
 class mdt_cfg(C.Structure):
     _fields_ = [("in_dim", C.c_int32), ("hidden", C.c_int32), ("latent", C.c_int32), ("max_batch", C.c_int32),
-                ("gemm_mode", C.c_int32), ("use_graph", C.c_int32), ("reserved", C.c_int32 * 2)]
+                ("gemm_mode", C.c_int32), ("use_graph", C.c_int32), ("exchange", C.c_int32), ("reserved", C.c_int32)]
 
 
 class mdt_adam(C.Structure):
     _fields_ = [("lr", C.c_double), ("beta1", C.c_double), ("beta2", C.c_double), ("eps", C.c_double)]
+
+
+class mdt_sgd(C.Structure):
+    _fields_ = [("lr", C.c_double), ("momentum", C.c_double), ("dampening", C.c_double), ("weight_decay", C.c_double),
+                ("nesterov", C.c_int32), ("reserved", C.c_int32)]
+
+
+class mdt_batch_source(C.Structure):
+    _fields_ = [("x_pool", C.c_void_p), ("images_u8", C.c_void_p), ("indices", C.c_void_p), ("n_batches", C.c_int64),
+                ("n_images", C.c_int64)]
 
 
 _P = C.c_void_p
@@ -32,6 +43,9 @@ _PROTOS = {
     "mdt_engine_broadcast_params": (C.c_int, [_P]),
     "mdt_engine_set_adam": (C.c_int, [_P, C.POINTER(mdt_adam), C.c_int64]),
     "mdt_engine_set_rng": (C.c_int, [_P, C.c_uint64, C.c_uint64]),
+    "mdt_engine_set_sgd": (C.c_int, [_P, C.POINTER(mdt_sgd), C.c_int64]),
+    "mdt_train_steps": (C.c_int, [_P, C.POINTER(mdt_batch_source), C.c_int, C.c_int64, C.c_int, _P]),
+    "mdt_engine_exchange_bench": (C.c_int, [_P, C.c_int, C.POINTER(C.c_double)]),
     "mdt_engine_get_state": (C.c_int, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_uint64)]),
     "mdt_engine_input_buffer": (C.c_int, [_P, C.POINTER(_P)]),
     "mdt_forward": (C.c_int, [_P, _P, C.c_int, _P, _P, _P, _P]),

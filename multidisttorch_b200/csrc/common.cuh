@@ -88,16 +88,30 @@ struct StepState {
   unsigned long long* host_mailbox;  // pinned, device-mapped ring of 64 words: slot seq % 64 = (seq << 32) | bits(loss)
   unsigned int xch_seq;              // peer-memory gradient exchanges completed (never reset: the flags are monotonic)
   unsigned int xch_error;            // set when a bounded wait on a peer's flag expired
+  unsigned int* host_error;          // pinned, device-mapped word the host checks before every step (or NULL): receives
+                                     // xch_error, so a failed exchange stops the trial at the next call without a sync
+  long long x_cursor;                // mdt_train_steps: index of the batch the NEXT step reads from the caller's pool /
+                                     // index table; advanced once per published step
+  float* loss_hist;                  // ring of kLossHist per-step losses (slot = (published step count - 1) % kLossHist)
 };
+constexpr unsigned int kLossHist = 4096;
+
+// A bounded wait on a peer expired: remember it on the device and tell the host (one posted store over PCIe).
+__device__ __forceinline__ void flag_exchange_error(StepState* st) {
+  st->xch_error = 1u;
+  if (st->host_error != nullptr) *reinterpret_cast<volatile unsigned int*>(st->host_error) = 1u;
+}
 
 // Called by the one thread that finalises a training step's loss: hands (sequence number, loss) to the host in a
 // single 8-byte store over PCIe, so mdt_train_step_host can poll for it instead of issuing a D2H copy + stream sync.
 __device__ __forceinline__ void publish_loss(StepState* st, float loss) {
   unsigned long long* mb = st->host_mailbox;
-  if (mb == nullptr) return;
   const unsigned int seq = (st->host_seq + 1u) & 0x7fffffffu;   // 31 bits: the host keeps the top bit for tickets of
                                                                   // steps that did not go through the mailbox
   st->host_seq = seq;
+  st->x_cursor += 1;
+  if (st->loss_hist != nullptr) st->loss_hist[(seq - 1u) & (kLossHist - 1u)] = loss;
+  if (mb == nullptr) return;
   // one posted 8-byte store, nothing ordered behind it: no system-scope fence (it would hold the step's last CTA for
   // a PCIe round trip)
   // the mailbox is a ring of 64 words indexed by the sequence number, so the host may have several steps in flight

@@ -363,6 +363,62 @@ __global__ void __launch_bounds__(kAdamThreads) adam_flat_kernel(AdamArgs a) {
   }
 }
 
+// ============================================================================
+// Flat fused SGD (torch.optim.SGD semantics: weight decay, momentum, dampening, Nesterov), north_star (c).
+//   g  = grad_scale * g_sum + wd * p
+//   buf = g                      (first step with momentum)      | buf = mu * buf + (1 - dampening) * g
+//   g  = g + mu * buf (nesterov) | buf (momentum) | g (plain)    ;  p -= lr * g
+// Same grid / loss-finalising duty / step counter as adam_flat_kernel; `m` is the momentum buffer.
+// ============================================================================
+struct SgdScalars { float lr, momentum, dampening, weight_decay; int nesterov; };
+
+__device__ __forceinline__ void sgd_elem(float& p, float g, float& buf, const SgdScalars& h, bool first) {
+  if (h.weight_decay != 0.f) g = g + h.weight_decay * p;
+  if (h.momentum != 0.f) {
+    buf = first ? g : h.momentum * buf + (1.0f - h.dampening) * g;
+    g = h.nesterov ? g + h.momentum * buf : buf;
+  }
+  p = p - h.lr * g;
+}
+
+__global__ void __launch_bounds__(kAdamThreads) sgd_flat_kernel(AdamArgs a, SgdScalars h) {
+  pdl_wait();
+  pdl_trigger();
+  const bool first = a.st->adam_t == 0;             // torch clones the gradient into the buffer on the first step
+  const float gs = a.grad_scale;
+  if (a.loss_out != nullptr && blockIdx.x == 0) {
+    __shared__ float red[32];
+    float t = 0.f;
+    for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) t += __ldcg(a.loss_part_a + i);
+    for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) t += __ldcg(a.loss_part_b + i);
+    t = block_sum(t, red);
+    if (threadIdx.x == 0) { *a.loss_out = t; publish_loss(a.st, t); }
+  }
+  const long long n4 = a.n >> 2;                    // flat buffers are padded to a multiple of 32 floats
+  float4* p4 = reinterpret_cast<float4*>(a.p);
+  const float4* g4 = reinterpret_cast<const float4*>(a.g);
+  float4* m4 = reinterpret_cast<float4*>(a.m);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 p = p4[i], m = m4[i];
+    float4 g = __ldg(g4 + i);
+    sgd_elem(p.x, g.x * gs, m.x, h, first);
+    sgd_elem(p.y, g.y * gs, m.y, h, first);
+    sgd_elem(p.z, g.z * gs, m.z, h, first);
+    sgd_elem(p.w, g.w * gs, m.w, h, first);
+    p4[i] = p;
+    if (h.momentum != 0.f) m4[i] = m;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(&a.st->ticket_adam, 1u) == gridDim.x - 1) {
+      a.st->adam_t += 1;
+      a.st->ticket_adam = 0;
+      __threadfence();
+    }
+  }
+}
+
 // Adam element update for the fused weight-gradient epilogues and adam_tile_kernel.  Same formula as adam_elem (elementwise.cuh); the
 // square root and the quotient use the branch-free SFU forms (rsqrt / rcp approximations, <= 2 ulp) so that the 32
 // elements a thread owns form independent instruction chains the scheduler can interleave -- with the IEEE forms
@@ -519,23 +575,30 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a
               omb2 = a.st->next[4], eps = a.st->next[5];
   const unsigned int t = a.st->xch_seq + 1u;          // bumped by the last block, after every block has read it
   const float gs = a.grad_scale;
+  __shared__ int peers_ok;
+  if (threadIdx.x == 0) peers_ok = 1;
+  __syncthreads();
   if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
     if (blockIdx.x == 0) {                            // this rank's gradient is complete (the kernel is stream-ordered
       __threadfence_system();                         // behind its weight-gradient GEMMs): tell peer threadIdx.x
       st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
     }
-    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) a.st->xch_error = 1u;
+    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) { flag_exchange_error(a.st); peers_ok = 0; }
   }
   __syncthreads();
+  const bool update = peers_ok != 0;                  // a peer never showed up: leave parameters and moments untouched
   if (a.loss_out != nullptr && blockIdx.x == 0) {     // block-uniform branch (same duty as in adam_flat_kernel)
     __shared__ float red[32];
     float l = 0.f;
     for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) l += __ldcg(a.loss_part_a + i);
     for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) l += __ldcg(a.loss_part_b + i);
     l = block_sum(l, red);
-    if (threadIdx.x == 0) { *a.loss_out = l; publish_loss(a.st, l); }
+    if (threadIdx.x == 0) {
+      if (!update) l = __int_as_float(0x7fc00000);    // NaN: the step did not happen
+      *a.loss_out = l; publish_loss(a.st, l);
+    }
   }
-  const long long n4 = a.n >> 2;                      // the flat layout is a multiple of 32 floats: no scalar tail
+  const long long n4 = update ? (a.n >> 2) : 0;       // the flat layout is a multiple of 32 floats: no scalar tail
   float4* p4 = reinterpret_cast<float4*>(a.p);
   float4* m4 = reinterpret_cast<float4*>(a.m);
   float4* v4 = reinterpret_cast<float4*>(a.v);
@@ -572,7 +635,7 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a
       for (int r = 0; r < pa.n; ++r)                  // every block of this rank has finished reading the peers' buffers
         if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
       for (int r = 0; r < pa.n; ++r)
-        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) a.st->xch_error = 1u;
+        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) flag_exchange_error(a.st);
     }
   }
 }
@@ -592,7 +655,7 @@ __global__ void __launch_bounds__(kAdamThreads) p2p_reduce_slice_kernel(PeerArgs
       __threadfence_system();
       st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
     }
-    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) st->xch_error = 1u;
+    if (!wait_flag_ge(pa.flags[pa.me] + threadIdx.x, t)) flag_exchange_error(st);
   }
   __syncthreads();
   const long long s4 = (n4 + pa.n - 1) / pa.n;        // float4 per slice
@@ -627,18 +690,25 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allgather_kernel(AdamArgs a
               omb2 = a.st->next[4], eps = a.st->next[5];
   const unsigned int t = a.st->xch_seq + 1u;
   const float gs = a.grad_scale;
-  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me)
-    if (!wait_flag_ge(pa.flags[pa.me] + 2 * kMaxPeers + threadIdx.x, t)) a.st->xch_error = 1u;
+  __shared__ int peers_ok;
+  if (threadIdx.x == 0) peers_ok = 1;
   __syncthreads();
+  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me)
+    if (!wait_flag_ge(pa.flags[pa.me] + 2 * kMaxPeers + threadIdx.x, t)) { flag_exchange_error(a.st); peers_ok = 0; }
+  __syncthreads();
+  const bool update = peers_ok != 0 && a.st->xch_error == 0u;   // (the reduce-slice kernel may have timed out already)
   if (a.loss_out != nullptr && blockIdx.x == 0) {
     __shared__ float red[32];
     float l = 0.f;
     for (int i = threadIdx.x; i < a.n_part_a; i += blockDim.x) l += __ldcg(a.loss_part_a + i);
     for (int i = threadIdx.x; i < a.n_part_b; i += blockDim.x) l += __ldcg(a.loss_part_b + i);
     l = block_sum(l, red);
-    if (threadIdx.x == 0) { *a.loss_out = l; publish_loss(a.st, l); }
+    if (threadIdx.x == 0) {
+      if (!update) l = __int_as_float(0x7fc00000);
+      *a.loss_out = l; publish_loss(a.st, l);
+    }
   }
-  const long long n4 = a.n >> 2;
+  const long long n4 = update ? (a.n >> 2) : 0;
   const long long s4 = (n4 + pa.n - 1) / pa.n;
   float4* p4 = reinterpret_cast<float4*>(a.p);
   float4* m4 = reinterpret_cast<float4*>(a.m);
@@ -671,7 +741,7 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allgather_kernel(AdamArgs a
       for (int r = 0; r < pa.n; ++r)                  // this rank has finished reading gradients and reduced slices
         if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
       for (int r = 0; r < pa.n; ++r)
-        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) a.st->xch_error = 1u;
+        if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) flag_exchange_error(a.st);
     }
   }
 }

@@ -224,6 +224,9 @@ struct Tc05Epi {
   int a_tmem;    // TF32X3: the split warps put hi / lo of the A tile into tensor memory (MMA TS form) instead of
                  // writing lo next to it in shared memory -- the MMAs then read only B from shared memory
   int cluster;   // split-K CTAs of a tile form a thread-block cluster (1,1,splits): partials are exchanged through DSMEM
+  int pre_a, pre_b;  // the A / B operand is not written by any kernel of this step before this one (a weight or its
+                     // transposed shadow: last written a whole step ago): its TMA loads for the first ring pass are issued
+                     // BEFORE griddepcontrol.wait, so they land while the predecessor kernel is still running
   // optional phase timing (clock64 stamps of CTA (0,0)); NULL in production
   long long* dbg;
 };
@@ -350,10 +353,24 @@ __device__ __forceinline__ void tc05_prefetch(const Tc05Epi& ep, int m0, int n0,
       pre.aux[i] = (i < rows_valid && (i % it_ns) == it_rank) ? __ldg(reinterpret_cast<const float4*>(sp + i * step))
                                                              : make_float4(fill, fill, fill, fill);
   }
+}
+
+// Fused Adam (EPI_GRADW): the step's scalars and this thread's slice of the weight and both moments.  Called BEFORE the
+// dependency wait: the scalars change only after every CTA of the step's weight-gradient GEMMs has taken its ticket
+// (kernel tail of the PREVIOUS step by the time any kernel of this step runs), and nobody but this tile's CTA writes
+// this tile of p / m / v, last in the previous step.  Plain loads (the data is rewritten in the epilogue).
+template <int BN, int kEpi>
+__device__ __forceinline__ void tc05_prefetch_adam(const Tc05Epi& ep, int m0, int n0, int M, int N, int et, Tc05Pre<BN>& pre) {
+  constexpr int F4R = BN / 4;
+  constexpr int RPP = kTcEpiThreads / F4R;
+  constexpr int ITERS = kTcBM / RPP;
+  const int c4 = et % F4R, rbase = et / F4R;
+  const int n = n0 + 4 * c4;
+  const bool nvalid = n < N;
+  const int rows_valid = nvalid ? (M - m0 - rbase + RPP - 1) / RPP : 0;
+  const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   pre.adam_loaded = false;
   if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
-    // Safe this early: the scalars change only after every CTA of the step's weight-gradient GEMMs has taken its
-    // ticket (kernel tail), and nobody else writes this tile of p / m / v.  Plain loads (the data is rewritten below).
 #pragma unroll
     for (int k = 0; k < 6; ++k) pre.as[k] = ep.adam_st->next[k];
     if (Tc05Pre<BN>::kAdamRegs && gridDim.z == 1) {
@@ -684,8 +701,22 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  // everything above touched only shared memory, TMEM and kernel parameters: from here on the kernel reads what
-  // its predecessor wrote
+  // everything above touched only shared memory, TMEM and kernel parameters.  Still ahead of the dependency wait:
+  // whatever this kernel reads that NO kernel of this step has written before it -- by the time this kernel can be
+  // scheduled its predecessor has passed its own wait, so everything older than the predecessor is complete.
+  int pre_kb = 0;                                  // ring stages whose static operand is already in flight (producer only)
+  if ((ep.pre_a | ep.pre_b) != 0 && warp == 0 && lane == 0) {
+    pre_kb = min(num_kb, S::STAGES);
+    for (int kb = 0; kb < pre_kb; ++kb) {
+      const uint32_t sa = smem_base + kb * S::STAGE;
+      ptx::mbar_expect_tx(bar_full + 8 * kb, S::HB);
+      if (ep.pre_a) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * kb);
+      if (ep.pre_b) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * kb);
+    }
+  }
+  Tc05Pre<BN> pre;
+  const bool is_epi_warp = warp >= 2 && warp < 2 + kTcEpiThreads / 32;
+  if (kEpi == EPI_GRADW && is_epi_warp) tc05_prefetch_adam<BN, kEpi>(ep, m0, n0, M, N, (int)threadIdx.x - 64, pre);
   pdl_wait();
   pdl_trigger();
   if (threadIdx.x == 0) TC_STAMP(1);
@@ -700,11 +731,14 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % S::STAGES;
         const uint32_t ph = (kb / S::STAGES) & 1;
-        ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
         const uint32_t sa = smem_base + s * S::STAGE;
-        ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
-        ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * s);
-        ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * s);
+        const bool early = kb < pre_kb;            // expect_tx and the static operand(s) went out before the wait
+        if (!early) {
+          ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
+          ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
+        }
+        if (!(early && ep.pre_a)) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * s);
+        if (!(early && ep.pre_b)) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * s);
       }
       TC_STAMP(2);
     }
@@ -793,7 +827,6 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     constexpr bool kDist = kEpi != EPI_REPARAM && kEpi != EPI_REPARAM_BWD;
     const bool dist = kDist && ep.cluster && gridDim.z > 1;
     const int it_rank = dist ? (int)blockIdx.z : 0, it_ns = dist ? (int)gridDim.z : 1;
-    Tc05Pre<BN> pre;
     tc05_prefetch<BN, kEpi>(ep, m0, n0, M, N, et, pre, it_rank, it_ns);
     // bias gradient of the weight-gradient GEMMs: row sums of the A operand (fixed order), done first: it overlaps the latency of the first TMA loads
     if (kEpi == EPI_GRADW && blockIdx.x == 0 && blockIdx.z == 0 && ep.db != nullptr) {
@@ -1100,6 +1133,13 @@ struct PrepArgs {
   StepState* st;
   long long S;
   unsigned long long offset_inc;
+  // mdt_train_steps: x is batch (StepState.x_cursor % n_batches) of a device-resident source -- either a pool of fp32
+  // batches or a uint8 image table gathered through the sampler's index order (value / 255, as ToTensor()).  The
+  // index is read from device memory, so the graphs that hold this kernel are launched unmodified step after step.
+  const float* pool;
+  const uint8_t* images;
+  const long long* indices;
+  long long n_batches, n_images;
 };
 
 __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
@@ -1107,15 +1147,30 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
   pdl_trigger();
   if ((int)blockIdx.x < a.tr_blocks) {
     __shared__ float t[32][33];
-    const TrJob job = a.tr.job[0];
+    TrJob job = a.tr.job[0];
     const int tile = (int)blockIdx.x;
     const int r0 = (tile / job.tiles_c) * 32, c0 = (tile % job.tiles_c) * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+    const bool sourced = a.pool != nullptr || a.images != nullptr;
+    long long bidx = 0;
+    if (sourced) {
+      bidx = a.st->x_cursor % a.n_batches;
+      if (a.pool != nullptr) job.in = a.pool + (size_t)bidx * job.R * job.C;
+    }
 #pragma unroll
     for (int i = ty; i < 32; i += 8) {
       const int r = r0 + i, c = c0 + tx;
       const bool ok = r < job.R && c < job.C;
-      const float v = ok ? job.in[(size_t)r * job.ld_in + c] : 0.f;
+      float v = 0.f;
+      if (ok) {
+        if (a.images != nullptr && a.pool == nullptr) {
+          long long src = a.indices[bidx * job.R + r];
+          if (src < 0 || src >= a.n_images) src = 0;                    // never read out of bounds (host validates)
+          v = __fdiv_rn((float)a.images[(size_t)src * job.C + c], 255.0f);   // IEEE division: bit-identical to ToTensor()
+        } else {
+          v = job.in[(size_t)r * job.ld_in + c];
+        }
+      }
       t[i][tx] = v;
       if (ok && a.x_copy != nullptr) a.x_copy[(size_t)r * job.C + c] = v;
     }
@@ -1329,6 +1384,9 @@ struct Tc05Plan {
   // Where the next forward's x lives (NULL: already in the stage buffer).  The prologue kernel reads it from there and
   // fills the stage buffer itself; last_prep / prep_launched let the engine find and re-point that kernel in a graph.
   const float* x_src = nullptr;
+  // mdt_train_steps: set while its graphs are captured (see PrepArgs)
+  const float* src_pool = nullptr; const uint8_t* src_images = nullptr; const long long* src_indices = nullptr;
+  long long src_n_batches = 0, src_n_images = 0;
   // Non-NULL while the engine enqueues a peer-memory exchange step: the weight-gradient GEMMs of tc05_backward write
   // the gradient there (the buffer the group's peers have mapped) instead of into the caller's gradient buffer.
   float* grads_override = nullptr;
@@ -1336,6 +1394,7 @@ struct Tc05Plan {
   // sm_count / sm_share SMs, so that the kernels of different trials run side by side instead of queueing for SMs
   // (measured, 8 trials: 3.5 -> 5.1 M samples/s).
   int sm_share = 1;
+  int preload = 1;     // issue weight-operand TMA loads before the dependency wait (MDT_NO_PRELOAD=1 turns it off)
   PrepArgs last_prep{};
   bool prep_launched = false;
   cudaStream_t side = nullptr, side2 = nullptr, side3 = nullptr, side4 = nullptr;
@@ -1413,8 +1472,9 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   if (const char* v = getenv("MDT_BN_DWA")) p->bn_dwa = atoi(v);
   if (const char* v = getenv("MDT_BN_FC4")) p->bn_fc4 = atoi(v);          // tuning knobs (16 / 32 / 64)
   if (const char* v = getenv("MDT_BN_H")) p->bn_h = atoi(v);
-  if (const char* v = getenv("MDT_BN_SKINNY")) p->bn_skinny = atoi(v);
   p->bn_skinny = b.Bmax > 1024 ? 64 : (b.Bmax > 256 ? 32 : 16);
+  if (const char* v = getenv("MDT_BN_SKINNY")) { const int c = atoi(v); if (c == 16 || c == 32 || c == 64) p->bn_skinny = c; }
+  p->preload = getenv("MDT_NO_PRELOAD") == nullptr ? 1 : 0;
   const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
@@ -1527,6 +1587,11 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       tr_add(pa.tr, blocks, src, p->xT, B, D, D, p->ldB);
       pa.tr_blocks = blocks;
       pa.x_copy = (src != b.x_stage) ? b.x_stage : nullptr;
+      if (p->src_pool != nullptr || p->src_images != nullptr) {
+        pa.pool = p->src_pool; pa.images = p->src_images; pa.indices = p->src_indices;
+        pa.n_batches = p->src_n_batches; pa.n_images = p->src_n_images; pa.st = b.st;
+        pa.x_copy = b.x_stage;
+      }
       if (eps_in == nullptr) {
         pa.eps_out = b.eps; pa.n_eps = (long long)B * Z; pa.st = b.st;
         torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
@@ -1540,6 +1605,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     }
     Tc05Epi e1{};
     e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
+    e1.pre_b = p->preload;                       // W1: last written by the previous step's update
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
     if (p->simt_latent) {
@@ -1556,6 +1622,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e2.C = b.ml; e2.ldc = 2 * Z; e2.bias = P + b.L.off[B2X]; e2.eps_in = eps_in;
     e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
     e2.kl_partials = p->kl_partials;
+    e2.pre_a = p->preload;                       // W2x
     MDT_TRY(tc05_launch<EPI_REPARAM>(p->bn_skinny, sp, p->mW2x, m->h1B, 2 * Z, B, H, e2, s,
                                       tc05_splits(p, e2, 2 * Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc2x_reparam_fwd");
@@ -1564,6 +1631,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
   if (decode_only || !p->simt_latent) {
     Tc05Epi e3{};
     e3.C = b.h3; e3.ldc = H; e3.CT = p->h3T; e3.ldct = p->ldB; e3.bias = P + b.L.off[B3]; e3.act = MDT_ACT_RELU;
+    e3.pre_b = p->preload;                       // W3
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->z, p->mW3, B, H, Z, e3, s));
     TC_NOTE(p, "fc3_fwd");
   }
@@ -1572,11 +1640,13 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
     e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
     e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + p->bn_skinny - 1) / p->bn_skinny;
+    e4.pre_b = p->preload;                       // W4
     MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_bce_fwd");
   } else {
     Tc05Epi e4{};
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.act = MDT_ACT_SIGMOID;
+    e4.pre_b = p->preload;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_fwd");
   }
@@ -1639,6 +1709,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   if (b.bucket_ready) MDT_TRY(b.bucket_ready(b.note_ctx, 0, sw));   // fc4.weight + fc4.bias gradients: DDP's first bucket
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
+  e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
   MDT_TRY(fork_to(sw3));                          // da3^T ready (z^T since the forward)
@@ -1651,6 +1722,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   } else {
     e = Tc05Epi{};
     e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+    e.pre_a = p->preload;                        // W3^T
     MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
                                           tc05_splits(p, e, Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc3_dX_reparam_bwd");
@@ -1663,6 +1735,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   if (!p->simt_latent) {
     e = Tc05Epi{};
     e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+    e.pre_b = p->preload;                        // W2x^T
     MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
     TC_NOTE(p, "fc2x_dX");
   }
@@ -1773,6 +1846,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   };
   Tc05Epi e{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
+  e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
   if (p->simt_latent) {
@@ -1802,6 +1876,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     MDT_TRY(launch_dw(0, sa));
     e = Tc05Epi{};
     e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
+    e.pre_a = p->preload;                        // W3^T
     MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
                                           tc05_splits(p, e, Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc3_dX_reparam_bwd");
@@ -1809,6 +1884,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     MDT_TRY(launch_dw(1, sb));
     e = Tc05Epi{};
     e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
+    e.pre_b = p->preload;                        // W2x^T
     MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
     TC_NOTE(p, "fc2x_dX");
     MDT_TRY(after_main(sc, sd));                  // E3: W2x^T no longer needed, da1^T ready

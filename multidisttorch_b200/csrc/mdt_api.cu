@@ -117,6 +117,16 @@ struct mdt_engine {
   // diagnostic switches, read from the environment once when the engine is created
   bool opt_fused_adam = true, opt_nccl_in_graph = true, opt_zerocopy = true, opt_h2d_prefetch = true;
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
+  volatile unsigned int* err_word = nullptr;        // pinned word the exchange kernels set when a peer never answered
+  float* loss_hist = nullptr;                       // device ring of the last kLossHist per-step losses
+  long long cursor_expected = -1;                   // host's view of StepState.x_cursor (-1: unknown, set it)
+  const void* src_sig[4] = {nullptr, nullptr, nullptr, nullptr};   // batch source the cached multi-step graphs were captured for
+  bool sourced = false;                             // inside mdt_train_steps
+  bool use_sgd = false;                             // mdt_engine_set_sgd: the flat SGD kernel replaces every Adam form
+  SgdScalars sgd{};
+  int exchange = 0;                                 // mdt_exchange from the cfg (0 = automatic choice)
+  long long two_shot_bytes = 16ll << 20;            // automatic choice: two-shot once a rank would read more than this
+  int two_shot_from = 3;                            // ... and the group has at least this many ranks
   // host-buffer steps submitted while the GPU is still busy: x is DMA'd into a small ring of device buffers on a copy
   // stream (overlapping the step in flight) instead of being read over PCIe by the step's own first kernel
   static constexpr int kPreSlots = 4;
@@ -139,6 +149,7 @@ struct mdt_engine {
   cudaEvent_t ev_comm_done = nullptr;
   bool bucket0_sent = false;
   bool defer_buckets = false;   // compat-mode backward: the caller all-reduces later (mdt_allreduce_grads)
+  bool one_bucket = false;      // small flat gradient: ONE all-reduce after backward instead of DDP's two buckets
 
   struct Graph {
     cudaGraphExec_t exec; long long kernels;
@@ -189,7 +200,7 @@ int carve_workspace(mdt_engine* e) {
       {&e->x_stage, B * D}, {&e->eps_stage, B * Z}, {&e->h1, B * H}, {&e->ml, B * 2 * Z}, {&e->eps, B * Z},
       {&e->sd, B * Z}, {&e->z, B * Z}, {&e->h3, B * H}, {&e->recon, B * D}, {&e->da4, B * D}, {&e->da3, B * H},
       {&e->dz, B * Z}, {&e->dml_kl, B * 2 * Z}, {&e->dml, B * 2 * Z}, {&e->da1, B * H},
-      {&e->loss_partials, (size_t)kLossMaxBlocks}, {&e->loss_dev, 64},
+      {&e->loss_partials, (size_t)kLossMaxBlocks}, {&e->loss_dev, 64}, {&e->loss_hist, (size_t)kLossHist},
   };
   size_t bytes = 0;
   for (auto& it : items) bytes += align_up(it.n * sizeof(float), 256);
@@ -294,8 +305,13 @@ int enqueue_adam(mdt_engine* e, float grad_scale, bool finalize_loss = false) {
     tc05_loss_partials(e->tc, e->last_B, &a.loss_part_a, &a.n_part_a, &a.loss_part_b, &a.n_part_b);
     a.loss_out = e->loss_dev;
   }
-  MDT_CUDA(launch_pdl(adam_flat_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a));
-  MDT_TRY(note_launch(e, "adam_flat"));
+  if (e->use_sgd) {
+    MDT_CUDA(launch_pdl(sgd_flat_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a, e->sgd));
+    MDT_TRY(note_launch(e, "sgd_flat"));
+  } else {
+    MDT_CUDA(launch_pdl(adam_flat_kernel, dim3(adam_grid(a.n, e->dev->sm_count)), dim3(kAdamThreads), 0, e->stream, a));
+    MDT_TRY(note_launch(e, "adam_flat"));
+  }
   if (e->tc) MDT_TRY(tc05_params_changed(e->tc, e->stream));   // refresh the transposed weight shadows
   return MDT_OK;
 }
@@ -312,10 +328,10 @@ int enqueue_adam_p2p(mdt_engine* e, float grad_scale) {
   // (reduce own slice, then gather the reduced slices inside the Adam pass: 2(n-1)/n x M) for 3+ ranks with more than
   // 16 MB to read.  Measured on 4 ranks: M = 2.6 MB one-shot 5.57 vs two-shot 5.27 M samples/s; M = 26.7 MB one-shot
   // 1.66 vs two-shot 1.85 M (NCCL 1.83 M).
-  static const int two_shot_from = getenv("MDT_P2P_TWO_SHOT_FROM") ? atoi(getenv("MDT_P2P_TWO_SHOT_FROM")) : 3;
-  static const long long two_shot_bytes = getenv("MDT_P2P_TWO_SHOT_BYTES") ? atoll(getenv("MDT_P2P_TWO_SHOT_BYTES")) : (16ll << 20);
   const long long peer_bytes = (long long)(pa.n - 1) * a.n * (long long)sizeof(float);
-  if (pa.n >= two_shot_from && peer_bytes > two_shot_bytes) {
+  const bool two_shot = e->exchange == MDT_EXCHANGE_P2P_TWO_SHOT ||
+                        (e->exchange != MDT_EXCHANGE_P2P_ONE_SHOT && pa.n >= e->two_shot_from && peer_bytes > e->two_shot_bytes);
+  if (two_shot) {
     const dim3 grid(adam_grid(a.n, e->dev->sm_count));
     MDT_CUDA(launch_pdl(p2p_reduce_slice_kernel, dim3(grid.x / (unsigned)pa.n + 1), dim3(kAdamThreads), 0, e->stream, pa,
                         (long long)(a.n >> 2), e->st));
@@ -342,6 +358,9 @@ int check_batch(mdt_engine* e, int B) {
   MDT_CHECK(e != nullptr, "engine is NULL");
   if (!e->bound) return set_error(MDT_ERR_STATE, "mdt_engine_bind_buffers has not been called");
   MDT_CHECK(B >= 0 && B <= e->Bmax, "batch %d outside [0, max_batch=%d]", B, e->Bmax);
+  if (e->err_word != nullptr && *e->err_word != 0u)
+    return set_error(MDT_ERR_STATE, "a peer of this trial group never delivered its gradient (peer-memory exchange timed out): "
+                     "that step was skipped (NaN loss, parameters untouched) and the trial cannot continue");
   return MDT_OK;
 }
 
@@ -369,7 +388,7 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
     ce = cudaGraphInstantiate(&ex, g, 0);
     if (ce != cudaSuccess) { cudaGraphDestroy(g); return set_error(MDT_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce)); }
     mdt_engine::Graph entry{ex, kernels};
-    if (e->tc && e->tc->prep_launched) {
+    if (e->tc && e->tc->prep_launched && !e->sourced) {
       // remember the prologue kernel's node: its x pointer is the one launch parameter that changes between steps
       size_t nn = 0;
       cudaGraphGetNodes(g, nullptr, &nn);
@@ -443,7 +462,7 @@ int allreduce_grads(mdt_engine* e) {
 // the all-reduce of that bucket goes to the communication stream behind an event.
 int bucket_ready_cb(void* ctx, int bucket, cudaStream_t on) {
   mdt_engine* e = static_cast<mdt_engine*>(ctx);
-  if (e->gsize <= 1 || e->comm == nullptr || e->prof_on || e->defer_buckets) return MDT_OK;
+  if (e->gsize <= 1 || e->comm == nullptr || e->prof_on || e->defer_buckets || e->one_bucket) return MDT_OK;
   MDT_TRY(load_nccl());
   MDT_CUDA(cudaEventRecord(e->ev_bucket[bucket], on));
   MDT_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_bucket[bucket], 0));
@@ -459,8 +478,17 @@ int finish_allreduce(mdt_engine* e) {
     return set_error(MDT_ERR_STATE, "group_size %d but no NCCL communicator was given to mdt_engine_create", e->gsize);
   MDT_TRY(load_nccl());
   if (e->prof_on) { e->bucket0_sent = false; return allreduce_grads(e); }
-  if (!e->bucket0_sent) MDT_TRY(bucket_ready_cb(e, 0, e->stream));
-  MDT_TRY(bucket_ready_cb(e, 1, e->stream));
+  if (e->one_bucket) {
+    // Below a few MB an all-reduce is latency-bound: two buckets cost two latencies (measured on 8 ranks: 2 x 31 us
+    // against 36 us for the whole 2.6 MB gradient) and only the first overlaps backward.  One call, on the
+    // communication stream so that the step's graph keeps the same shape.
+    MDT_CUDA(cudaEventRecord(e->ev_bucket[1], e->stream));
+    MDT_CUDA(cudaStreamWaitEvent(e->comm_stream, e->ev_bucket[1], 0));
+    MDT_NCCL(g_nccl.AllReduce(e->grads, e->grads, (size_t)e->L.total, ncclFloat, ncclSum, e->comm, e->comm_stream));
+  } else {
+    if (!e->bucket0_sent) MDT_TRY(bucket_ready_cb(e, 0, e->stream));
+    MDT_TRY(bucket_ready_cb(e, 1, e->stream));
+  }
   e->bucket0_sent = false;
   MDT_CUDA(cudaEventRecord(e->ev_comm_done, e->comm_stream));
   MDT_CUDA(cudaStreamWaitEvent(e->stream, e->ev_comm_done, 0));
@@ -478,29 +506,58 @@ int enqueue_fwd_loss_bwd(mdt_engine* e, const float* x, int B, const float* eps)
   return enqueue_backward_fp32(e, x, B);
 }
 
-int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
+// `steps` > 1 (mdt_train_steps only): that many consecutive steps in ONE graph.
+int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, int steps = 1) {
   e->last_B = B;
+  if (B == 0 && e->gsize > 1)   // the peers of a group would wait for this rank's gradient: refuse instead of hanging them
+    return set_error(MDT_ERR_INVALID, "an empty batch on one rank of a %d-rank trial group would stall its peers", e->gsize);
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
-  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1);   // graphs are per (eps given, SM share)
-  if (e->tc) e->pub_expected = (e->pub_expected + 1u) & 0x7fffffffu;   // every tensor-core training step publishes
+  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8);   // graphs are per (eps given, SM share, steps)
+  if (e->tc) e->pub_expected = (e->pub_expected + (unsigned)steps) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
-  if (e->gsize == 1 && e->tc && e->opt_fused_adam) {
+  if (e->tc && !e->sourced) e->cursor_expected = -1;                     // ... and moves the device-side batch cursor
+  const int kbase = e->sourced ? 20 : 0;                                 // graphs of mdt_train_steps are keyed apart
+  if (steps > 1) {
+    auto one = [&]() -> int {
+      if (e->gsize == 1 && e->opt_fused_adam && !e->use_sgd) {
+        MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
+        return tc05_backward_fused_adam(e->tc, e->stream, B);
+      }
+      if (e->gsize > 1 && e->p2p && !e->use_sgd && e->exchange != MDT_EXCHANGE_NCCL) {
+        e->tc->grads_override = e->xch;
+        e->defer_buckets = true;
+        int rc = enqueue_fwd_loss_bwd(e, x, B, eps);
+        e->defer_buckets = false;
+        e->tc->grads_override = nullptr;
+        MDT_TRY(rc);
+        return enqueue_adam_p2p(e, gscale);
+      }
+      MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
+      MDT_TRY(finish_allreduce(e));
+      return enqueue_adam(e, gscale, true);
+    };
+    return run_cached(e, kbase + 9, B, fl, [&]() -> int {
+      for (int i = 0; i < steps; ++i) MDT_TRY(one());
+      return MDT_OK;
+    });
+  }
+  if (e->gsize == 1 && e->tc && e->opt_fused_adam && !e->use_sgd) {
     // single-rank group on the tensor-core path: Adam runs inside the weight-gradient epilogues
-    return run_cached(e, /*kind=*/7, B, fl, [&]() -> int {
+    return run_cached(e, kbase + 7, B, fl, [&]() -> int {
       MDT_TRY(tc05_forward(e->tc, e->stream, x, B, eps, false, /*fuse_loss=*/true));
       return tc05_backward_fused_adam(e->tc, e->stream, B);
     });
   }
   if (e->gsize == 1) {
-    return run_cached(e, /*kind=*/0, B, fl, [&]() -> int {
+    return run_cached(e, kbase + 0, B, fl, [&]() -> int {
       MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
       return enqueue_adam(e, gscale, true);
     });
   }
-  if (e->p2p && e->tc && !e->prof_on) {
+  if (e->p2p && e->tc && !e->prof_on && !e->use_sgd && e->exchange != MDT_EXCHANGE_NCCL) {
     // group on one node with peer access: gradients are exchanged through NVLink peer memory inside the Adam kernel
-    return run_cached(e, /*kind=*/8, B, fl, [&]() -> int {
+    return run_cached(e, kbase + 8, B, fl, [&]() -> int {
       e->tc->grads_override = e->xch;
       e->defer_buckets = true;                    // no NCCL buckets in this step
       int rc = enqueue_fwd_loss_bwd(e, x, B, eps);
@@ -516,7 +573,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps) {
     return run_cached(e, /*kind=*/2, B, fl & ~1, [&]() -> int { return enqueue_adam(e, gscale, true); });
   }
   // one graph for the whole step, the group's NCCL all-reduces included (bucket 0 overlaps the rest of backward)
-  return run_cached(e, /*kind=*/6, B, fl, [&]() -> int {
+  return run_cached(e, kbase + 6, B, fl, [&]() -> int {
     MDT_TRY(enqueue_fwd_loss_bwd(e, x, B, eps));
     MDT_TRY(finish_allreduce(e));
     return enqueue_adam(e, gscale, true);
@@ -551,6 +608,7 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
             "in_dim, hidden and latent must be multiples of 4 (16-byte rows)");
   MDT_CHECK(group_size >= 1 && group_rank >= 0 && group_rank < group_size, "bad group size/rank");
   MDT_CHECK(cfg->gemm_mode >= MDT_GEMM_FP32 && cfg->gemm_mode <= MDT_GEMM_TF32X3, "unknown gemm_mode %d", cfg->gemm_mode);
+  MDT_CHECK(cfg->exchange >= MDT_EXCHANGE_AUTO && cfg->exchange <= MDT_EXCHANGE_P2P_TWO_SHOT, "unknown exchange %d", cfg->exchange);
   DeviceInfo* di = nullptr;
   MDT_TRY(device_info(&di));
   if (cfg->gemm_mode != MDT_GEMM_FP32 && di->cc_major != 10)
@@ -567,6 +625,10 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   e->opt_nccl_in_graph = !(getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0');
   e->opt_zerocopy = getenv("MDT_NO_ZEROCOPY") == nullptr;
   e->opt_h2d_prefetch = getenv("MDT_NO_H2D_PREFETCH") == nullptr;
+  e->exchange = cfg->exchange;
+  if (const char* v = getenv("MDT_P2P_TWO_SHOT_FROM")) e->two_shot_from = atoi(v);
+  if (const char* v = getenv("MDT_P2P_TWO_SHOT_BYTES")) e->two_shot_bytes = atoll(v);
+  e->one_bucket = (size_t)e->L.total * sizeof(float) < ((size_t)8 << 20) && getenv("MDT_NCCL_TWO_BUCKETS") == nullptr;
   if (stream) {
     e->stream = reinterpret_cast<cudaStream_t>(stream);
   } else {
@@ -588,17 +650,36 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
     cudaError_t ce = cudaMallocHost(&e->loss_pinned, 1024);
     if (ce != cudaSuccess) r = set_error(MDT_ERR_CUDA, "cudaMallocHost: %s", cudaGetErrorString(ce));
   }
+  if (r == MDT_OK) memset(e->loss_pinned, 0, 1024);
   if (r == MDT_OK && e->cfg.gemm_mode != MDT_GEMM_FP32) {
-    memset(e->loss_pinned, 0, 1024);
+    // pinned page: [0] loss of synchronous steps, [8] exchange-error word, [16..144) mailbox ring of 64 words
     e->mailbox = reinterpret_cast<volatile unsigned long long*>(e->loss_pinned + 16);
     void* dptr = nullptr;
-    if (cudaHostGetDevicePointer(&dptr, e->loss_pinned + 16, 0) == cudaSuccess && dptr != nullptr) {
-      unsigned long long* mb = static_cast<unsigned long long*>(dptr);
+    if (cudaHostGetDevicePointer(&dptr, e->loss_pinned, 0) == cudaSuccess && dptr != nullptr) {
+      unsigned long long* mb = reinterpret_cast<unsigned long long*>(static_cast<float*>(dptr) + 16);
+      unsigned int* ew = reinterpret_cast<unsigned int*>(static_cast<float*>(dptr) + 8);
       if (cudaMemcpy(&e->st->host_mailbox, &mb, sizeof(mb), cudaMemcpyHostToDevice) != cudaSuccess) e->mailbox = nullptr;
+      if (cudaMemcpy(&e->st->host_error, &ew, sizeof(ew), cudaMemcpyHostToDevice) == cudaSuccess)
+        e->err_word = reinterpret_cast<volatile unsigned int*>(e->loss_pinned + 8);
     } else {
       e->mailbox = nullptr;
     }
     cudaGetLastError();
+    if (cudaMemcpy(&e->st->loss_hist, &e->loss_hist, sizeof(float*), cudaMemcpyHostToDevice) != cudaSuccess)
+      r = set_error(MDT_ERR_CUDA, "could not publish the loss-history ring");
+    // host-buffer steps: copy stream, ring of device input buffers and their events -- created here, not on the first
+    // submit, so that no step ever pays for a cudaMalloc
+    if (r == MDT_OK && e->mailbox != nullptr) {
+      if (cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
+        r = set_error(MDT_ERR_CUDA, "could not create the copy stream");
+      for (int k = 0; k < mdt_engine::kPreSlots && r == MDT_OK; ++k) {
+        if (cudaMalloc(&e->x_pre[k], (size_t)e->Bmax * e->D * sizeof(float)) != cudaSuccess ||
+            cudaEventCreateWithFlags(&e->ev_copied[k], cudaEventDisableTiming) != cudaSuccess ||
+            cudaEventCreateWithFlags(&e->ev_used[k], cudaEventDisableTiming) != cudaSuccess)
+          r = set_error(MDT_ERR_CUDA, "could not create the host-input staging ring (%zu bytes per slot)",
+                        (size_t)e->Bmax * e->D * sizeof(float));
+      }
+    }
   }
   if (r == MDT_OK) {
     mdt_adam h{1e-3, 0.9, 0.999, 1e-8};
@@ -756,6 +837,31 @@ int mdt_engine_set_adam(mdt_engine* e, const mdt_adam* h, int64_t completed_step
   adam_next_scalars(host.lr, host.b1, host.b2, host.eps, host.b1_pow, host.b2_pow, host.next);
   MDT_CUDA(cudaMemcpyAsync(&e->st->adam_t, &host, sizeof(host), cudaMemcpyHostToDevice, e->stream));
   MDT_CUDA(cudaStreamSynchronize(e->stream));  // `host` lives on this stack frame
+  if (e->use_sgd) {                            // back from SGD: the captured steps hold the other optimizer's kernels
+    e->use_sgd = false;
+    for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
+    e->graphs.clear();
+  }
+  return MDT_OK;
+}
+
+namespace {
+void drop_graphs(mdt_engine* e) {
+  for (auto& kv : e->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.graph) cudaGraphDestroy(kv.second.graph); }
+  e->graphs.clear();
+}
+}  // namespace
+
+int mdt_engine_set_sgd(mdt_engine* e, const mdt_sgd* h, int64_t completed_steps) {
+  MDT_CHECK(e && h, "NULL argument");
+  MDT_CHECK(h->lr >= 0 && h->momentum >= 0 && h->weight_decay >= 0, "negative SGD hyper-parameter");
+  MDT_CHECK(!(h->nesterov && (h->momentum <= 0 || h->dampening != 0)), "Nesterov momentum requires a momentum and zero dampening");
+  MDT_CUDA(cudaStreamSynchronize(e->stream));
+  e->use_sgd = true;
+  e->sgd = SgdScalars{(float)h->lr, (float)h->momentum, (float)h->dampening, (float)h->weight_decay, h->nesterov ? 1 : 0};
+  long long t = completed_steps;
+  MDT_CUDA(cudaMemcpy(&e->st->adam_t, &t, sizeof(t), cudaMemcpyHostToDevice));
+  drop_graphs(e);                                  // the scalars are kernel arguments of the captured steps
   return MDT_OK;
 }
 
@@ -845,6 +951,100 @@ int mdt_train_step(mdt_engine* e, const float* x, int batch, const float* eps_or
   return MDT_OK;
 }
 
+int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64_t first_batch, int n_steps,
+                    float* losses_out) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(src != nullptr && n_steps >= 0 && batch > 0, "bad argument");
+  MDT_CHECK(src->n_batches > 0 && first_batch >= 0, "the batch source is empty or first_batch is negative");
+  MDT_CHECK(src->x_pool != nullptr || (src->images_u8 != nullptr && src->indices != nullptr && src->n_images > 0),
+            "the batch source needs x_pool, or images_u8 + indices + n_images");
+  MDT_CHECK(losses_out == nullptr || n_steps <= (int)kLossHist, "losses_out holds at most %u steps per call", kLossHist);
+  if (n_steps == 0) return MDT_OK;
+  if (e->tc == nullptr) {
+    // fp32 FFMA path (no step prologue kernel): one call per batch
+    MDT_CHECK(src->x_pool != nullptr, "the uint8 source needs a tensor-core gemm_mode");
+    for (int i = 0; i < n_steps; ++i) {
+      const float* x = src->x_pool + (size_t)((first_batch + i) % src->n_batches) * batch * e->D;
+      MDT_TRY(mdt_train_step(e, x, batch, nullptr, losses_out ? losses_out + i : nullptr));
+    }
+    return MDT_OK;
+  }
+  // the batch index of the next step lives on the device (StepState.x_cursor, +1 per published step): only written from
+  // here when the caller jumps somewhere the device does not expect
+  if (e->cursor_expected < 0 || (e->cursor_expected - first_batch) % src->n_batches != 0) {
+    const long long c = first_batch;
+    MDT_CUDA(cudaMemcpyAsync(&e->st->x_cursor, &c, sizeof(c), cudaMemcpyHostToDevice, e->stream));
+    MDT_CUDA(cudaStreamSynchronize(e->stream));     // `c` lives on this stack frame
+  }
+  Tc05Plan* p = e->tc;
+  p->src_pool = src->x_pool; p->src_images = src->x_pool ? nullptr : src->images_u8;
+  p->src_indices = reinterpret_cast<const long long*>(src->indices);
+  p->src_n_batches = src->n_batches; p->src_n_images = src->n_images;
+  static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 8;
+  const int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
+  // graphs are specific to the source (its pointers are kernel arguments): a new source drops the cached ones
+  const void* sig[4] = {src->x_pool, src->x_pool ? nullptr : (const void*)src->images_u8, src->indices,
+                        reinterpret_cast<const void*>((uintptr_t)src->n_batches)};
+  if (memcmp(sig, e->src_sig, sizeof(sig)) != 0) {
+    for (auto it = e->graphs.begin(); it != e->graphs.end();) {
+      if (std::get<0>(it->first) >= 20) {
+        cudaGraphExecDestroy(it->second.exec); if (it->second.graph) cudaGraphDestroy(it->second.graph);
+        it = e->graphs.erase(it);
+      } else {
+        ++it;
+      }
+    }
+    memcpy(e->src_sig, sig, sizeof(sig));
+  }
+  const unsigned int seq0 = e->pub_expected;        // published steps before this call
+  int rc = MDT_OK;
+  e->sourced = true;
+  for (int done = 0; done < n_steps && rc == MDT_OK;) {
+    const int u = (n_steps - done >= U) ? U : 1;
+    rc = train_step_device(e, e->x_stage, batch, nullptr, u);
+    done += u;
+  }
+  e->sourced = false;
+  p->src_pool = nullptr; p->src_images = nullptr; p->src_indices = nullptr;
+  MDT_TRY(rc);
+  e->cursor_expected = first_batch + n_steps;
+  if (losses_out != nullptr) {
+    const unsigned int lo = seq0 & (kLossHist - 1u);
+    const unsigned int n1 = (lo + (unsigned)n_steps <= kLossHist) ? (unsigned)n_steps : kLossHist - lo;
+    MDT_CUDA(cudaMemcpyAsync(losses_out, e->loss_hist + lo, n1 * sizeof(float), cudaMemcpyDeviceToDevice, e->stream));
+    if (n1 < (unsigned)n_steps)
+      MDT_CUDA(cudaMemcpyAsync(losses_out + n1, e->loss_hist, ((unsigned)n_steps - n1) * sizeof(float),
+                               cudaMemcpyDeviceToDevice, e->stream));
+  }
+  return MDT_OK;
+}
+
+int mdt_engine_exchange_bench(mdt_engine* e, int iters, double* seconds) {
+  MDT_TRY(check_batch(e, 0));
+  MDT_CHECK(seconds && iters > 0, "bad argument");
+  MDT_CHECK(e->p2p && e->tc, "the peer-memory exchange is not enabled on this engine (mdt_engine_set_peers)");
+  cudaEvent_t e0, e1;
+  MDT_CUDA(cudaEventCreate(&e0));
+  MDT_CUDA(cudaEventCreate(&e1));
+  const float gs = 1.0f / (float)e->gsize;
+  e->last_B = e->Bmax;
+  int rc = enqueue_adam_p2p(e, gs);                  // warm-up (also the first cross-rank rendezvous)
+  if (rc == MDT_OK) rc = cudaEventRecord(e0, e->stream) == cudaSuccess ? MDT_OK : set_error(MDT_ERR_CUDA, "event");
+  for (int i = 0; i < iters && rc == MDT_OK; ++i) rc = enqueue_adam_p2p(e, gs);
+  if (rc == MDT_OK) {
+    cudaEventRecord(e1, e->stream);
+    if (cudaEventSynchronize(e1) != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "exchange bench failed: %s", cudaGetErrorString(cudaGetLastError()));
+  }
+  float ms = 0.f;
+  if (rc == MDT_OK) cudaEventElapsedTime(&ms, e0, e1);
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  e->pub_expected = (e->pub_expected + (unsigned)iters + 1u) & 0x7fffffffu;   // every exchange kernel publishes once
+  MDT_TRY(rc);
+  *seconds = (double)ms * 1e-3 / iters;
+  return MDT_OK;
+}
+
 int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch) {
   MDT_CHECK(engines && xs && n_trials >= 0, "bad argument");
   // the trials share the GPU: each one's kernels are sized for 1/n of the SMs (Tc05Plan::sm_share)
@@ -882,15 +1082,7 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
       // Is the step submitted last still running?  Then there is compute to hide a DMA behind.
       const unsigned int last = e->pub_expected;
       const bool busy = last != 0 && (unsigned int)(e->mailbox[last & 63u] >> 32) != last;
-      if (busy && e->opt_h2d_prefetch) {
-        if (e->copy_stream == nullptr) {
-          MDT_CUDA(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
-          for (int k = 0; k < mdt_engine::kPreSlots; ++k) {
-            MDT_CUDA(cudaMalloc(&e->x_pre[k], (size_t)e->Bmax * e->D * sizeof(float)));
-            MDT_CUDA(cudaEventCreateWithFlags(&e->ev_copied[k], cudaEventDisableTiming));
-            MDT_CUDA(cudaEventCreateWithFlags(&e->ev_used[k], cudaEventDisableTiming));
-          }
-        }
+      if (busy && e->opt_h2d_prefetch && e->copy_stream != nullptr) {
         slot = (int)(e->pre_next++ % mdt_engine::kPreSlots);
         if (e->pre_used[slot]) MDT_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_used[slot], 0));
         MDT_CUDA(cudaMemcpyAsync(e->x_pre[slot], x_host, (size_t)batch * e->D * sizeof(float), cudaMemcpyHostToDevice,

@@ -59,6 +59,29 @@ def recognise(module):
     return D, H, Z
 
 
+class _Mismatch(Exception):
+    """The module has the reference VAE's layers but does not compute the reference VAE's forward."""
+
+
+def _cuda_leg_is_nccl(pg):
+    """True when collectives on CUDA tensors of ``pg`` go through NCCL.  ``dist.get_backend`` returns the backend
+    STRING the group was created with -- "nccl", but also "cpu:gloo,cuda:nccl" for the groups this repo's own
+    setup_ddp creates -- so the decision is taken on the backend object that serves the CUDA device."""
+    try:
+        backend = (pg if pg is not None else dist.group.WORLD)._get_backend(torch.device("cuda"))
+        return isinstance(backend, dist.ProcessGroupNCCL)
+    except Exception:
+        name = str(dist.get_backend(pg))
+        return name == "nccl" or "cuda:nccl" in name
+
+
+def _notice(msg, pg):
+    if os.environ.get("MDT_DROPIN_QUIET", "0") == "1":
+        return
+    if not dist.is_initialized() or pg is None or dist.get_rank(pg) == 0:
+        print(f"[multidisttorch_b200] {msg}", flush=True)
+
+
 class _VAEFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, anchor, owner):
@@ -95,6 +118,11 @@ class EngineModule(nn.Module):
                         use_graph=os.environ.get("MDT_GRAPH", "1") != "0", group=self.process_group, device=dev)
         if first:
             eng.load_reference_state_dict(self.module.state_dict())
+            try:
+                self._verify(eng)
+            except _Mismatch:
+                eng.close()
+                raise
             if eng.group_size > 1:
                 eng.broadcast_params()          # DDP constructor: parameters of group-rank 0 win
         else:
@@ -113,6 +141,44 @@ class EngineModule(nn.Module):
             p.grad = gv[name]
             _ENGINE_OF_PARAM[id(p)] = self
         self._sync_rng(force=True)
+
+    def _verify(self, eng):
+        """Behaviour check before the swap: the module's OWN forward (eps pinned by intercepting ``torch.randn_like``
+        for the duration of the call) must agree with the engine on a small batch.  A model that merely has layers
+        named fc1 .. fc4 but another activation, dropout, a scaled reparameterisation or a different output tuple
+        raises _Mismatch and is left to torch."""
+        D, H, Z = self.dims
+        dev = eng.device
+        g = torch.Generator(device="cpu").manual_seed(20240607)
+        x = torch.rand(4, D, generator=g).to(dev)
+        eps = torch.randn(4, Z, generator=g).to(dev)
+        orig = torch.randn_like
+        calls = []
+
+        def pinned(like, *a, **k):
+            calls.append(tuple(like.shape))
+            return eps.to(like.dtype) if tuple(like.shape) == (4, Z) else orig(like, *a, **k)
+
+        was_training = self.module.training
+        try:
+            torch.randn_like = pinned
+            with torch.no_grad():
+                out = self.module(x)
+        except Exception as exc:          # the module cannot even take a [B, D] batch
+            raise _Mismatch(f"forward failed on a [4, {D}] batch: {exc}")
+        finally:
+            torch.randn_like = orig
+            self.module.train(was_training)
+        if not (isinstance(out, tuple) and len(out) == 3 and all(torch.is_tensor(t) for t in out)):
+            raise _Mismatch("forward does not return (recon, mu, logvar)")
+        if [tuple(t.shape) for t in out] != [(4, D), (4, Z), (4, Z)] or calls != [(4, Z)]:
+            raise _Mismatch("forward has other shapes / another source of eps than the reference VAE")
+        got = eng.forward(x, eps)
+        tol = 3e-2 if self.gemm_mode in ("tf32", "bf16") else 1e-4
+        for name, a, b in zip(("recon", "mu", "logvar"), got, out):
+            err = float((a - b).norm() / b.norm().clamp_min(1e-30))
+            if not err <= tol:
+                raise _Mismatch(f"{name} differs from the module's own forward (rel. L2 {err:.2e} > {tol:.0e})")
 
     def _sync_rng(self, force=False):
         off = int(self._gen.get_offset())
@@ -191,7 +257,7 @@ def _wants_engine_ddp(module, args, kwargs):
     if dims is None:
         return None
     pg = kwargs.get("process_group")
-    if pg is not None and dist.is_initialized() and dist.get_world_size(pg) > 1 and dist.get_backend(pg) != "nccl":
+    if dist.is_initialized() and dist.get_world_size(pg) > 1 and not _cuda_leg_is_nccl(pg):
         return None         # e.g. DDP_BACKEND=gloo with CUDA tensors: leave to torch
     return dims
 
@@ -206,7 +272,15 @@ def _make_shims(orig_ddp, orig_adam):
             if cls is DistributedDataParallel and isinstance(module, nn.Module):
                 dims = _wants_engine_ddp(module, args, kwargs)
                 if dims is not None:
-                    return EngineModule(module, dims, kwargs.get("process_group"))
+                    pg = kwargs.get("process_group")
+                    try:
+                        em = EngineModule(module, dims, pg)
+                        _notice(f"DistributedDataParallel(VAE {dims[0]}-{dims[1]}-{dims[2]}) -> B200 engine "
+                                f"(gemm_mode={em.gemm_mode}, group of {em.engine.group_size}, "
+                                f"gradient exchange: {'peer memory' if em.engine.p2p else 'NCCL' if em.engine.group_size > 1 else 'none'})", pg)
+                        return em
+                    except _Mismatch as why:
+                        _notice(f"module has the reference VAE's layers but {why}: left to torch DDP", pg)
             return super().__new__(cls)
 
     class Adam(orig_adam):

@@ -13,7 +13,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from ._lib import MDT_GEMM, SEGMENTS, check, mdt_adam, mdt_cfg
+from ._lib import MDT_EXCHANGE, MDT_GEMM, SEGMENTS, check, mdt_adam, mdt_batch_source, mdt_cfg, mdt_sgd
 
 # reference parameter names, ref:vae-hpo.py:23-27
 REF_NAMES = ("fc1.weight", "fc1.bias", "fc21.weight", "fc21.bias", "fc22.weight", "fc22.bias",
@@ -43,7 +43,9 @@ def nccl_comm_ptr(group, device):
 
 class VAEEngine:
     def __init__(self, in_dim=784, hidden=400, latent=20, max_batch=128, gemm_mode="tf32x3", use_graph=True,
-                 group=None, device=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8):
+                 group=None, device=None, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, exchange=None):
+        """``exchange``: how a group of n > 1 ranks sums its gradients -- "auto" (peer memory for groups of up to
+        MDT_P2P_MAX_RANKS=4 ranks on one node, else NCCL), "nccl", "p2p" (one-shot) or "p2p_two_shot"."""
         if not torch.cuda.is_available():
             raise RuntimeError("multidisttorch_b200.VAEEngine needs a CUDA device; there is no CPU path")
         self.lib = _lib.load()
@@ -53,7 +55,11 @@ class VAEEngine:
         self.group = group
         self.group_size = dist.get_world_size(group) if (group is not None and dist.is_initialized()) else 1
         self.group_rank = dist.get_rank(group) if self.group_size > 1 else 0
-        self.cfg = mdt_cfg(in_dim, hidden, latent, max_batch, MDT_GEMM[gemm_mode], int(bool(use_graph)))
+        if exchange is None:      # environment default (MDT_P2P_ALLREDUCE=0 keeps NCCL everywhere)
+            exchange = {"0": "nccl"}.get(os.environ.get("MDT_P2P_ALLREDUCE", "1"), "auto")
+        self.exchange = exchange
+        self.cfg = mdt_cfg(in_dim, hidden, latent, max_batch, MDT_GEMM[gemm_mode], int(bool(use_graph)),
+                           MDT_EXCHANGE[exchange], 0)
         off = (C.c_int64 * 8)()
         num = (C.c_int64 * 8)()
         tot = C.c_int64()
@@ -82,16 +88,10 @@ class VAEEngine:
             self.stream = torch.cuda.ExternalStream(s.value, device=self.device)
             self.p2p = False
             # Gradient exchange over NVLink peer memory inside the Adam kernel (one-shot, or two-shot when a rank would
-            # read more than 16 MB from its peers) against NCCL in the same build, samples/s:
-            #   2 ranks: 3.19 vs 3.03 M at H=400 (2.6 MB of gradient), 2.27 vs 1.94 M at H=4096 (26.7 MB)
-            #   4 ranks: 11.1 vs 10.9 M at H=400 (2x4 layout), 1.85 vs 1.83 M at H=4096 (two-shot)
-            #   8 ranks: one-shot 7.7 vs 9.1 M at H=400; two-shot not measured on 8 -> NCCL unless forced
-            mode = os.environ.get("MDT_P2P_ALLREDUCE", "1")
+            # read more than 16 MB from its peers) against NCCL: measured figures in DESIGN.md section 5.
             max_ranks = int(os.environ.get("MDT_P2P_MAX_RANKS", "4"))
-            want = self.group_size <= max_ranks
-            if mode == "force":
-                want = self.group_size <= 8
-            if self.group_size > 1 and gemm_mode != "fp32" and mode != "0" and want:
+            want = self.group_size <= max_ranks or exchange in ("p2p", "p2p_two_shot")
+            if self.group_size > 1 and gemm_mode != "fp32" and exchange != "nccl" and want and self.group_size <= 8:
                 self.p2p = self._connect_peers()
         self.set_adam(lr, betas, eps, 0)
 
@@ -180,6 +180,11 @@ class VAEEngine:
         h = mdt_adam(lr, betas[0], betas[1], eps)
         check(self.lib.mdt_engine_set_adam(self._h, C.byref(h), completed_steps))
 
+    def set_sgd(self, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, completed_steps=0):
+        """optim.SGD in place of Adam (mdt_engine_set_sgd); exp_avg becomes the momentum buffer."""
+        h = mdt_sgd(lr, momentum, dampening, weight_decay, int(bool(nesterov)), 0)
+        check(self.lib.mdt_engine_set_sgd(self._h, C.byref(h), completed_steps))
+
     def set_rng(self, seed, offset=0):
         check(self.lib.mdt_engine_set_rng(self._h, seed, offset))
 
@@ -216,6 +221,28 @@ class VAEEngine:
         x = self._x2d(x)
         check(self.lib.mdt_train_step(self._h, _ptr(x), x.shape[0], _ptr(eps), _ptr(self._loss) if want_loss else None))
         return self._loss if want_loss else None
+
+    def train_steps(self, pool, first_batch, n_steps, losses=None):
+        """``n_steps`` consecutive steps on a device-resident pool [n_batches, B, D] (mdt_train_steps): step i trains on
+        ``pool[(first_batch + i) % n_batches]``.  ``losses``: optional device tensor of n_steps floats."""
+        nb, B = pool.shape[0], pool.shape[1]
+        assert pool.dtype == torch.float32 and pool.is_contiguous() and pool.numel() == nb * B * self.D
+        src = mdt_batch_source(pool.data_ptr(), None, None, nb, 0)
+        check(self.lib.mdt_train_steps(self._h, C.byref(src), B, first_batch, n_steps, _ptr(losses)))
+
+    def train_steps_u8(self, images_u8, indices, batch, first_batch, n_steps, losses=None):
+        """Same from a device-resident uint8 image table [n_images, D] and the sampler's int64 index order
+        (batch-major, n_batches * batch entries): gather + /255 run inside each step's first kernel."""
+        assert images_u8.dtype == torch.uint8 and images_u8.is_contiguous() and indices.dtype == torch.int64
+        nb = indices.numel() // batch
+        src = mdt_batch_source(None, images_u8.data_ptr(), indices.data_ptr(), nb, images_u8.shape[0])
+        check(self.lib.mdt_train_steps(self._h, C.byref(src), batch, first_batch, n_steps, _ptr(losses)))
+
+    def exchange_bench(self, iters=20):
+        """Seconds per gradient exchange + optimizer pass of this group (mdt_engine_exchange_bench; scratch engines only)."""
+        s = C.c_double()
+        check(self.lib.mdt_engine_exchange_bench(self._h, iters, C.byref(s)))
+        return float(s.value)
 
     def train_step_staged(self, batch, eps=None, want_loss=True):
         """Step on a batch that is already in the engine's stage buffer (device-resident data path: no copy)."""

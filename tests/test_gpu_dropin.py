@@ -101,3 +101,28 @@ def test_dropin_adam_takes_per_trial_hyperparameters_from_env(monkeypatch):
         assert abs(a - b) <= 2e-5 * abs(b), (got, want)
     for (n, p), (_, q) in zip(wrapped.module.named_parameters(), plain.named_parameters()):
         assert rel_l2(p.detach().cpu().numpy(), q.detach().cpu().numpy()) < 2e-4, n
+
+
+def test_dropin_leaves_lookalike_models_to_torch(capsys):
+    """A model with the reference VAE's layer names and shapes but another forward (here: no sigmoid, LeakyReLU) must
+    NOT be swapped for the reference VAE's math: the shim checks behaviour on a small batch and falls through."""
+    from multidisttorch_b200 import dropin
+
+    class LookAlike(TP.VAEPort):
+        def forward(self, x, eps=None):
+            h1 = F.leaky_relu(self.fc1(x.view(-1, self.in_dim)), 0.2)
+            mu, logvar = self.fc21(h1), self.fc22(h1)
+            z = mu + torch.randn_like(logvar) * torch.exp(0.5 * logvar)
+            return self.fc4(F.leaky_relu(self.fc3(z), 0.2)), mu, logvar
+
+    assert dropin.install() or dropin._ORIG
+    try:
+        m = LookAlike().cuda()
+        with pytest.raises(Exception, match="process group|init_process_group"):   # the real DDP constructor ran
+            torch.nn.parallel.DistributedDataParallel(m, process_group=None)
+        assert "left to torch DDP" in capsys.readouterr().out
+        ok = torch.nn.parallel.DistributedDataParallel(TP.VAEPort().cuda(), process_group=None)
+        assert isinstance(ok, dropin.EngineModule)
+        assert "-> B200 engine" in capsys.readouterr().out
+    finally:
+        dropin.uninstall()

@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol():
     for n in names:
         assert hasattr(lib, n), f"{n} declared in include/mdt_b200.h but not exported"
     assert sorted(_lib.exported_symbols()) == names, "ctypes prototypes and header disagree"
-    assert lib.mdt_version() == 100
+    assert lib.mdt_version() == 200
 
 
 @pytest.mark.parametrize("H", [400, 4096])
