@@ -49,7 +49,9 @@ typedef enum mdt_status {
 typedef enum mdt_gemm_mode {
   MDT_GEMM_FP32 = 0,   /* fp32 FFMA tiles: the tight-tolerance parity path */
   MDT_GEMM_TF32 = 1,   /* tcgen05.mma kind::tf32, TMA-staged, TMEM accumulators */
-  MDT_GEMM_TF32X3 = 2  /* 3-pass split-TF32 on tcgen05 (fp32-grade accuracy) */
+  MDT_GEMM_TF32X3 = 2, /* 3-pass split-TF32 on tcgen05 (fp32-grade accuracy) */
+  MDT_GEMM_BF16 = 3    /* tcgen05.mma kind::f16 on bf16 copies of activations and weights (written by the producing
+                          epilogues), fp32 accumulate, fp32 master weights and Adam: BASELINE config 4 "bf16 GEMMs" */
 } mdt_gemm_mode;
 
 /* How a trial group of n > 1 ranks sums its gradients (the DDP reducer of ref:vae-hpo.py:130). */

@@ -6,7 +6,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "csrc", "libmdt_b200.so")
 
-MDT_GEMM = {"fp32": 0, "tf32": 1, "tf32x3": 2}
+MDT_GEMM = {"fp32": 0, "tf32": 1, "tf32x3": 2, "bf16": 3}
 MDT_ACT = {"none": 0, "relu": 1, "sigmoid": 2}
 MDT_EXCHANGE = {"auto": 0, "nccl": 1, "p2p": 2, "p2p_two_shot": 3}
 SEGMENTS = ("W1", "b1", "W2x", "b2x", "W3", "b3", "W4", "b4")

@@ -18,6 +18,7 @@
 #pragma once
 
 #include <cuda.h>
+#include <cuda_bf16.h>
 
 #include <map>
 
@@ -97,6 +98,15 @@ __device__ __forceinline__ void mma_tf32(uint32_t tmem_d, uint64_t adesc, uint64
       "{\n\t.reg .pred p;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
       "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// D[tmem] (+)= A[smem] . B[smem]^T, bf16 (or fp16) inputs as the instruction descriptor says, fp32 accumulate.
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
@@ -183,6 +193,29 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// Instruction descriptor, kind::f16 with BF16 operands: D format F32 (bits [4,6) = 1), A and B format BF16 (bits [7,10)
+// and [10,13) = 1), both K-major, N >> 3 in [17,23), M >> 4 in [24,29).  UMMA_K = 16 (32 bytes, like tf32's 8 x 4).
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// ------------------------------------------------------------------------------------------------
+// bf16 operand mirrors (MDT_GEMM_BF16): every buffer a GEMM reads through TMA exists as bf16; the kernel that produces
+// the fp32 value writes the mirror too.  Buffers that are ONLY GEMM operands (the transposed activations) hold bf16
+// instead of fp32 in that mode -- `b16` selects the element type of such a store.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_operand(void* base, size_t idx, float v, bool b16) {
+  if (b16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+  else reinterpret_cast<float*>(base)[idx] = v;
+}
+__device__ __forceinline__ void st_bf16x4(__nv_bfloat16* dst, float4 v) {      // dst 8-byte aligned
+  const __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+  uint2 u;
+  u.x = *reinterpret_cast<const uint32_t*>(&lo);
+  u.y = *reinterpret_cast<const uint32_t*>(&hi);
+  *reinterpret_cast<uint2*>(dst) = u;
+}
+
 // ------------------------------------------------------------------------------------------------
 // epilogues
 // ------------------------------------------------------------------------------------------------
@@ -198,20 +231,20 @@ enum Tc05EpiKind {
 struct Tc05Epi {
   // generic
   float* C; int ldc;
-  float* CT; int ldct;
+  void* CT; int ldct;          // transposed copy: fp32, or bf16 when `bf16` is set
   const float* bias; int act;
   const float* mask; int ldmask;
   // reparameterisation (forward)
   const float* eps_in; StepState* st; long long philox_S; unsigned long long philox_inc;
-  float *z, *zT, *eps_out, *sd_out, *dml_kl; int Z; int ldzT;
+  float *z; void* zT; float *eps_out, *sd_out, *dml_kl; int Z; int ldzT;
   float* kl_partials;
   // BCE
-  const float* x; int ldx; float* da4; float* da4T; int ld_da4T;
+  const float* x; int ldx; float* da4; void* da4T; int ld_da4T;
   float* bce_partials; unsigned int* ticket; float* loss_out; int n_kl_partials;
   // weight gradient
   const float* a_src; int lda_src; float* db;
   // reparameterisation (backward)
-  const float *eps, *sd; float *dml, *dmlT; int ld_dmlT;
+  const float *eps, *sd; float *dml; void* dmlT; int ld_dmlT;
   // weight-gradient GEMM with the Adam update fused in (single-rank trial groups): parameter / moment segments of
   // this weight (same [M][ldc] layout as the gradient), its transposed shadow (or NULL), the bias segments, the
   // device-resident step state and, for the CTA that takes the step's last ticket, the loss partials to add up
@@ -224,6 +257,13 @@ struct Tc05Epi {
   int a_tmem;    // TF32X3: the split warps put hi / lo of the A tile into tensor memory (MMA TS form) instead of
                  // writing lo next to it in shared memory -- the MMAs then read only B from shared memory
   int cluster;   // split-K CTAs of a tile form a thread-block cluster (1,1,splits): partials are exchanged through DSMEM
+  // MDT_GEMM_BF16: operands are bf16 (kind::f16, 64 K-values per k-block); transposed outputs (CT, da4T, zT, dmlT,
+  // adam_pT16) hold bf16; Cb / da4b / zb / dmlb are row-major bf16 mirrors of C / da4 / z / dml (or NULL)
+  int bf16;
+  __nv_bfloat16* Cb; int ldcb;
+  __nv_bfloat16* da4b; __nv_bfloat16* zb; int ldzb; __nv_bfloat16* dmlb;
+  __nv_bfloat16* adam_p16; int adam_ldp16;      // row-major bf16 copy of the updated weight
+  __nv_bfloat16* adam_pT16;                     // transposed bf16 shadow of the updated weight (leading dim adam_ldpT)
   int pre_a, pre_b;  // the A / B operand is not written by any kernel of this step before this one (a weight or its
                      // transposed shadow: last written a whole step ago): its TMA loads for the first ring pass are issued
                      // BEFORE griddepcontrol.wait, so they land while the predecessor kernel is still running
@@ -274,22 +314,22 @@ __device__ __forceinline__ float fast_dlogit(float r, float x) {
 // Transposed store of the tile: thread = (tile row, column half); reads float4 from its row, writes four scalars,
 // each of which is coalesced across the warp (consecutive lanes = consecutive m).
 template <int BN>
-__device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, float* CT, int ldct, int m0, int n0, int M,
-                                                      int N, int et) {
+__device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, void* CT, int ldct, int m0, int n0, int M,
+                                                      int N, int et, bool b16 = false) {
   const int r = et % kTcBM, ch = et / kTcBM;     // 256 threads: two column halves
   const int m = m0 + r;
   if (m >= M) return;
   constexpr int HALF = BN / 2;
   const float* trow = T + r * ldt + ch * HALF;
-  float* tp = CT + (size_t)(n0 + ch * HALF) * ldct + m;
+  const size_t base = (size_t)(n0 + ch * HALF) * ldct + m;
   const int cvalid = N - n0 - ch * HALF;         // columns of this half that exist
 #pragma unroll
   for (int c = 0; c < HALF; c += 4) {
     const float4 t = *reinterpret_cast<const float4*>(trow + c);
-    if (c + 0 < cvalid) tp[(size_t)(c + 0) * ldct] = t.x;
-    if (c + 1 < cvalid) tp[(size_t)(c + 1) * ldct] = t.y;
-    if (c + 2 < cvalid) tp[(size_t)(c + 2) * ldct] = t.z;
-    if (c + 3 < cvalid) tp[(size_t)(c + 3) * ldct] = t.w;
+    if (c + 0 < cvalid) st_operand(CT, base + (size_t)(c + 0) * ldct, t.x, b16);
+    if (c + 1 < cvalid) st_operand(CT, base + (size_t)(c + 1) * ldct, t.y, b16);
+    if (c + 2 < cvalid) st_operand(CT, base + (size_t)(c + 2) * ldct, t.z, b16);
+    if (c + 3 < cvalid) st_operand(CT, base + (size_t)(c + 3) * ldct, t.w, b16);
   }
 }
 
@@ -297,19 +337,19 @@ __device__ __forceinline__ void tc05_store_transposed(const float* T, int ldt, f
 // columns), one float4 read and 4 coalesced scalar stores.  Used when the passes of a tile are shared out among the
 // CTAs of a split-K cluster.
 template <int BN>
-__device__ __forceinline__ void tc05_store_transposed_rows(const float* T, int ldt, float* CT, int ldct, int m0, int n0,
-                                                           int M, int N, int et, int row_lo) {
+__device__ __forceinline__ void tc05_store_transposed_rows(const float* T, int ldt, void* CT, int ldct, int m0, int n0,
+                                                           int M, int N, int et, int row_lo, bool b16 = false) {
   constexpr int RPP = kTcEpiThreads / (BN / 4);
   const int r = row_lo + et % RPP, c0 = (et / RPP) * 4;
   const int m = m0 + r;
   if (m >= M) return;
   const float4 t = *reinterpret_cast<const float4*>(T + r * ldt + c0);
-  float* tp = CT + (size_t)(n0 + c0) * ldct + m;
+  const size_t base = (size_t)(n0 + c0) * ldct + m;
   const int cvalid = N - n0 - c0;
-  if (0 < cvalid) tp[0] = t.x;
-  if (1 < cvalid) tp[(size_t)ldct] = t.y;
-  if (2 < cvalid) tp[(size_t)2 * ldct] = t.z;
-  if (3 < cvalid) tp[(size_t)3 * ldct] = t.w;
+  if (0 < cvalid) st_operand(CT, base, t.x, b16);
+  if (1 < cvalid) st_operand(CT, base + (size_t)ldct, t.y, b16);
+  if (2 < cvalid) st_operand(CT, base + (size_t)2 * ldct, t.z, b16);
+  if (3 < cvalid) st_operand(CT, base + (size_t)3 * ldct, t.w, b16);
 }
 
 // Global inputs of the element-wise epilogues (bias, ReLU mask / BCE target) that do not depend on this kernel's own
@@ -408,7 +448,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
   const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
   if (kEpi == EPI_BIAS_ACT || kEpi == EPI_RELU_MASK || kEpi == EPI_GRADW) {
     float* const Cp = ep.C;
-    float* const CTp0 = (kEpi != EPI_GRADW) ? ep.CT : nullptr;
+    void* const CTp0 = (kEpi != EPI_GRADW) ? ep.CT : nullptr;
     const int ldc = ep.ldc, act = ep.act;
     float4 v[ITERS];
 #pragma unroll
@@ -443,7 +483,15 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       for (int i = 0; i < ITERS; ++i)
         if (i < rows_valid && (i % it_ns) == it_rank) *reinterpret_cast<float4*>(cp + i * cstep) = v[i];
     }
-    float* CTp = CTp0;
+    if (kEpi != EPI_GRADW && ep.Cb != nullptr) {          // bf16 mirror of the activation (operand of a later GEMM)
+      __nv_bfloat16* const cb = ep.Cb + (size_t)(m0 + rbase) * ep.ldcb + n;
+      const size_t cstep = (size_t)RPP * ep.ldcb;
+#pragma unroll
+      for (int i = 0; i < ITERS; ++i)
+        if (i < rows_valid && (i % it_ns) == it_rank) st_bf16x4(cb + i * cstep, v[i]);
+    }
+    void* CTp = CTp0;
+    bool ct16 = ep.bf16 != 0;                              // element type of the transposed store below
     if (kEpi == EPI_GRADW && ep.adam_p != nullptr) {
       // fused Adam on this tile of the weight (adam_elem_fast: same formula as adam_flat_kernel, SFU sqrt/quotient)
       const float step_size = pre.as[0], bc2_sqrt = __frcp_rn(pre.as[1]), omb1 = pre.as[2], b2 = pre.as[3], omb2 = pre.as[4],
@@ -483,17 +531,32 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
           v[i0 + c] = pp[c];                               // the updated weight feeds the transposed shadow below
         }
       }
+      if (ep.adam_p16 != nullptr) {                        // bf16 mode: the GEMMs of the next step read this copy
+        __nv_bfloat16* const wb = ep.adam_p16 + (size_t)(m0 + rbase) * ep.adam_ldp16 + n;
+        const size_t wstep = (size_t)RPP * ep.adam_ldp16;
+#pragma unroll
+        for (int i = 0; i < ITERS; ++i)
+          if (i < rows_valid && (i % it_ns) == it_rank) st_bf16x4(wb + i * wstep, v[i]);
+      }
       CTp = ep.adam_pT;
+      ct16 = false;                                        // the fp32 shadow (read by the CUDA-core latent kernels)
     }
     const int ldct = (kEpi == EPI_GRADW) ? ep.adam_ldpT : ep.ldct;
-    if (CTp != nullptr) {
+    void* const CT16 = (kEpi == EPI_GRADW) ? (void*)ep.adam_pT16 : nullptr;   // second, bf16 shadow of an updated weight
+    if (CTp != nullptr || CT16 != nullptr) {
 #pragma unroll
       for (int i = 0; i < ITERS; ++i) *reinterpret_cast<float4*>(T + (rbase + i * RPP) * ldt + 4 * c4) = v[i];
       ptx::bar_sync_epi();
-      if (it_ns == 1) {
-        tc05_store_transposed<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et);
-      } else {
-        for (int i = it_rank; i < ITERS; i += it_ns) tc05_store_transposed_rows<BN>(T, ldt, CTp, ldct, m0, n0, M, N, et, i * RPP);
+#pragma unroll
+      for (int pass = 0; pass < 2; ++pass) {
+        void* const dst = pass == 0 ? CTp : CT16;
+        const bool b16 = pass == 0 ? ct16 : true;
+        if (dst == nullptr) continue;
+        if (it_ns == 1) {
+          tc05_store_transposed<BN>(T, ldt, dst, ldct, m0, n0, M, N, et, b16);
+        } else {
+          for (int i = it_rank; i < ITERS; i += it_ns) tc05_store_transposed_rows<BN>(T, ldt, dst, ldct, m0, n0, M, N, et, i * RPP, b16);
+        }
       }
     }
   } else if (kEpi == EPI_SIGMOID_BCE) {
@@ -523,6 +586,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
       if (ok) {
         *reinterpret_cast<float4*>(rp + i * cstep) = r;
         *reinterpret_cast<float4*>(gp + i * cstep) = g;
+        if (ep.da4b != nullptr) st_bf16x4(ep.da4b + (size_t)(m0 + rbase) * ldc + n + i * cstep, g);
       }
       v[i] = g;
     }
@@ -532,10 +596,10 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     if (lane == 0) red[ew] = part;
     ptx::bar_sync_epi();
     if (it_ns == 1) {
-      tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et);
+      tc05_store_transposed<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et, ep.bf16 != 0);
     } else {
       for (int i = it_rank; i < ITERS; i += it_ns)
-        tc05_store_transposed_rows<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et, i * RPP);
+        tc05_store_transposed_rows<BN>(T, ldt, ep.da4T, ep.ld_da4T, m0, n0, M, N, et, i * RPP, ep.bf16 != 0);
     }
     // per-CTA partial only: the loss itself is not needed by any later kernel of the step, so the fixed-order sum
     // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here.
@@ -583,7 +647,8 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
         ep.C[m * 2 * Z + j] = mu;
         ep.C[m * 2 * Z + Z + j] = lv;
         ep.z[m * Z + j] = zv;
-        ep.zT[(size_t)j * ep.ldzT + m] = zv;
+        st_operand(ep.zT, (size_t)j * ep.ldzT + m, zv, ep.bf16 != 0);
+        if (ep.zb != nullptr) ep.zb[m * ep.ldzb + j] = __float2bfloat16_rn(zv);
         if (ep.eps_out != ep.eps_in) ep.eps_out[m * Z + j] = e;
         ep.sd_out[m * Z + j] = sd;
         ep.dml_kl[m * 2 * Z + j] = mu;
@@ -630,8 +695,12 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
         const float dlv = g * sE[idx] * sS[idx] * 0.5f + sK[n * 2 * Z + Z + j];
         ep.dml[m * 2 * Z + j] = dmu;
         ep.dml[m * 2 * Z + Z + j] = dlv;
-        ep.dmlT[(size_t)j * ep.ld_dmlT + m] = dmu;
-        ep.dmlT[(size_t)(Z + j) * ep.ld_dmlT + m] = dlv;
+        st_operand(ep.dmlT, (size_t)j * ep.ld_dmlT + m, dmu, ep.bf16 != 0);
+        st_operand(ep.dmlT, (size_t)(Z + j) * ep.ld_dmlT + m, dlv, ep.bf16 != 0);
+        if (ep.dmlb != nullptr) {
+          ep.dmlb[m * 2 * Z + j] = __float2bfloat16_rn(dmu);
+          ep.dmlb[m * 2 * Z + Z + j] = __float2bfloat16_rn(dlv);
+        }
       }
     }
   }
@@ -654,7 +723,9 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int n0 = blockIdx.x * BN, m0 = blockIdx.y * kTcBM;
   // split-K: gridDim.z CTAs share one output tile, each streaming a contiguous range of k-blocks
-  const int total_kb = (K + kTcBK - 1) / kTcBK;
+  // elements of K per k-block: one 128-byte swizzle row = 32 fp32 (tf32 kinds) or 64 bf16 (kind::f16)
+  const int kbk = (!kSplit && ep.bf16) ? 2 * kTcBK : kTcBK;
+  const int total_kb = (K + kbk - 1) / kbk;
   const int kb_per_split = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
   const int kb0 = (int)blockIdx.z * kb_per_split;
   const int num_kb = min(kb_per_split, total_kb - kb0);      // >= 1 (the host picks gridDim.z accordingly)
@@ -710,8 +781,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int kb = 0; kb < pre_kb; ++kb) {
       const uint32_t sa = smem_base + kb * S::STAGE;
       ptx::mbar_expect_tx(bar_full + 8 * kb, S::HB);
-      if (ep.pre_a) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * kb);
-      if (ep.pre_b) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * kb);
+      if (ep.pre_a) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kbk, m0, bar_full + 8 * kb);
+      if (ep.pre_b) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kbk, n0, bar_full + 8 * kb);
     }
   }
   Tc05Pre<BN> pre;
@@ -737,8 +808,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
           ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
         }
-        if (!(early && ep.pre_a)) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kTcBK, m0, bar_full + 8 * s);
-        if (!(early && ep.pre_b)) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kTcBK, n0, bar_full + 8 * s);
+        if (!(early && ep.pre_a)) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kbk, m0, bar_full + 8 * s);
+        if (!(early && ep.pre_b)) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kbk, n0, bar_full + 8 * s);
       }
       TC_STAMP(2);
     }
@@ -747,6 +818,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = umma_idesc_tf32(kTcBM, BN);
+      constexpr uint32_t idesc16 = umma_idesc_bf16(kTcBM, BN);
+      const bool b16 = !kSplit && ep.bf16 != 0;
       for (int kb = 0; kb < num_kb; ++kb) {
         const int s = kb % S::STAGES;
         const uint32_t ph = (kb / S::STAGES) & 1;
@@ -776,6 +849,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
             ptx::mma_tf32(td, a_lo + koff, b_hi + koff, idesc, k ? 1u : 0u);
             ptx::mma_tf32(td, a_hi + koff, b_lo + koff, idesc, 1u);
             ptx::mma_tf32(td, a_hi + koff, b_hi + koff, idesc, 1u);
+          } else if (b16) {                         // 16 bf16 K-values per instruction: the same 32-byte step
+            ptx::mma_f16(td, a_hi + koff, b_hi + koff, idesc16, (kb | k) ? 1u : 0u);
           } else {
             ptx::mma_tf32(td, a_hi + koff, b_hi + koff, idesc, (kb | k) ? 1u : 0u);
           }
@@ -839,6 +914,29 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       float acc[RW];
 #pragma unroll
       for (int i = 0; i < RW; ++i) acc[i] = 0.f;
+      if (!kSplit && ep.bf16) {
+        // the A operand is bf16 here: 8 values per 16-byte load (rows are 16-byte aligned: lda % 8 == 0)
+        const __nv_bfloat16* const ab = reinterpret_cast<const __nv_bfloat16*>(ep.a_src) + (size_t)(m0 + ew * RW) * ep.lda_src;
+        const int K8 = K & ~7;
+        for (int k = 8 * lane; k < K8; k += 256) {
+          uint4 t[RW];
+#pragma unroll
+          for (int i = 0; i < RW; ++i)
+            t[i] = (i < rows_here) ? __ldg(reinterpret_cast<const uint4*>(ab + i * lda + k)) : make_uint4(0u, 0u, 0u, 0u);
+#pragma unroll
+          for (int i = 0; i < RW; ++i) {
+            const uint32_t w[4] = {t[i].x, t[i].y, t[i].z, t[i].w};
+            float s8 = 0.f;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) s8 += __uint_as_float(w[q] << 16) + __uint_as_float(w[q] & 0xffff0000u);
+            acc[i] += s8;
+          }
+        }
+        for (int k = K8 + lane; k < K; k += 32) {
+#pragma unroll
+          for (int i = 0; i < RW; ++i) acc[i] += (i < rows_here) ? __bfloat162float(ab[i * lda + k]) : 0.f;
+        }
+      } else {
       const int K4 = K & ~3;                               // lda is a multiple of 4 floats: rows are 16-byte aligned
       for (int k = 4 * lane; k < K4; k += 128) {           // RW independent 16-byte loads in flight per step
         float4 t[RW];
@@ -851,6 +949,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       for (int k = K4 + lane; k < K; k += 32) {            // ragged batch tail
 #pragma unroll
         for (int i = 0; i < RW; ++i) acc[i] += (i < rows_here) ? __ldg(abase + i * lda + k) : 0.f;
+      }
       }
       float mine = 0.f;                                   // lane i keeps the sum of row i
 #pragma unroll
@@ -1086,14 +1185,38 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
 // ------------------------------------------------------------------------------------------------
 struct TrJob {
   const float* in;   // [R][ld_in]
-  float* out;        // [C][ld_out]
+  void* out;         // [C][ld_out] transposed copy, fp32 (or bf16 when out_is16), may be NULL
   int R, C, ld_in, ld_out;
   int tile_begin, tiles_c;
+  // MDT_GEMM_BF16 operand mirrors written in the same pass (NULL when not wanted)
+  int out_is16;
+  __nv_bfloat16* out_t16;              // second transposed copy, bf16, leading dimension ld_out
+  __nv_bfloat16* copy16; int ld_copy16;   // row-major bf16 copy [R][ld_copy16]
 };
 struct TrArgs {
   TrJob job[4];
   int njobs;
 };
+
+// One 32 x 32 tile of a job: t[][] holds the tile; writes whatever outputs the job asks for.
+__device__ __forceinline__ void tr_store_tile(const TrJob& job, float (*t)[33], int r0, int c0, int tx, int ty) {
+#pragma unroll
+  for (int i = ty; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + tx;
+    if (c < job.C && r < job.R) {
+      const float v = t[tx][i];
+      if (job.out != nullptr) st_operand(job.out, (size_t)c * job.ld_out + r, v, job.out_is16 != 0);
+      if (job.out_t16 != nullptr) job.out_t16[(size_t)c * job.ld_out + r] = __float2bfloat16_rn(v);
+    }
+  }
+  if (job.copy16 != nullptr) {
+#pragma unroll
+    for (int i = ty; i < 32; i += 8) {
+      const int r = r0 + i, c = c0 + tx;
+      if (r < job.R && c < job.C) job.copy16[(size_t)r * job.ld_copy16 + c] = __float2bfloat16_rn(t[i][tx]);
+    }
+  }
+}
 
 __global__ void __launch_bounds__(256) transpose_kernel(TrArgs a) {
   __shared__ float t[32][33];
@@ -1113,10 +1236,16 @@ __global__ void __launch_bounds__(256) transpose_kernel(TrArgs a) {
     t[i][tx] = (r < job.R && c < job.C) ? job.in[(size_t)r * job.ld_in + c] : 0.f;
   }
   __syncthreads();
-#pragma unroll
-  for (int i = ty; i < 32; i += 8) {
-    const int c = c0 + i, r = r0 + tx;
-    if (c < job.C && r < job.R) job.out[(size_t)c * job.ld_out + r] = t[tx][i];
+  tr_store_tile(job, t, r0, c0, tx, ty);
+}
+
+// rows of an fp32 matrix -> bf16 (leading dimensions may differ): mdt_decode's z in bf16 mode
+__global__ void __launch_bounds__(256) rows_to_bf16_kernel(const float* in, int ld_in, __nv_bfloat16* out, int ld_out, int R, int C) {
+  pdl_wait();
+  pdl_trigger();
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < R * C; i += gridDim.x * blockDim.x) {
+    const int r = i / C, c = i - r * C;
+    out[(size_t)r * ld_out + c] = __float2bfloat16_rn(in[(size_t)r * ld_in + c]);
   }
 }
 
@@ -1175,11 +1304,7 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
       if (ok && a.x_copy != nullptr) a.x_copy[(size_t)r * job.C + c] = v;
     }
     __syncthreads();
-#pragma unroll
-    for (int i = ty; i < 32; i += 8) {
-      const int c = c0 + i, r = r0 + tx;
-      if (c < job.C && r < job.R) job.out[(size_t)c * job.ld_out + r] = t[tx][i];
-    }
+    tr_store_tile(job, t, r0, c0, tx, ty);
     return;
   }
   const unsigned long long seed = a.st->philox_seed, offset = a.st->philox_offset;
@@ -1198,9 +1323,11 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
   }
 }
 
-inline int tr_add(TrArgs& a, int& blocks, const float* in, float* out, int R, int C, int ld_in, int ld_out) {
+inline int tr_add(TrArgs& a, int& blocks, const float* in, void* out, int R, int C, int ld_in, int ld_out, bool out_is16 = false,
+                  __nv_bfloat16* out_t16 = nullptr, __nv_bfloat16* copy16 = nullptr, int ld_copy16 = 0) {
   TrJob& j = a.job[a.njobs++];
   j.in = in; j.out = out; j.R = R; j.C = C; j.ld_in = ld_in; j.ld_out = ld_out;
+  j.out_is16 = out_is16 ? 1 : 0; j.out_t16 = out_t16; j.copy16 = copy16; j.ld_copy16 = ld_copy16;
   j.tile_begin = blocks; j.tiles_c = (C + 31) / 32;
   blocks += ((R + 31) / 32) * j.tiles_c;
   return 0;
@@ -1225,18 +1352,20 @@ inline PFN_mdt_encodeTiled tc05_encode_fn() {
   return fn;
 }
 
-// K-major fp32 matrix [rows][K] with leading dimension ld (floats); box = box_rows x 32 floats, SWIZZLE_128B.
-inline int tc05_encode(CUtensorMap* out, const float* ptr, int rows, int K, int ld, int box_rows) {
+// K-major matrix [rows][K] with leading dimension ld (elements), fp32 or bf16; box = box_rows x one 128-byte swizzle row
+// (32 fp32 / 64 bf16), SWIZZLE_128B.
+inline int tc05_encode(CUtensorMap* out, const void* ptr, int rows, int K, int ld, int box_rows, bool bf16 = false) {
   PFN_mdt_encodeTiled fn = tc05_encode_fn();
   if (!fn) return set_error(MDT_ERR_UNSUPPORTED, "cuTensorMapEncodeTiled is not available from this driver");
+  const int esz = bf16 ? 2 : 4;
   MDT_CHECK(rows > 0 && K > 0 && ld >= K, "tensor map: bad shape rows=%d K=%d ld=%d", rows, K, ld);
-  MDT_CHECK(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && (ld % 4) == 0, "tensor map: base and row pitch must be 16-byte aligned");
+  MDT_CHECK(reinterpret_cast<uintptr_t>(ptr) % 16 == 0 && ((size_t)ld * esz) % 16 == 0, "tensor map: base and row pitch must be 16-byte aligned");
   cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
-  cuuint64_t strides[1] = {(cuuint64_t)ld * sizeof(float)};
-  cuuint32_t box[2] = {(cuuint32_t)kTcBK, (cuuint32_t)box_rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * esz};
+  cuuint32_t box[2] = {(cuuint32_t)(128 / esz), (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+  CUresult r = fn(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(ptr), dims,
+                  strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_error(MDT_ERR_CUDA, "cuTensorMapEncodeTiled failed with CUresult %d", (int)r);
   return MDT_OK;
@@ -1307,7 +1436,8 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
 inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc05Epi& ep, size_t ws_floats) {
   if (ep.ws == nullptr || ep.ws_counters == nullptr) return 1;
   const int tiles = ((N + bn - 1) / bn) * ((M + kTcBM - 1) / kTcBM);
-  const int total_kb = (K + kTcBK - 1) / kTcBK;
+  const int kbk = ep.bf16 ? 2 * kTcBK : kTcBK;
+  const int total_kb = (K + kbk - 1) / kbk;
   // at least 3 k-blocks per split (4 without the cluster exchange, whose reduction costs ~1.5 us less: measured)
   const int min_kb = getenv("MDT_MIN_KB_PER_SPLIT") ? atoi(getenv("MDT_MIN_KB_PER_SPLIT"))
                                                            : (getenv("MDT_NO_CLUSTER_SPLITK") ? 4 : 3);
@@ -1350,6 +1480,7 @@ struct Tc05Buffers {
   StepState* st;
   int sm_count, max_threads_sm;
   bool split3;
+  bool bf16;          // MDT_GEMM_BF16: bf16 operand mirrors, kind::f16 MMAs (fp32 accumulate, fp32 master weights and Adam)
   void* note_ctx;
   int (*note)(void* ctx, const char* label);   // engine book-keeping after every kernel launch
   const bool* serial;                          // when *serial is true (per-kernel profiling) nothing is forked
@@ -1375,6 +1506,11 @@ struct Tc05Plan {
   int bn_dwa;         // BLOCK_N of the Adam-fused weight-gradient GEMMs (narrow: the update's traffic is bound per SM)
   char* slab = nullptr;
   float *xT, *h1T, *zT, *h3T, *da4T, *da3T, *dmlT, *da1T, *W4T, *W3T, *W2xT, *kl_partials, *bce_partials, *ws, *ws_dw;
+  // MDT_GEMM_BF16 operand mirrors (row-major activations, weights and weight shadows); in that mode the transposed
+  // activations above hold bf16 as well
+  __nv_bfloat16 *x16 = nullptr, *h1_16 = nullptr, *z16 = nullptr, *h3_16 = nullptr, *da4_16 = nullptr, *da3_16 = nullptr, *dml16 = nullptr;
+  __nv_bfloat16 *W1_16 = nullptr, *W2x_16 = nullptr, *W3_16 = nullptr, *W4_16 = nullptr, *W4T_16 = nullptr, *W3T_16 = nullptr, *W2xT_16 = nullptr;
+  int ldz16 = 0;      // leading dimension of z16 / W3_16 (Z rounded up to 8: 16-byte rows)
   unsigned int* ticket;
   unsigned int* ws_counters;
   static constexpr size_t kWsFloats = 2u << 20;   // 8 MB split-K workspace
@@ -1408,9 +1544,19 @@ inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
   const Tc05Buffers& b = p->b;
   TrArgs a{};
   int blocks = 0;
-  tr_add(a, blocks, b.params + b.L.off[W4], p->W4T, b.D, b.H, b.H, b.D);
-  tr_add(a, blocks, b.params + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H);
-  tr_add(a, blocks, b.params + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z);
+  const float* P = b.params;
+  if (b.bf16) {
+    // bf16 mode: W4^T is only a GEMM operand (bf16 shadow); W3^T / W2x^T are also read in fp32 by the CUDA-core latent
+    // kernels; every weight gets a row-major bf16 copy
+    tr_add(a, blocks, P + b.L.off[W4], nullptr, b.D, b.H, b.H, b.D, false, p->W4T_16, p->W4_16, b.H);
+    tr_add(a, blocks, P + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H, false, p->W3T_16, p->W3_16, p->ldz16);
+    tr_add(a, blocks, P + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z, false, p->W2xT_16, p->W2x_16, b.H);
+    tr_add(a, blocks, P + b.L.off[W1], nullptr, b.H, b.D, b.D, b.H, false, nullptr, p->W1_16, b.D);
+  } else {
+    tr_add(a, blocks, P + b.L.off[W4], p->W4T, b.D, b.H, b.H, b.D);
+    tr_add(a, blocks, P + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H);
+    tr_add(a, blocks, P + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z);
+  }
   MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
   TC_NOTE(p, "weights_T");
   return MDT_OK;
@@ -1432,7 +1578,7 @@ inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* n
   int ns = 1;
   if (!getenv("MDT_NO_SPLITK")) {
     Tc05Epi e{};
-    e.ws = p->ws; e.ws_counters = p->ws_counters;
+    e.ws = p->ws; e.ws_counters = p->ws_counters; e.bf16 = p->b.bf16 ? 1 : 0;
     ns = tc05_pick_splits(B, D, p->b.H, p->bn_fc4, tc05_sms(p), e, Tc05Plan::kWsFloats);
   }
   *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM) * ns;
@@ -1457,7 +1603,8 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   (void)tc05_dbg_buffer();          // allocate the optional phase-timing buffer outside any stream capture
   Tc05Plan* p = new Tc05Plan();
   p->b = b;
-  p->ldB = (int)round_up(b.Bmax, 4);
+  p->ldB = (int)round_up(b.Bmax, b.bf16 ? 8 : 4);      // 16-byte rows of the transposed activations
+  p->ldz16 = (int)round_up(b.Z, 8);
   p->bn_h = b.H >= 2048 ? 64 : 32;
   p->bn_d = b.Bmax > 512 ? 64 : 32;
   p->bn_fc4 = b.Bmax > 512 ? 64 : 32;   // 32: 25 tiles x 4 splits still fit as co-resident clusters (16: 49 x 3 do not)
@@ -1480,8 +1627,16 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
                   {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
                   {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, 2 * Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 8192}};
+  // bf16 operand mirrors: sizes in bf16 elements
+  struct Item16 { __nv_bfloat16** ptr; size_t n; };
+  const size_t Bm = b.Bmax, lz = p->ldz16;
+  Item16 items16[] = {{&p->x16, Bm * D}, {&p->h1_16, Bm * H}, {&p->z16, Bm * lz}, {&p->h3_16, Bm * H}, {&p->da4_16, Bm * D},
+                      {&p->da3_16, Bm * H}, {&p->dml16, Bm * 2 * Z}, {&p->W1_16, H * D}, {&p->W2x_16, 2 * Z * H}, {&p->W3_16, H * lz},
+                      {&p->W4_16, D * H}, {&p->W4T_16, H * D}, {&p->W3T_16, Z * H}, {&p->W2xT_16, H * 2 * Z}};
   size_t bytes = 256;
   for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
+  if (b.bf16)
+    for (auto& it : items16) bytes += (it.n * sizeof(__nv_bfloat16) + 255) / 256 * 256;
   cudaError_t ce = cudaMalloc(&p->slab, bytes);
   if (ce != cudaSuccess) { delete p; return set_error(MDT_ERR_CUDA, "cudaMalloc(%zu) for the tcgen05 plan: %s", bytes, cudaGetErrorString(ce)); }
   cudaMemsetAsync(p->slab, 0, bytes, s);
@@ -1489,6 +1644,8 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->ticket = reinterpret_cast<unsigned int*>(q);
   q += 256;
   for (auto& it : items) { *it.ptr = reinterpret_cast<float*>(q); q += (it.n * sizeof(float) + 255) / 256 * 256; }
+  if (b.bf16)
+    for (auto& it : items16) { *it.ptr = reinterpret_cast<__nv_bfloat16*>(q); q += (it.n * sizeof(__nv_bfloat16) + 255) / 256 * 256; }
   int r = MDT_OK;
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&p->side2, cudaStreamNonBlocking) != cudaSuccess ||
@@ -1502,13 +1659,15 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
     if (r == MDT_OK && cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
   if (r == MDT_OK && cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming) != cudaSuccess) r = set_error(MDT_ERR_CUDA, "event");
   const float* P = b.params;
-  if (r == MDT_OK) r = tc05_encode(&p->mW1, P + b.L.off[W1], b.H, b.D, b.D, p->bn_h);
-  if (r == MDT_OK) r = tc05_encode(&p->mW2x, P + b.L.off[W2X], 2 * b.Z, b.H, b.H, kTcBM);
-  if (r == MDT_OK) r = tc05_encode(&p->mW3, P + b.L.off[W3], b.H, b.Z, b.Z, p->bn_h);
-  if (r == MDT_OK) r = tc05_encode(&p->mW4, P + b.L.off[W4], b.D, b.H, b.H, p->bn_fc4);
-  if (r == MDT_OK) r = tc05_encode(&p->mW4T, p->W4T, b.H, b.D, b.D, p->bn_h);
-  if (r == MDT_OK) r = tc05_encode(&p->mW3T, p->W3T, b.Z, b.H, b.H, kTcBM);
-  if (r == MDT_OK) r = tc05_encode(&p->mW2xT, p->W2xT, b.H, 2 * b.Z, 2 * b.Z, p->bn_h);
+  const bool bf = b.bf16;
+  // weight operands: the fp32 parameters themselves (tf32 kinds), or their bf16 copies
+  if (r == MDT_OK) r = tc05_encode(&p->mW1, bf ? (const void*)p->W1_16 : P + b.L.off[W1], b.H, b.D, b.D, p->bn_h, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW2x, bf ? (const void*)p->W2x_16 : P + b.L.off[W2X], 2 * b.Z, b.H, b.H, kTcBM, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW3, bf ? (const void*)p->W3_16 : P + b.L.off[W3], b.H, b.Z, bf ? p->ldz16 : b.Z, p->bn_h, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW4, bf ? (const void*)p->W4_16 : P + b.L.off[W4], b.D, b.H, b.H, p->bn_fc4, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW4T, bf ? (const void*)p->W4T_16 : p->W4T, b.H, b.D, b.D, p->bn_h, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW3T, bf ? (const void*)p->W3T_16 : p->W3T, b.Z, b.H, b.H, kTcBM, bf);
+  if (r == MDT_OK) r = tc05_encode(&p->mW2xT, bf ? (const void*)p->W2xT_16 : p->W2xT, b.H, 2 * b.Z, 2 * b.Z, p->bn_h, bf);
   if (r == MDT_OK) r = tc05_weight_shadows(p, s);
   if (r != MDT_OK) { tc05_destroy(p); return r; }
   *out = p;
@@ -1521,26 +1680,29 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
     const Tc05Buffers& b = p->b;
     Tc05ActMaps m;
     const int ldB = p->ldB;
-    MDT_TRY(tc05_encode(&m.x, b.x_stage, B, b.D, b.D, kTcBM));
-    MDT_TRY(tc05_encode(&m.h1, b.h1, B, b.H, b.H, kTcBM));
-    MDT_TRY(tc05_encode(&m.z, b.z, B, b.Z, b.Z, kTcBM));
-    MDT_TRY(tc05_encode(&m.h3, b.h3, B, b.H, b.H, kTcBM));
-    MDT_TRY(tc05_encode(&m.da4, b.da4, B, b.D, b.D, kTcBM));
-    MDT_TRY(tc05_encode(&m.da3, b.da3, B, b.H, b.H, kTcBM));
-    MDT_TRY(tc05_encode(&m.dml, b.dml, B, 2 * b.Z, 2 * b.Z, kTcBM));
-    MDT_TRY(tc05_encode(&m.da4T, p->da4T, b.D, B, ldB, kTcBM));
-    MDT_TRY(tc05_encode(&m.da3T, p->da3T, b.H, B, ldB, kTcBM));
-    MDT_TRY(tc05_encode(&m.dmlT, p->dmlT, 2 * b.Z, B, ldB, kTcBM));
-    MDT_TRY(tc05_encode(&m.da1T, p->da1T, b.H, B, ldB, kTcBM));
-    MDT_TRY(tc05_encode(&m.h3T, p->h3T, b.H, B, ldB, p->bn_dw));
-    MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32));
-    MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_dw));
-    MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_dw));
-    MDT_TRY(tc05_encode(&m.h3Ta, p->h3T, b.H, B, ldB, p->bn_dwa));
-    MDT_TRY(tc05_encode(&m.h1Ta, p->h1T, b.H, B, ldB, p->bn_dwa));
-    MDT_TRY(tc05_encode(&m.xTa, p->xT, b.D, B, ldB, p->bn_dwa));
-    MDT_TRY(tc05_encode(&m.h1B, b.h1, B, b.H, b.H, p->bn_skinny));
-    MDT_TRY(tc05_encode(&m.da3B, b.da3, B, b.H, b.H, p->bn_skinny));
+    const bool bf = b.bf16;
+    auto act = [&](const float* f32, const __nv_bfloat16* b16) -> const void* { return bf ? (const void*)b16 : (const void*)f32; };
+    MDT_TRY(tc05_encode(&m.x, act(b.x_stage, p->x16), B, b.D, b.D, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.h1, act(b.h1, p->h1_16), B, b.H, b.H, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.z, act(b.z, p->z16), B, b.Z, bf ? p->ldz16 : b.Z, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.h3, act(b.h3, p->h3_16), B, b.H, b.H, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.da4, act(b.da4, p->da4_16), B, b.D, b.D, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.da3, act(b.da3, p->da3_16), B, b.H, b.H, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.dml, act(b.dml, p->dml16), B, 2 * b.Z, 2 * b.Z, kTcBM, bf));
+    // transposed activations: one buffer each, holding fp32 or bf16 as the mode says
+    MDT_TRY(tc05_encode(&m.da4T, p->da4T, b.D, B, ldB, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.da3T, p->da3T, b.H, B, ldB, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.dmlT, p->dmlT, 2 * b.Z, B, ldB, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.da1T, p->da1T, b.H, B, ldB, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.h3T, p->h3T, b.H, B, ldB, p->bn_dw, bf));
+    MDT_TRY(tc05_encode(&m.zT, p->zT, b.Z, B, ldB, 32, bf));
+    MDT_TRY(tc05_encode(&m.h1T, p->h1T, b.H, B, ldB, p->bn_dw, bf));
+    MDT_TRY(tc05_encode(&m.xT, p->xT, b.D, B, ldB, p->bn_dw, bf));
+    MDT_TRY(tc05_encode(&m.h3Ta, p->h3T, b.H, B, ldB, p->bn_dwa, bf));
+    MDT_TRY(tc05_encode(&m.h1Ta, p->h1T, b.H, B, ldB, p->bn_dwa, bf));
+    MDT_TRY(tc05_encode(&m.xTa, p->xT, b.D, B, ldB, p->bn_dwa, bf));
+    MDT_TRY(tc05_encode(&m.h1B, act(b.h1, p->h1_16), B, b.H, b.H, p->bn_skinny, bf));
+    MDT_TRY(tc05_encode(&m.da3B, act(b.da3, p->da3_16), B, b.H, b.H, p->bn_skinny, bf));
     it = p->maps.emplace(B, m).first;
   }
   *out = &it->second;
@@ -1584,7 +1746,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       PrepArgs pa{};
       int blocks = 0;
       const float* src = (p->x_src != nullptr) ? p->x_src : x;
-      tr_add(pa.tr, blocks, src, p->xT, B, D, D, p->ldB);
+      tr_add(pa.tr, blocks, src, p->xT, B, D, D, p->ldB, b.bf16, nullptr, b.bf16 ? p->x16 : nullptr, D);
       pa.tr_blocks = blocks;
       pa.x_copy = (src != b.x_stage) ? b.x_stage : nullptr;
       if (p->src_pool != nullptr || p->src_images != nullptr) {
@@ -1606,6 +1768,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     Tc05Epi e1{};
     e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
     e1.pre_b = p->preload;                       // W1: last written by the previous step's update
+    e1.bf16 = b.bf16; e1.Cb = b.bf16 ? p->h1_16 : nullptr; e1.ldcb = H;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
     if (p->simt_latent) {
@@ -1613,6 +1776,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       la.h1 = b.h1; la.H = H; la.W2x = P + b.L.off[W2X]; la.b2x = P + b.L.off[B2X]; la.W3 = P + b.L.off[W3]; la.b3 = P + b.L.off[B3];
       la.eps_in = eps_in; la.ml = b.ml; la.z = b.z; la.zT = p->zT; la.ldT = p->ldB; la.eps_out = b.eps; la.sd_out = b.sd;
       la.dml_kl = b.dml_kl; la.kl_partials = p->kl_partials; la.h3 = b.h3; la.h3T = p->h3T; la.B = B; la.Z = Z;
+      la.bf16 = b.bf16; la.h3b = b.bf16 ? p->h3_16 : nullptr;
       la.dbg = tc05_dbg_buffer();
       if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
       MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, tc05_sms(p)), s));
@@ -1623,15 +1787,21 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e2.z = b.z; e2.zT = p->zT; e2.ldzT = p->ldB; e2.eps_out = b.eps; e2.sd_out = b.sd; e2.dml_kl = b.dml_kl; e2.Z = Z;
     e2.kl_partials = p->kl_partials;
     e2.pre_a = p->preload;                       // W2x
+    e2.bf16 = b.bf16; e2.zb = b.bf16 ? p->z16 : nullptr; e2.ldzb = p->ldz16;
     MDT_TRY(tc05_launch<EPI_REPARAM>(p->bn_skinny, sp, p->mW2x, m->h1B, 2 * Z, B, H, e2, s,
                                       tc05_splits(p, e2, 2 * Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc2x_reparam_fwd");
     }
   }
+  if (decode_only && b.bf16) {                    // z came from the caller (fp32): make the bf16 operand
+    MDT_CUDA(launch_pdl(rows_to_bf16_kernel, dim3((B * Z + 255) / 256), dim3(256), 0, s, (const float*)b.z, Z, p->z16, p->ldz16, B, Z));
+    TC_NOTE(p, "z_bf16");
+  }
   if (decode_only || !p->simt_latent) {
     Tc05Epi e3{};
     e3.C = b.h3; e3.ldc = H; e3.CT = p->h3T; e3.ldct = p->ldB; e3.bias = P + b.L.off[B3]; e3.act = MDT_ACT_RELU;
     e3.pre_b = p->preload;                       // W3
+    e3.bf16 = b.bf16; e3.Cb = b.bf16 ? p->h3_16 : nullptr; e3.ldcb = H;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->z, p->mW3, B, H, Z, e3, s));
     TC_NOTE(p, "fc3_fwd");
   }
@@ -1641,12 +1811,13 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
     e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + p->bn_skinny - 1) / p->bn_skinny;
     e4.pre_b = p->preload;                       // W4
+    e4.bf16 = b.bf16; e4.da4b = b.bf16 ? p->da4_16 : nullptr;
     MDT_TRY(tc05_launch<EPI_SIGMOID_BCE>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_bce_fwd");
   } else {
     Tc05Epi e4{};
     e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.act = MDT_ACT_SIGMOID;
-    e4.pre_b = p->preload;
+    e4.pre_b = p->preload; e4.bf16 = b.bf16;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_fc4, sp, m->h3, p->mW4, B, D, H, e4, s, tc05_splits(p, e4, B, D, H, p->bn_fc4)));
     TC_NOTE(p, "fc4_fwd");
   }
@@ -1657,7 +1828,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
 inline int tc05_after_external_da4(Tc05Plan* p, cudaStream_t s, int B) {
   TrArgs a{};
   int blocks = 0;
-  tr_add(a, blocks, p->b.da4, p->da4T, B, p->b.D, p->b.D, p->ldB);
+  tr_add(a, blocks, p->b.da4, p->da4T, B, p->b.D, p->b.D, p->ldB, p->b.bf16, nullptr, p->b.bf16 ? p->da4_16 : nullptr, p->b.D);
   MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
   TC_NOTE(p, "da4_T");
   return MDT_OK;
@@ -1669,7 +1840,7 @@ inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
   LatentBwdArgs la{};
   la.da3 = b.da3; la.H = b.H; la.W3T = p->W3T; la.W2xT = p->W2xT; la.h1 = b.h1;
   la.eps = b.eps; la.sd = b.sd; la.dml_kl = b.dml_kl; la.dml = b.dml; la.dmlT = p->dmlT; la.ldT = p->ldB; la.da1T = p->da1T;
-  la.B = B; la.Z = b.Z;
+  la.B = B; la.Z = b.Z; la.bf16 = b.bf16;
   la.dbg = tc05_dbg_buffer();
   if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true), s));
@@ -1703,18 +1874,19 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   // critical path on `s`: fc4 dX -> dz/reparam -> fc2x dX
   MDT_TRY(fork_to(sw));                           // da4^T, h3^T ready
   e = Tc05Epi{};
-  e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
+  e.bf16 = b.bf16; e.C = G + b.L.off[W4]; e.ldc = H; e.a_src = p->da4T; e.lda_src = ldB; e.db = G + b.L.off[B4];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw, tc05_splits_dw(p, e, D, H, B, p->bn_dw)));
   TC_NOTE(p, "fc4_dW");
   if (b.bucket_ready) MDT_TRY(b.bucket_ready(b.note_ctx, 0, sw));   // fc4.weight + fc4.bias gradients: DDP's first bucket
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update
+  e.bf16 = b.bf16; e.Cb = b.bf16 ? p->da3_16 : nullptr; e.ldcb = H;
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
   MDT_TRY(fork_to(sw3));                          // da3^T ready (z^T since the forward)
   e = Tc05Epi{};
-  e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
+  e.bf16 = b.bf16; e.C = G + b.L.off[W3]; e.ldc = Z; e.a_src = p->da3T; e.lda_src = ldB; e.db = G + b.L.off[B3];
   MDT_TRY(tc05_launch<EPI_GRADW>(32, sp, m->da3T, m->zT, H, Z, B, e, sw3, tc05_splits_dw(p, e, H, Z, B, 32, 1)));
   TC_NOTE(p, "fc3_dW");
   if (p->simt_latent) {
@@ -1723,24 +1895,26 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
     e = Tc05Epi{};
     e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
     e.pre_a = p->preload;                        // W3^T
+    e.bf16 = b.bf16; e.dmlb = b.bf16 ? p->dml16 : nullptr;
     MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
                                           tc05_splits(p, e, Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc3_dX_reparam_bwd");
   }
   MDT_TRY(fork_to(sw2x));                         // dml^T ready (latent_bwd: da1^T too)
   e = Tc05Epi{};
-  e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
+  e.bf16 = b.bf16; e.C = G + b.L.off[W2X]; e.ldc = H; e.a_src = p->dmlT; e.lda_src = ldB; e.db = G + b.L.off[B2X];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->dmlT, m->h1T, 2 * Z, H, B, e, sw2x, tc05_splits_dw(p, e, 2 * Z, H, B, p->bn_dw, 2)));
   TC_NOTE(p, "fc2x_dW");
   if (!p->simt_latent) {
     e = Tc05Epi{};
     e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
     e.pre_b = p->preload;                        // W2x^T
+    e.bf16 = b.bf16;
     MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
     TC_NOTE(p, "fc2x_dX");
   }
   e = Tc05Epi{};
-  e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
+  e.bf16 = b.bf16; e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, s, tc05_splits_dw(p, e, H, D, B, p->bn_dw, 3)));
   TC_NOTE(p, "fc1_dW");
   if (fork) {                                     // join: the gradient buffer is complete once the side streams drain
@@ -1786,7 +1960,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   struct Dw { int seg_w, seg_b, M, N, bn, slot; const CUtensorMap *a, *bm; const float* a_src; float* pT; int ldpT; const char* label; int ns; };
   // MDT_W4_SPLIT=1: fc4's update runs apart from its weight-gradient GEMM (adam_tile_kernel, see there)
   // (measured: 60.5 vs 57.4 us/step -- the update's 325 small blocks crowd the SMs the other GEMMs need; kept as a knob)
-  const bool w4_split = getenv("MDT_W4_SPLIT") != nullptr;
+  const bool w4_split = getenv("MDT_W4_SPLIT") != nullptr && !b.bf16;
   int bn4 = w4_split ? p->bn_dw : bna;
   if (const char* v = getenv("MDT_BN_DW4")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn4 = c; }
   int bn1 = bna;
@@ -1804,10 +1978,18 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     e = Tc05Epi{};
     const int64_t ow = b.L.off[dw[i].seg_w], ob = b.L.off[dw[i].seg_b];
     e.C = G + ow; e.ldc = dw[i].N; e.a_src = dw[i].a_src; e.lda_src = ldB; e.db = G + ob;
+    e.bf16 = b.bf16;
     const bool fused = !(i == 0 && w4_split);
     if (fused) {
       e.adam_p = b.params + ow; e.adam_m = b.exp_avg + ow; e.adam_v = b.exp_avg_sq + ow;
       e.adam_pT = dw[i].pT; e.adam_ldpT = dw[i].ldpT;
+      if (b.bf16) {       // the next step's GEMMs read bf16 copies of the updated weight (and of its transpose)
+        __nv_bfloat16* const p16[4] = {p->W4_16, p->W3_16, p->W2x_16, p->W1_16};
+        __nv_bfloat16* const pT16[4] = {p->W4T_16, p->W3T_16, p->W2xT_16, nullptr};
+        const int ld16[4] = {H, p->ldz16, H, D};
+        e.adam_p16 = p16[i]; e.adam_ldp16 = ld16[i]; e.adam_pT16 = pT16[i];
+        if (i == 0) e.adam_pT = nullptr;             // W4^T has no fp32 reader in this mode
+      }
       e.adam_pb = b.params + ob; e.adam_mb = b.exp_avg + ob; e.adam_vb = b.exp_avg_sq + ob;
       e.adam_st = b.st;
     }
@@ -1847,6 +2029,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   Tc05Epi e{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update
+  e.bf16 = b.bf16; e.Cb = b.bf16 ? p->da3_16 : nullptr; e.ldcb = H;
   MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->da4, p->mW4T, B, H, D, e, s, tc05_splits(p, e, B, H, D, p->bn_h)));
   TC_NOTE(p, "fc4_dX");
   if (p->simt_latent) {
@@ -1877,6 +2060,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     e = Tc05Epi{};
     e.Z = Z; e.dml_kl = b.dml_kl; e.eps = b.eps; e.sd = b.sd; e.dml = b.dml; e.dmlT = p->dmlT; e.ld_dmlT = ldB;
     e.pre_a = p->preload;                        // W3^T
+    e.bf16 = b.bf16; e.dmlb = b.bf16 ? p->dml16 : nullptr;
     MDT_TRY(tc05_launch<EPI_REPARAM_BWD>(p->bn_skinny, sp, p->mW3T, m->da3B, Z, B, H, e, s,
                                           tc05_splits(p, e, Z, B, H, p->bn_skinny)));
     TC_NOTE(p, "fc3_dX_reparam_bwd");
@@ -1885,6 +2069,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     e = Tc05Epi{};
     e.CT = p->da1T; e.ldct = ldB; e.mask = b.h1; e.ldmask = H;
     e.pre_b = p->preload;                        // W2x^T
+    e.bf16 = b.bf16;
     MDT_TRY(tc05_launch<EPI_RELU_MASK>(p->bn_h, sp, m->dml, p->mW2xT, B, H, 2 * Z, e, s));
     TC_NOTE(p, "fc2x_dX");
     MDT_TRY(after_main(sc, sd));                  // E3: W2x^T no longer needed, da1^T ready

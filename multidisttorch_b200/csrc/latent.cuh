@@ -13,6 +13,8 @@
 // One launch replaces two GEMMs and their split-K reductions; the work is bound by the L2 -> SM traffic of the
 // weight rows (96 KB per CTA), about 1.5 us.
 #pragma once
+#include <cuda_bf16.h>
+
 #include "common.cuh"
 
 namespace mdt {
@@ -27,11 +29,12 @@ struct LatentFwdArgs {
   const float* W3; const float* b3;   // [H, Z], [H]
   const float* eps_in;                // [B, Z]
   float* ml;                          // [B, 2Z]  mu | logvar
-  float* z; float* zT; int ldT;       // [B, Z], [Z, ldT]
+  float* z; void* zT; int ldT;        // [B, Z], [Z, ldT] (z^T / h3^T: bf16 instead of fp32 when `bf16` is set)
   float* eps_out; float* sd_out;      // [B, Z] (eps_out may equal eps_in)
   float* dml_kl;                      // [B, 2Z]  dKL/d(mu | logvar)
   float* kl_partials;                 // [gridDim.x]
-  float* h3; float* h3T;              // [B, H], [H, ldT]
+  float* h3; void* h3T;               // [B, H], [H, ldT]
+  int bf16; __nv_bfloat16* h3b;       // MDT_GEMM_BF16: row-major bf16 mirror of h3 (operand of fc4), or NULL
   int B, Z, nchunks;
   long long* dbg;                     // optional phase stamps (MDT_TC05_DBG=1), same slot layout as the GEMM kernel's
   int first_live_pass;                // always 1 (a run-time value, so the compiler cannot specialise the two passes)
@@ -44,12 +47,18 @@ struct LatentBwdArgs {
   const float* W2xT;                  // [H, 2Z]  (transposed shadow of fc21|fc22.weight)
   const float* h1;                    // [B, H]   ReLU mask of fc1
   const float* eps; const float* sd; const float* dml_kl;
-  float* dml; float* dmlT; int ldT;   // [B, 2Z], [2Z, ldT]
-  float* da1T;                        // [H, ldT]
+  float* dml; void* dmlT; int ldT;    // [B, 2Z], [2Z, ldT] (dml^T / da1^T: bf16 instead of fp32 when `bf16` is set)
+  void* da1T;                         // [H, ldT]
+  int bf16;
   int B, Z, nchunks;
   long long* dbg;
   int first_live_pass, first_pass;
 };
+
+__device__ __forceinline__ void lat_st_operand(void* base, size_t idx, float v, bool b16) {
+  if (b16) reinterpret_cast<__nv_bfloat16*>(base)[idx] = __float2bfloat16_rn(v);
+  else reinterpret_cast<float*>(base)[idx] = v;
+}
 
 __device__ __forceinline__ void lat_stamp(long long* dbg, int i) {
   if (dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) dbg[i] = clock64();
@@ -266,7 +275,7 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
         a.ml[m * 2 * Z + j] = mu;
         a.ml[m * 2 * Z + Z + j] = lv;
         a.z[m * Z + j] = zv;
-        a.zT[(size_t)j * a.ldT + m] = zv;
+        lat_st_operand(a.zT, (size_t)j * a.ldT + m, zv, a.bf16 != 0);
         if (a.eps_out != a.eps_in) a.eps_out[m * Z + j] = e;
         a.sd_out[m * Z + j] = sd;
         a.dml_kl[m * 2 * Z + j] = mu;
@@ -294,7 +303,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
             if (s < ns) {
               const float v = fmaxf(acc[s], 0.f);
               a.h3[(size_t)(m0 + s) * H + j] = v;
-              a.h3T[(size_t)j * a.ldT + m0 + s] = v;
+              lat_st_operand(a.h3T, (size_t)j * a.ldT + m0 + s, v, a.bf16 != 0);
+              if (a.h3b != nullptr) a.h3b[(size_t)(m0 + s) * H + j] = __float2bfloat16_rn(v);
             }
           }
         }
@@ -380,8 +390,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
       if (ok) {
         a.dml[m * 2 * Z + j] = dmu;
         a.dml[m * 2 * Z + Z + j] = dlv;
-        a.dmlT[(size_t)j * a.ldT + m] = dmu;
-        a.dmlT[(size_t)(Z + j) * a.ldT + m] = dlv;
+        lat_st_operand(a.dmlT, (size_t)j * a.ldT + m, dmu, a.bf16 != 0);
+        lat_st_operand(a.dmlT, (size_t)(Z + j) * a.ldT + m, dlv, a.bf16 != 0);
       }
       sDML[s * kLatMaxOut + j] = dmu;
       sDML[s * kLatMaxOut + Z + j] = dlv;
@@ -405,7 +415,7 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
           lat_row_dot<SC, 2 * ZQ>(f2[r], 2 * Z, sDML, kLatMaxOut, acc);
 #pragma unroll
           for (int s = 0; s < SC; ++s)
-            if (s < ns) a.da1T[(size_t)h * a.ldT + m0 + s] = mk[s] > 0.f ? acc[s] : 0.f;
+            if (s < ns) lat_st_operand(a.da1T, (size_t)h * a.ldT + m0 + s, mk[s] > 0.f ? acc[s] : 0.f, a.bf16 != 0);
         }
       }
     }

@@ -607,7 +607,7 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   MDT_CHECK(cfg->in_dim % 4 == 0 && cfg->hidden % 4 == 0 && cfg->latent % 4 == 0,
             "in_dim, hidden and latent must be multiples of 4 (16-byte rows)");
   MDT_CHECK(group_size >= 1 && group_rank >= 0 && group_rank < group_size, "bad group size/rank");
-  MDT_CHECK(cfg->gemm_mode >= MDT_GEMM_FP32 && cfg->gemm_mode <= MDT_GEMM_TF32X3, "unknown gemm_mode %d", cfg->gemm_mode);
+  MDT_CHECK(cfg->gemm_mode >= MDT_GEMM_FP32 && cfg->gemm_mode <= MDT_GEMM_BF16, "unknown gemm_mode %d", cfg->gemm_mode);
   MDT_CHECK(cfg->exchange >= MDT_EXCHANGE_AUTO && cfg->exchange <= MDT_EXCHANGE_P2P_TWO_SHOT, "unknown exchange %d", cfg->exchange);
   DeviceInfo* di = nullptr;
   MDT_TRY(device_info(&di));
@@ -812,6 +812,7 @@ int mdt_engine_bind_buffers(mdt_engine* e, float* params, float* grads, float* e
     b.loss_dev = e->loss_dev; b.note_ctx = e; b.note = note_cb; b.serial = &e->prof_on;
     b.bucket_ready = (e->gsize > 1) ? bucket_ready_cb : nullptr;
     b.split3 = (e->cfg.gemm_mode == MDT_GEMM_TF32X3);
+    b.bf16 = (e->cfg.gemm_mode == MDT_GEMM_BF16);
     MDT_TRY(tc05_create(&b, e->stream, &e->tc));
     e->tc->sm_share = e->sm_share_pending;
   }
@@ -1418,6 +1419,8 @@ int mdt_linear(const float* x, const float* w, const float* b, int M, int N, int
     MDT_CUDA((launch_gemm_simt<true, true>(x, w, M, N, K, K, K, EpiBiasAct{y, N, b, act}, s)));
     return MDT_OK;
   }
+  if (gemm_mode == MDT_GEMM_BF16)
+    return set_error(MDT_ERR_UNSUPPORTED, "mdt_linear takes fp32 operands: MDT_GEMM_BF16 exists inside the engine only (bf16 operand mirrors)");
   MDT_CHECK(gemm_mode == MDT_GEMM_TF32 || gemm_mode == MDT_GEMM_TF32X3, "unknown gemm_mode %d", gemm_mode);
   DeviceInfo* di = nullptr;
   MDT_TRY(device_info(&di));

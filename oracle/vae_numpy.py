@@ -258,11 +258,29 @@ def adam_update(p, g, m, v, t, lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
     p -= F32(step_size) * (m / denom)
 
 
+def sgd_update(p, g, buf, t, lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False):
+    """In-place torch.optim.SGD step t (1-based) on float32 arrays (torch/optim/sgd.py _single_tensor_sgd):
+    g += wd*p; buf = g on the first step, else momentum*buf + (1-dampening)*g; g = g + momentum*buf (nesterov)
+    or buf; p -= lr*g.  BASELINE north_star (c) names SGD next to Adam; the reference itself uses Adam only."""
+    g = g.astype(F32)
+    if weight_decay != 0:
+        g = g + F32(weight_decay) * p
+    if momentum != 0:
+        if t == 1:
+            buf[...] = g
+        else:
+            buf *= F32(momentum)
+            buf += F32(1.0 - dampening) * g
+        g = g + F32(momentum) * buf if nesterov else buf
+    p -= F32(lr) * g
+
+
 class Trainer:
     """N-step driver mirroring ref:vae-hpo.py:69-74 for one rank (or, with
     several batches per step, one DDP group)."""
 
-    def __init__(self, params: dict, dims: Dims = Dims(), lr=1e-3, b1=0.9, b2=0.999, eps=1e-8):
+    def __init__(self, params: dict, dims: Dims = Dims(), lr=1e-3, b1=0.9, b2=0.999, eps=1e-8, sgd=None):
+        self.sgd = sgd          # dict(lr=, momentum=, dampening=, weight_decay=, nesterov=) -> SGD instead of Adam
         self.dims = dims
         self.p = {k: np.array(v, dtype=F32, copy=True) for k, v in params.items()}
         self.m = {k: np.zeros_like(v) for k, v in self.p.items()}
@@ -281,7 +299,10 @@ class Trainer:
         g = grads[0] if len(grads) == 1 else ddp_average(grads)
         self.t += 1
         for k in self.p:
-            adam_update(self.p[k], g[k], self.m[k], self.v[k], self.t, lr=self.lr, b1=self.b1, b2=self.b2, eps=self.eps)
+            if self.sgd is not None:
+                sgd_update(self.p[k], g[k], self.m[k], self.t, **self.sgd)
+            else:
+                adam_update(self.p[k], g[k], self.m[k], self.v[k], self.t, lr=self.lr, b1=self.b1, b2=self.b2, eps=self.eps)
         return losses, g
 
 

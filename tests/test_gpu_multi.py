@@ -33,18 +33,37 @@ def run_world(world, tag, mode, extra_env=None):
     assert [p.returncode for p in procs] == [0] * world, "\n".join(l[-1500:] for l in logs)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
+def need(n):
+    return pytest.mark.skipif(torch.cuda.device_count() < n, reason=f"needs {n} GPUs")
+
+
+@need(2)
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3", "bf16"])
 def test_one_group_of_two_gpus_matches_reference_ddp(mode):
     run_world(2, "ddp_1x2_b32", mode)
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
-def test_one_group_of_two_gpus_nccl_path_matches_reference_ddp():
-    run_world(2, "ddp_1x2_b32", "tf32x3", {"MDT_P2P_ALLREDUCE": "0"})
+@need(2)
+@pytest.mark.parametrize("xch", ["nccl", "p2p", "p2p_two_shot"])
+def test_one_group_of_two_gpus_every_exchange_matches_reference_ddp(xch):
+    run_world(2, "ddp_1x2_b32", "tf32x3", {"MDT_EXCHANGE": xch})
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 4, reason="needs 4 GPUs")
+@need(4)
 @pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
 def test_two_groups_of_two_gpus_match_reference_ddp(mode):
     run_world(4, "ddp_2x2_b16", mode)
+
+
+@need(4)
+@pytest.mark.parametrize("xch", ["nccl", "p2p", "p2p_two_shot"])
+def test_one_group_of_four_gpus_matches_reference_ddp(xch):
+    run_world(4, "ddp_1x4_b32", "tf32x3", {"MDT_EXCHANGE": xch})
+
+
+@need(8)
+@pytest.mark.parametrize("tag", ["ddp_1x8_b16", "ddp_2x4_b128"])
+@pytest.mark.parametrize("xch", ["nccl", "p2p", "p2p_two_shot"])
+def test_eight_gpu_layouts_match_reference_ddp(tag, xch):
+    """1x8 (BASELINE config 5's layout) and 2x4 at 128 / rank (config 4's layout and batch)."""
+    run_world(8, tag, "tf32x3", {"MDT_EXCHANGE": xch})

@@ -22,8 +22,13 @@ TOL = {
     # steps 1.1e-3 (Adam's normalisation amplifies small gradient differences)
     "tf32x3": dict(loss=1e-5, act=2e-5, grad=1e-4, param=2e-4, mom=2e-3),
     "tf32":   dict(loss=1e-3, act=5e-3, grad=3e-2, param=1e-1, mom=1e-1),
+    # bf16 operands (8-bit mantissa), fp32 accumulate: loss-level and single-step-gradient-level agreement only; Adam's
+    # normalisation turns the gradient noise into O(lr) parameter differences, so the long-run parameter check is
+    # deliberately loose (SURVEY section 7 "Precision vs parity")
+    "bf16":   dict(loss=2e-3, act=2e-2, grad=1e-1, param=3e-1, mom=3e-1),
 }
-MODES = [m for m in os.environ.get("MDT_TEST_MODES", "fp32,tf32x3,tf32").split(",") if m]
+MODES = [m for m in os.environ.get("MDT_TEST_MODES", "fp32,tf32x3,tf32,bf16").split(",") if m]
+LINEAR_MODES = [m for m in MODES if m != "bf16"]       # mdt_linear takes fp32 operands; bf16 lives inside the engine
 
 
 def dev(a):
@@ -131,7 +136,7 @@ def test_reparam_philox_is_torch_cuda_randn(E, B, offset):
         np.testing.assert_allclose(O.cuda_randn(seed, offset, B * 20), want.cpu().numpy().ravel(), rtol=0, atol=2e-5)
 
 
-@pytest.mark.parametrize("mode", MODES)
+@pytest.mark.parametrize("mode", LINEAR_MODES)
 @pytest.mark.parametrize("M,N,K,act", [(128, 400, 784, "relu"), (128, 40, 400, "none"), (128, 400, 20, "relu"),
                                        (128, 784, 400, "sigmoid"), (48, 400, 784, "relu"), (1, 784, 400, "none"),
                                        (300, 400, 784, "none")])
@@ -199,13 +204,15 @@ def test_fused_bce_epilogue_on_reference_corners(E, mode):
     loss = float(eng.train_step(dev(x), dev(eps)).item())
     assert abs(loss - g["losses"][0]) <= tol["loss"] * abs(g["losses"][0]), (loss, g["losses"][0])
     recon = eng.workspace("recon", B).cpu().numpy()[:3, :n]
-    # recon at the corners: exact zeros and ones where the reference has them, 4 ulp elsewhere (denormals included)
+    # recon at the corners: exact zeros and ones where the reference has them; elsewhere (denormals included) within the
+    # SFU forms' error -- ex2.approx and the range reduction by log2(e) are ~2 ulp each: measured 2.4e-6 relative
     want = g["recon_edge"]
     assert np.array_equal(recon == 0, want == 0) and np.array_equal(recon == 1, want == 1), (recon, want)
-    np.testing.assert_allclose(recon, want, rtol=1e-6, atol=1e-44)
+    np.testing.assert_allclose(recon, want, rtol=6e-6, atol=1e-44)
     gr = eng.segments_to_numpy(eng.grads)
     # d loss / d fc4.bias at the pinned logits = sum over the batch of d(logits): exercises fast_dlogit's clamp branch
-    np.testing.assert_allclose(gr["b4"][:n], g["grad0.b4.edge"], rtol=2e-5, atol=1e-30)
+    # (bf16 mode sums the bias gradient from the bf16 operand copy of d(logits): 2^-9 per element)
+    np.testing.assert_allclose(gr["b4"][:n], g["grad0.b4.edge"], rtol=2e-5 if mode != "bf16" else 5e-3, atol=1e-30)
     for k in O.SEGMENTS:
         check_fp(g, "grad0", k, gr[k], tol["grad"], f"edge/{mode}")
     pN = eng.segments_to_numpy()
@@ -425,7 +432,8 @@ def test_batches_beyond_one_row_tile_vs_oracle(E, mode, B):
         # worth.  Rows of units whose mask disagrees are left out; a flipped fc3 unit also perturbs everything upstream.
         flip1 = np.flatnonzero(((eng.workspace("h1", B).cpu().numpy() > 0) != (act["h1"] > 0)).any(0))
         flip3 = np.flatnonzero(((eng.workspace("h3", B).cpu().numpy() > 0) != (act["h3"] > 0)).any(0))
-        max_flips = 3 if mode != "tf32" else p0["W1"].shape[0] // 4     # single-pass tf32 moves pre-activations by ~1e-3
+        coarse = mode in ("tf32", "bf16")                               # 10- / 8-bit operand mantissas move pre-activations by ~1e-3
+        max_flips = 3 if not coarse else p0["W1"].shape[0] // 4
         assert len(flip1) <= max_flips and len(flip3) <= max_flips, (flip1, flip3)
         flipped = flipped or len(flip1) > 0 or len(flip3) > 0
         for names, fl, n in ((("W1", "b1"), flip1, p0["W1"].shape[0]), (("W3", "b3"), flip3, p0["W3"].shape[0])):
@@ -433,7 +441,7 @@ def test_batches_beyond_one_row_tile_vs_oracle(E, mode, B):
                 keep[k] = np.setdiff1d(keep.get(k, np.arange(n)), fl)
         if t == 0:
             got = eng.segments_to_numpy(eng.grads)
-            loose = (50.0 if len(flip3) else 1.0) if mode != "tf32" else 3.0
+            loose = (50.0 if len(flip3) else 1.0) if not coarse else 3.0
             for k in O.SEGMENTS:
                 a, b = (got[k][keep[k]], g[k][keep[k]]) if k in keep else (got[k], g[k])
                 lim = tol["grad"] * (loose if k in ("W1", "b1", "W2x", "b2x", "W3", "b3") else 1.0)
@@ -444,7 +452,7 @@ def test_batches_beyond_one_row_tile_vs_oracle(E, mode, B):
     pN = eng.segments_to_numpy()
     for k in O.SEGMENTS:
         a, b = (pN[k][keep[k]], tr.p[k][keep[k]]) if k in keep else (pN[k], tr.p[k])
-        lim = tol["param"] * ((50.0 if flipped else 1.0) if mode != "tf32" else 3.0)
+        lim = tol["param"] * ((50.0 if flipped else 1.0) if not coarse else 3.0)
         assert rel_l2(a, b) < lim, (k, rel_l2(a, b))
     eng.close()
 

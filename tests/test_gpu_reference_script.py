@@ -1,8 +1,8 @@
 """The reference's own vae-hpo.py, UNCHANGED, on a GPU: once on plain torch-CUDA (+ NCCL DDP) and once with this
 repo's drop-in active (`from utils import *` resolves to the repo's utils.py, which installs the engine behind
-DistributedDataParallel / optim.Adam).  The script seeds nothing, so both runs start from torch's default generator
-state; the drop-in draws eps from the same Philox stream torch.randn_like would have used -- the printed losses of
-the two runs must agree.
+DistributedDataParallel / optim.Adam).  Both runs start from the same generator seed (set by the runner, outside
+the script); the drop-in draws eps from the same Philox stream torch.randn_like would have used -- the printed
+losses of the two runs must agree.
 
 The script is read from oracle/_ref/ (staged by oracle/vendor_ref.py from /root/reference; that directory travels to
 the GPU box) and executed with runpy, so nothing in it is edited.  MNIST cannot be downloaded here: synthetic idx
@@ -22,7 +22,9 @@ from tests.test_reference_scripts import _write_idx
 pytestmark = pytest.mark.gpu
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 SCRIPT = os.path.join(ROOT, "oracle", "_ref", "vae-hpo.py")
-RUNNER = ("import runpy, sys; sys.argv = sys.argv[1:]; "
+# The script seeds nothing and torch seeds its default generators from the OS, so two runs of it never agree; the
+# runner seeds torch (CPU and CUDA generators) BEFORE handing control to the untouched script.
+RUNNER = ("import runpy, sys, torch; torch.manual_seed(1234); sys.argv = sys.argv[1:]; "
           "runpy.run_path(sys.argv[0], run_name='__main__')")
 
 

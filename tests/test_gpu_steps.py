@@ -1,0 +1,99 @@
+"""mdt_train_steps (the inner loop of train(), ref:vae-hpo.py:67-74, as graphs of several steps over a device-resident
+batch source), the uint8 dataset source (gather + /255 inside the step, ref:vae-hpo.py:135-150) and the SGD update."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import vae_numpy as O
+from tests.golden_cases import PARAM_SEED, batch_seed, rel_l2
+
+pytestmark = pytest.mark.gpu
+
+
+def pair(E, mode, B, **kw):
+    engs = []
+    for _ in range(2):
+        e = E.VAEEngine(max_batch=B, gemm_mode=mode, **kw)
+        e.load_segments(O.init_params(PARAM_SEED))
+        e.set_rng(31, 0)
+        engs.append(e)
+    return engs
+
+
+@pytest.fixture(scope="module")
+def E():
+    from multidisttorch_b200 import engine
+    return engine
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3", "tf32", "bf16"])
+@pytest.mark.parametrize("B", [128, 48])
+def test_train_steps_over_a_pool_equal_single_steps_bit_for_bit(E, mode, B):
+    a, b = pair(E, mode, B)
+    pool = torch.rand(7, B, 784, generator=torch.Generator().manual_seed(B)).cuda()
+    n = 27                                              # three 8-step graphs + 3 single steps, wrapping the pool
+    losses = torch.zeros(n, device="cuda")
+    a.train_steps(pool, 5, n, losses)
+    want = [float(b.train_step(pool[(5 + i) % 7], None).item()) for i in range(n)]
+    a.synchronize()
+    assert losses.cpu().tolist() == want
+    assert torch.equal(a.params, b.params) and torch.equal(a.exp_avg_sq, b.exp_avg_sq)
+    assert a.state() == b.state()
+    # a second call that continues where the first stopped, and one that jumps
+    a.train_steps(pool, (5 + n) % 7, 9, None)
+    a.train_steps(pool, 2, 2, None)
+    for i in list(range(n, n + 9)):
+        b.train_step(pool[(5 + i) % 7], None)
+    for i in (2, 3):
+        b.train_step(pool[i], None)
+    a.synchronize(); b.synchronize()
+    assert torch.equal(a.params, b.params)
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+def test_train_steps_from_uint8_images_equal_the_torch_pipeline(E, mode):
+    """The step's first kernel gathers rows of a uint8 image table through the sampler's index order and divides by
+    255 (what datasets.MNIST + ToTensor + DistributedSampler + DataLoader hand to ref:vae-hpo.py:67-68)."""
+    B, n_img = 64, 1000
+    rs = np.random.RandomState(5)
+    images = torch.from_numpy(rs.randint(0, 256, (n_img, 784), dtype=np.uint8)).cuda()
+    order = torch.from_numpy(rs.permutation(n_img)[: 10 * B].astype(np.int64)).cuda()
+    a, b = pair(E, mode, B)
+    losses = torch.zeros(10, device="cuda")
+    a.train_steps_u8(images, order, B, 0, 10, losses)
+    want = []
+    for i in range(10):
+        x = images[order[i * B:(i + 1) * B]].to(torch.float32) / 255        # ToTensor(): uint8 -> float32, then / 255
+        want.append(float(b.train_step(x.contiguous(), None).item()))
+    a.synchronize()
+    assert losses.cpu().tolist() == want and torch.equal(a.params, b.params)
+    a.close(); b.close()
+
+
+@pytest.mark.parametrize("mode", ["fp32", "tf32x3"])
+@pytest.mark.parametrize("kw", [dict(lr=0.01), dict(lr=0.005, momentum=0.9), dict(lr=0.005, momentum=0.9, nesterov=True, weight_decay=1e-3),
+                                dict(lr=0.005, momentum=0.8, dampening=0.2)], ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()))
+def test_sgd_steps_match_the_oracle(E, mode, kw):
+    """north_star (c): SGD in place of Adam.  The oracle's SGD is pinned against torch.optim.SGD in
+    tests/test_hpo_surface.py; here the engine against the oracle over 4 steps (momentum buffer included)."""
+    B = 48
+    p0 = O.init_params(PARAM_SEED)
+    eng = E.VAEEngine(max_batch=B, gemm_mode=mode)
+    eng.load_segments(p0)
+    eng.set_sgd(**kw)
+    full = dict(dict(momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False), **kw)
+    tr = O.Trainer(p0, sgd=full)
+    for t in range(4):
+        x, eps = O.make_batch(batch_seed(t), B)
+        loss = float(eng.train_step(torch.from_numpy(x).cuda(), torch.from_numpy(eps).cuda()).item())
+        lo, _ = tr.step([(x, eps)])
+        assert abs(loss - lo[0]) <= 1e-5 * abs(lo[0]), (t, loss, lo[0])
+    p = eng.segments_to_numpy()
+    m = eng.segments_to_numpy(eng.exp_avg)
+    for k in O.SEGMENTS:
+        assert rel_l2(p[k], tr.p[k]) < 1e-5, (k, rel_l2(p[k], tr.p[k]))
+        if full["momentum"]:
+            assert rel_l2(m[k], tr.m[k]) < 1e-4, (k, rel_l2(m[k], tr.m[k]))
+    assert eng.state()[0] == 4
+    eng.close()

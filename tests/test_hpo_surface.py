@@ -85,3 +85,24 @@ def test_engine_with_per_trial_hyperparameters_vs_oracle(mode):
             assert rel_l2(got[k], tr.p[k]) < tol, (gid, k, rel_l2(got[k], tr.p[k]))
         assert eng.state()[0] == 6
         eng.close()
+
+
+@pytest.mark.parametrize("kw", [dict(lr=0.05), dict(lr=0.01, momentum=0.9), dict(lr=0.01, momentum=0.9, dampening=0.1),
+                                dict(lr=0.02, momentum=0.8, nesterov=True), dict(lr=0.01, momentum=0.9, weight_decay=1e-2)],
+                         ids=lambda k: "-".join(f"{a}{b}" for a, b in k.items()))
+def test_oracle_sgd_is_torch_sgd(kw):
+    """north_star (c) "fused per-trial Adam/SGD update": the oracle's SGD restatement pinned against torch.optim.SGD."""
+    import numpy as np
+    import torch
+    from oracle import vae_numpy as O
+    rs = np.random.RandomState(3)
+    p0 = rs.standard_normal(1000).astype(np.float32)
+    tp = torch.nn.Parameter(torch.from_numpy(p0.copy()))
+    opt = torch.optim.SGD([tp], **kw)
+    p, buf = p0.copy(), np.zeros_like(p0)
+    for t in range(1, 6):
+        g = (rs.standard_normal(1000) * 10.0 ** rs.uniform(-4, 1, 1000)).astype(np.float32)
+        tp.grad = torch.from_numpy(g.copy())
+        opt.step()
+        O.sgd_update(p, g, buf, t, **kw)
+        np.testing.assert_allclose(p, tp.detach().numpy(), rtol=2e-6, atol=1e-7)
