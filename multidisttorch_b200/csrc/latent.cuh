@@ -16,6 +16,7 @@
 #include <cuda_bf16.h>
 
 #include "common.cuh"
+#include "elementwise.cuh"
 
 namespace mdt {
 
@@ -27,7 +28,10 @@ struct LatentFwdArgs {
   const float* h1; int H;             // [B, H] row-major
   const float* W2x; const float* b2x; // [2Z, H], [2Z]
   const float* W3; const float* b3;   // [H, Z], [H]
-  const float* eps_in;                // [B, Z]
+  const float* eps_in;                // [B, Z], or NULL: eps is drawn here from Philox exactly as torch.randn_like would on
+                                      // CUDA (ref:vae-hpo.py:35), from the device-resident (seed, offset); the kernel's last
+                                      // block advances the offset
+  StepState* st; long long philox_S; unsigned long long philox_inc;
   float* ml;                          // [B, 2Z]  mu | logvar
   float* z; void* zT; int ldT;        // [B, Z], [Z, ldT] (z^T / h3^T: bf16 instead of fp32 when `bf16` is set)
   float* eps_out; float* sd_out;      // [B, Z] (eps_out may equal eps_in)
@@ -233,9 +237,16 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
   float b3r[1], e_pre = 0.f;
 #pragma unroll
   for (int r = 0; r < 1; ++r) b3r[r] = (threadIdx.x + r * kLatThreads < H) ? lat_ldg(a.b3 + threadIdx.x + r * kLatThreads) : 0.f;
+  // (seed, offset) were last written by the previous step's latent_fwd or by the host: safe before the wait, and the
+  // Philox rounds of the first chunk's eps overlap the predecessor kernel
+  const bool gen_eps = a.eps_in == nullptr;
+  unsigned long long ph_seed = 0, ph_off = 0;
+  if (gen_eps) { ph_seed = a.st->philox_seed; ph_off = a.st->philox_offset; }
   {
     const int m0 = blockIdx.x * SC, ns = min(SC, a.B - m0);
-    if ((int)threadIdx.x < ns * Z) e_pre = lat_ldg(a.eps_in + (size_t)m0 * Z + threadIdx.x);
+    if ((int)threadIdx.x < ns * Z)
+      e_pre = gen_eps ? torch_cuda_randn_elem(ph_seed, ph_off, (long long)m0 * Z + threadIdx.x, a.philox_S)
+                      : lat_ldg(a.eps_in + (size_t)m0 * Z + threadIdx.x);
   }
   // (The pass loop below can start with a dry run of the same code before the dependency wait -- MDT_LATENT_DRY=1 --
   // to pull the instructions into the caches early.  Measured: no gain, the kernel is not fetch-bound; left as a knob.)
@@ -267,7 +278,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
       const bool ok = s < ns;
       const size_t m = ok ? (size_t)(m0 + s) : 0;
       const float mu = sML[s * kLatMaxOut + j], lv = sML[s * kLatMaxOut + Z + j];
-      const float e = (first || !ok) ? e_pre : __ldg(a.eps_in + m * Z + j);   // SC * Z <= 128 < blockDim.x: one element per thread
+      const float e = (first || !ok) ? e_pre        // SC * Z <= 128 < blockDim.x: one element per thread
+                      : (gen_eps ? torch_cuda_randn_elem(ph_seed, ph_off, (long long)m * Z + j, a.philox_S) : __ldg(a.eps_in + m * Z + j));
       const float sd = __expf(0.5f * lv);
       const float ev = __expf(lv);
       const float zv = mu + e * sd;
@@ -318,6 +330,14 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
   lat_stamp(a.dbg, 5);
   kl = block_sum(kl, red);
   if (threadIdx.x == 0) a.kl_partials[blockIdx.x] = kl;
+  if (gen_eps && threadIdx.x == 0) {                  // every block has read the offset by the time the last ticket is taken
+    __threadfence();
+    if (atomicAdd(&a.st->ticket_reparam, 1u) == gridDim.x - 1) {
+      a.st->philox_offset = ph_off + a.philox_inc;
+      a.st->ticket_reparam = 0;
+      __threadfence();
+    }
+  }
   lat_stamp(a.dbg, 6);
   lat_stamp_end(a.dbg);
 }

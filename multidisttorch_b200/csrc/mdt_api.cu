@@ -1222,7 +1222,7 @@ int mdt_engine_profile_step(mdt_engine* e, const float* x, int batch, int iters,
   for (int it = 0; it < iters && rc == MDT_OK; ++it) {
     e->prof_marks.clear();
     // keep the GPU busy while the host enqueues the whole step, so intervals are device time, not launch time
-    spin_kernel<<<1, 1, 0, e->stream>>>(300000);
+    spin_kernel<<<1, 1, 0, e->stream>>>(1000000);
     rc = note_launch(e, "_start");
     if (rc == MDT_OK) {   // calibration: an empty kernel, so the caller can subtract the launch + event overhead
       null_kernel<<<1, 32, 0, e->stream>>>();

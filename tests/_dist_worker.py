@@ -40,12 +40,12 @@ def main():
             print0("hello", 3, process_group=grp)
         res["print0"] = pb.getvalue()
     if mode == "allreduce" and mine:
-        # per-group gradient averaging exactly as the engine's torch.distributed leg does it
-        from multidisttorch_b200.gradsync import average_flat_
+        # per-group gradient averaging with DDP's semantics on a flat buffer: g <- sum_r (g_r / n) (ref:vae-hpo.py:130)
         grp = mine[0]
         n = dist.get_world_size(grp)
         flat = torch.arange(1000, dtype=torch.float32) * (rank + 1)
-        average_flat_(flat, grp)
+        flat.div_(n)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=grp)
         res["avg_head"] = flat[:4].tolist()
         res["group_ranks"] = dist.get_process_group_ranks(grp)
     if world_has_all_members(size, ngroups):
