@@ -1269,6 +1269,7 @@ struct PrepArgs {
   const uint8_t* images;
   const long long* indices;
   long long n_batches, n_images;
+  int cursor_add;      // 1: this launch fetches the NEXT step's batch while the current step runs (see Tc05Plan::pipelined)
 };
 
 __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
@@ -1283,7 +1284,7 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
     const bool sourced = a.pool != nullptr || a.images != nullptr;
     long long bidx = 0;
     if (sourced) {
-      bidx = a.st->x_cursor % a.n_batches;
+      bidx = (a.st->x_cursor + a.cursor_add) % a.n_batches;
       if (a.pool != nullptr) job.in = a.pool + (size_t)bidx * job.R * job.C;
     }
 #pragma unroll
@@ -1493,6 +1494,7 @@ struct Tc05ActMaps {   // tensor maps whose extents depend on the batch size B
   CUtensorMap h3T, zT, h1T, xT;                        // B operands [*, B]
   CUtensorMap h1B, da3B;                               // B operands [B, *] of the transposed (skinny-output) GEMMs
   CUtensorMap h3Ta, h1Ta, xTa;                         // B operands [*, B] of the Adam-fused weight-gradient GEMMs (bn_dwa rows)
+  CUtensorMap x_1, xT_1, xTa_1;                        // the same three x maps over the second input set (Tc05Plan::xpar == 1)
 };
 
 struct Tc05Plan {
@@ -1530,6 +1532,22 @@ struct Tc05Plan {
   // sm_count / sm_share SMs, so that the kernels of different trials run side by side instead of queueing for SMs
   // (measured, 8 trials: 3.5 -> 5.1 M samples/s).
   int sm_share = 1;
+  // Two-set pipelining of the step (CUDA-core latent path).  The step's prologue (x -> stage copy, x^T, bf16 copy) does
+  // not depend on the previous step, and fc3's update only conflicts with latent_bwd through W3^T.  So both exist twice:
+  //  * input sets: while step j computes on set `xpar`, a side stream fills the other set with batch j+1 (mdt_train_steps
+  //    knows it: the batch index lives on the device), so the next step starts with its first GEMM, not with a prologue
+  //    kernel behind four full dependencies;
+  //  * W3^T sets: latent_bwd reads W3T_set[w3par] while fc3's weight-gradient + Adam kernel, started as early as fc4's,
+  //    writes the updated transpose into the other one -- it leaves the step's tail.
+  float* x_stage_set[2] = {nullptr, nullptr};
+  float* xT_set[2] = {nullptr, nullptr};
+  __nv_bfloat16* x16_set[2] = {nullptr, nullptr};
+  float* W3T_set[2] = {nullptr, nullptr};
+  int xpar = 0, w3par = 0;
+  bool pipelined = false;        // set by mdt_train_steps around its enqueues: no prologue in the step, prefetch the next batch
+  bool prefetch_pending = false; // a prefetch was forked in this step and has not been joined yet
+  cudaStream_t side_pf = nullptr;
+  cudaEvent_t ev_pf_fork = nullptr, ev_pf_join = nullptr;
   int preload = 1;     // issue weight-operand TMA loads before the dependency wait (MDT_NO_PRELOAD=1 turns it off)
   PrepArgs last_prep{};
   bool prep_launched = false;
@@ -1549,12 +1567,12 @@ inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
     // bf16 mode: W4^T is only a GEMM operand (bf16 shadow); W3^T / W2x^T are also read in fp32 by the CUDA-core latent
     // kernels; every weight gets a row-major bf16 copy
     tr_add(a, blocks, P + b.L.off[W4], nullptr, b.D, b.H, b.H, b.D, false, p->W4T_16, p->W4_16, b.H);
-    tr_add(a, blocks, P + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H, false, p->W3T_16, p->W3_16, p->ldz16);
+    tr_add(a, blocks, P + b.L.off[W3], p->W3T_set[p->w3par], b.H, b.Z, b.Z, b.H, false, p->W3T_16, p->W3_16, p->ldz16);
     tr_add(a, blocks, P + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z, false, p->W2xT_16, p->W2x_16, b.H);
     tr_add(a, blocks, P + b.L.off[W1], nullptr, b.H, b.D, b.D, b.H, false, nullptr, p->W1_16, b.D);
   } else {
     tr_add(a, blocks, P + b.L.off[W4], p->W4T, b.D, b.H, b.H, b.D);
-    tr_add(a, blocks, P + b.L.off[W3], p->W3T, b.H, b.Z, b.Z, b.H);
+    tr_add(a, blocks, P + b.L.off[W3], p->W3T_set[p->w3par], b.H, b.Z, b.Z, b.H);
     tr_add(a, blocks, P + b.L.off[W2X], p->W2xT, 2 * b.Z, b.H, b.H, 2 * b.Z);
   }
   MDT_CUDA(launch_pdl(transpose_kernel, dim3(blocks), dim3(256), 0, s, a));
@@ -1589,6 +1607,9 @@ inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* n
 inline void tc05_destroy(Tc05Plan* p) {
   if (!p) return;
   if (p->side) cudaStreamDestroy(p->side);
+  if (p->side_pf) cudaStreamDestroy(p->side_pf);
+  if (p->ev_pf_fork) cudaEventDestroy(p->ev_pf_fork);
+  if (p->ev_pf_join) cudaEventDestroy(p->ev_pf_join);
   for (cudaStream_t st : {p->side2, p->side3, p->side4}) if (st) cudaStreamDestroy(st);
   for (cudaEvent_t ev : {p->ev_join2, p->ev_join3, p->ev_join4}) if (ev) cudaEventDestroy(ev);
   for (auto& ev : p->ev_fork) if (ev) cudaEventDestroy(ev);
@@ -1626,13 +1647,14 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
                   {&p->da3T, H * ldB}, {&p->dmlT, 2 * Z * ldB}, {&p->da1T, H * ldB}, {&p->W4T, H * D}, {&p->W3T, Z * H},
-                  {&p->W2xT, H * 2 * Z}, {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, 2 * Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 8192}};
+                  {&p->W2xT, H * 2 * Z}, {&p->x_stage_set[1], (size_t)b.Bmax * D}, {&p->xT_set[1], D * ldB}, {&p->W3T_set[1], Z * H},
+                  {&p->kl_partials, 1024}, {&p->bce_partials, 65536}, {&p->ws, Tc05Plan::kWsFloats}, {&p->ws_dw, 2 * Tc05Plan::kWsFloats}, {reinterpret_cast<float**>(&p->ws_counters), 8192}};
   // bf16 operand mirrors: sizes in bf16 elements
   struct Item16 { __nv_bfloat16** ptr; size_t n; };
   const size_t Bm = b.Bmax, lz = p->ldz16;
   Item16 items16[] = {{&p->x16, Bm * D}, {&p->h1_16, Bm * H}, {&p->z16, Bm * lz}, {&p->h3_16, Bm * H}, {&p->da4_16, Bm * D},
                       {&p->da3_16, Bm * H}, {&p->dml16, Bm * 2 * Z}, {&p->W1_16, H * D}, {&p->W2x_16, 2 * Z * H}, {&p->W3_16, H * lz},
-                      {&p->W4_16, D * H}, {&p->W4T_16, H * D}, {&p->W3T_16, Z * H}, {&p->W2xT_16, H * 2 * Z}};
+                      {&p->W4_16, D * H}, {&p->W4T_16, H * D}, {&p->W3T_16, Z * H}, {&p->W2xT_16, H * 2 * Z}, {&p->x16_set[1], Bm * D}};
   size_t bytes = 256;
   for (auto& it : items) bytes += (it.n * sizeof(float) + 255) / 256 * 256;
   if (b.bf16)
@@ -1646,7 +1668,12 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   for (auto& it : items) { *it.ptr = reinterpret_cast<float*>(q); q += (it.n * sizeof(float) + 255) / 256 * 256; }
   if (b.bf16)
     for (auto& it : items16) { *it.ptr = reinterpret_cast<__nv_bfloat16*>(q); q += (it.n * sizeof(__nv_bfloat16) + 255) / 256 * 256; }
+  p->x_stage_set[0] = b.x_stage; p->xT_set[0] = p->xT; p->W3T_set[0] = p->W3T; p->x16_set[0] = p->x16;
   int r = MDT_OK;
+  if (cudaStreamCreateWithFlags(&p->side_pf, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_pf_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_pf_join, cudaEventDisableTiming) != cudaSuccess)
+    r = set_error(MDT_ERR_CUDA, "prefetch stream");
   if (cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&p->side2, cudaStreamNonBlocking) != cudaSuccess ||
       cudaStreamCreateWithFlags(&p->side3, cudaStreamNonBlocking) != cudaSuccess ||
@@ -1701,6 +1728,9 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
     MDT_TRY(tc05_encode(&m.h3Ta, p->h3T, b.H, B, ldB, p->bn_dwa, bf));
     MDT_TRY(tc05_encode(&m.h1Ta, p->h1T, b.H, B, ldB, p->bn_dwa, bf));
     MDT_TRY(tc05_encode(&m.xTa, p->xT, b.D, B, ldB, p->bn_dwa, bf));
+    MDT_TRY(tc05_encode(&m.x_1, act(p->x_stage_set[1], p->x16_set[1]), B, b.D, b.D, kTcBM, bf));
+    MDT_TRY(tc05_encode(&m.xT_1, p->xT_set[1], b.D, B, ldB, p->bn_dw, bf));
+    MDT_TRY(tc05_encode(&m.xTa_1, p->xT_set[1], b.D, B, ldB, p->bn_dwa, bf));
     MDT_TRY(tc05_encode(&m.h1B, act(b.h1, p->h1_16), B, b.H, b.H, p->bn_skinny, bf));
     MDT_TRY(tc05_encode(&m.da3B, act(b.da3, p->da3_16), B, b.H, b.H, p->bn_skinny, bf));
     it = p->maps.emplace(B, m).first;
@@ -1730,6 +1760,43 @@ inline int tc05_splits_dw(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn, 
   return tc05_pick_splits(M, N, K, bn, tc05_sms(p) / 2, e, Tc05Plan::kWsFloats / 2);
 }
 
+// The step's prologue kernel into input set `set`: x -> stage copy (+ bf16 copy) and x^T; with `with_eps` also the
+// step's eps from Philox (tensor-core latent path: the CUDA-core latent_fwd draws its own).  cursor_add = 1 fetches the
+// NEXT step's batch of a mdt_train_steps source.
+inline int tc05_prep(Tc05Plan* p, cudaStream_t s, const float* x, int B, int set, bool with_eps, int cursor_add, const char* label,
+                     bool programmatic = true) {
+  const Tc05Buffers& b = p->b;
+  const int D = b.D, Z = b.Z;
+  PrepArgs pa{};
+  int blocks = 0;
+  const float* src = (p->x_src != nullptr) ? p->x_src : x;
+  float* const stage = p->x_stage_set[set];
+  tr_add(pa.tr, blocks, src, p->xT_set[set], B, D, D, p->ldB, b.bf16, nullptr, b.bf16 ? p->x16_set[set] : nullptr, D);
+  pa.tr_blocks = blocks;
+  pa.x_copy = (src != stage) ? stage : nullptr;
+  if (p->src_pool != nullptr || p->src_images != nullptr) {
+    pa.pool = p->src_pool; pa.images = p->src_images; pa.indices = p->src_indices;
+    pa.n_batches = p->src_n_batches; pa.n_images = p->src_n_images; pa.st = b.st;
+    pa.x_copy = stage;
+    pa.cursor_add = cursor_add;
+  }
+  if (with_eps) {
+    pa.eps_out = b.eps; pa.n_eps = (long long)B * Z; pa.st = b.st;
+    torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
+    blocks += (int)((pa.n_eps + 255) / 256);
+  }
+  if (programmatic) {
+    MDT_CUDA(launch_pdl(prep_kernel, dim3(blocks), dim3(256), 0, s, pa));
+  } else {
+    prep_kernel<<<dim3(blocks), dim3(256), 0, s>>>(pa);
+    MDT_CUDA(cudaGetLastError());
+  }
+  p->last_prep = pa;
+  p->prep_launched = true;
+  TC_NOTE(p, label);
+  return MDT_OK;
+}
+
 // Forward.  fuse_loss: fc4's epilogue also produces the loss, d(logits) and its transpose (training step);
 // otherwise fc4 stops at recon (mdt_forward / eval / decode) and the stand-alone loss kernel may follow.
 inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, const float* eps_in, bool decode_only,
@@ -1740,41 +1807,46 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
   const float* P = b.params;
   Tc05ActMaps* m = nullptr;
   MDT_TRY(tc05_act_maps(p, B, &m));
+  const bool pipe = p->pipelined && p->simt_latent && !decode_only && fuse_loss;
+  if (!pipe) p->xpar = 0;                        // everything but the pipelined steps of mdt_train_steps works on input set 0
+  const int xs = p->xpar;
+  const float* const xst = p->x_stage_set[xs];   // this step's x (BCE target, fc1's A operand through its tensor map)
+  bool gen_eps_latent = false;                   // latent_fwd draws eps itself
   if (!decode_only) {
     MDT_CHECK(x == b.x_stage, "tcgen05 path reads x from the engine's stage buffer");
-    {
-      PrepArgs pa{};
-      int blocks = 0;
-      const float* src = (p->x_src != nullptr) ? p->x_src : x;
-      tr_add(pa.tr, blocks, src, p->xT, B, D, D, p->ldB, b.bf16, nullptr, b.bf16 ? p->x16 : nullptr, D);
-      pa.tr_blocks = blocks;
-      pa.x_copy = (src != b.x_stage) ? b.x_stage : nullptr;
-      if (p->src_pool != nullptr || p->src_images != nullptr) {
-        pa.pool = p->src_pool; pa.images = p->src_images; pa.indices = p->src_indices;
-        pa.n_batches = p->src_n_batches; pa.n_images = p->src_n_images; pa.st = b.st;
-        pa.x_copy = b.x_stage;
-      }
-      if (eps_in == nullptr) {
-        pa.eps_out = b.eps; pa.n_eps = (long long)B * Z; pa.st = b.st;
-        torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
-        blocks += (int)((pa.n_eps + 255) / 256);
-        eps_in = b.eps;
-      }
-      MDT_CUDA(launch_pdl(prep_kernel, dim3(blocks), dim3(256), 0, s, pa));
-      p->last_prep = pa;
-      p->prep_launched = true;
-      TC_NOTE(p, "prep_xT_eps");
+    bool prep_eps = false;
+    if (eps_in == nullptr) {
+      if (p->simt_latent) gen_eps_latent = true; // the CUDA-core latent_fwd draws eps itself, ahead of its dependency wait
+      else { prep_eps = true; eps_in = b.eps; }  // tensor-core latent path: drawn by the prologue kernel
     }
+    // pipelined steps have no prologue: set `xs` was filled while the previous step ran (or by mdt_train_steps' first call)
+    if (!pipe) MDT_TRY(tc05_prep(p, s, x, B, xs, prep_eps, 0, "prep_xT_eps"));
     Tc05Epi e1{};
     e1.C = b.h1; e1.ldc = H; e1.CT = p->h1T; e1.ldct = p->ldB; e1.bias = P + b.L.off[B1]; e1.act = MDT_ACT_RELU;
-    e1.pre_b = p->preload;                       // W1: last written by the previous step's update
+    // W1 was last written by the previous step's update: its loads may go out before the dependency wait -- but only
+    // when a prologue kernel sits between that update and this GEMM (a pipelined step follows the update directly)
+    e1.pre_b = pipe ? 0 : p->preload;
     e1.bf16 = b.bf16; e1.Cb = b.bf16 ? p->h1_16 : nullptr; e1.ldcb = H;
-    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
+    MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, xs ? m->x_1 : m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
+    if (pipe) {
+      // the next step's batch goes into the other input set on a side stream, behind this step's first GEMM (whose
+      // start implies the previous step, the last reader of that set, is complete); joined where the step joins its
+      // weight-gradient streams
+      MDT_CUDA(cudaEventRecord(p->ev_pf_fork, s));
+      MDT_CUDA(cudaStreamWaitEvent(p->side_pf, p->ev_pf_fork, 0));
+      // NOT a programmatic launch: its blocks would be resident from this GEMM's start, parked in the dependency wait
+      // on the SMs the next kernel of the step needs for its own early start (measured: latent_fwd entered 3 us late)
+      MDT_TRY(tc05_prep(p, p->side_pf, x, B, xs ^ 1, false, 1, "prefetch_xT", /*programmatic=*/false));
+      MDT_CUDA(cudaEventRecord(p->ev_pf_join, p->side_pf));
+      p->prefetch_pending = true;
+    }
     if (p->simt_latent) {
       LatentFwdArgs la{};
       la.h1 = b.h1; la.H = H; la.W2x = P + b.L.off[W2X]; la.b2x = P + b.L.off[B2X]; la.W3 = P + b.L.off[W3]; la.b3 = P + b.L.off[B3];
-      la.eps_in = eps_in; la.ml = b.ml; la.z = b.z; la.zT = p->zT; la.ldT = p->ldB; la.eps_out = b.eps; la.sd_out = b.sd;
+      la.eps_in = gen_eps_latent ? nullptr : eps_in; la.ml = b.ml;
+      la.st = b.st;
+      torch_randn_policy((long long)B * Z, b.sm_count, b.max_threads_sm, &la.philox_S, &la.philox_inc); la.z = b.z; la.zT = p->zT; la.ldT = p->ldB; la.eps_out = b.eps; la.sd_out = b.sd;
       la.dml_kl = b.dml_kl; la.kl_partials = p->kl_partials; la.h3 = b.h3; la.h3T = p->h3T; la.B = B; la.Z = Z;
       la.bf16 = b.bf16; la.h3b = b.bf16 ? p->h3_16 : nullptr;
       la.dbg = tc05_dbg_buffer();
@@ -1807,7 +1879,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
   }
   if (fuse_loss && !decode_only) {
     Tc05Epi e4{};
-    e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = x; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
+    e4.C = b.recon; e4.ldc = D; e4.bias = P + b.L.off[B4]; e4.x = xst; e4.ldx = D; e4.da4 = b.da4; e4.da4T = p->da4T;
     e4.ld_da4T = p->ldB; e4.bce_partials = p->bce_partials; e4.ticket = p->ticket; e4.loss_out = b.loss_dev;
     e4.kl_partials = p->kl_partials; e4.n_kl_partials = (B + p->bn_skinny - 1) / p->bn_skinny;
     e4.pre_b = p->preload;                       // W4
@@ -1838,13 +1910,23 @@ inline int tc05_after_external_da4(Tc05Plan* p, cudaStream_t s, int B) {
 inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
   const Tc05Buffers& b = p->b;
   LatentBwdArgs la{};
-  la.da3 = b.da3; la.H = b.H; la.W3T = p->W3T; la.W2xT = p->W2xT; la.h1 = b.h1;
+  la.da3 = b.da3; la.H = b.H; la.W3T = p->W3T_set[p->w3par]; la.W2xT = p->W2xT; la.h1 = b.h1;
   la.eps = b.eps; la.sd = b.sd; la.dml_kl = b.dml_kl; la.dml = b.dml; la.dmlT = p->dmlT; la.ldT = p->ldB; la.da1T = p->da1T;
   la.B = B; la.Z = b.Z; la.bf16 = b.bf16;
   la.dbg = tc05_dbg_buffer();
   if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true), s));
   TC_NOTE(p, "latent_bwd");
+  return MDT_OK;
+}
+
+// End of a pipelined step: the next batch (fetched on the side stream since this step's first GEMM) is in place; the
+// step after this one works on the other input set.
+inline int tc05_join_prefetch(Tc05Plan* p, cudaStream_t s) {
+  if (!p->prefetch_pending) return MDT_OK;
+  MDT_CUDA(cudaStreamWaitEvent(s, p->ev_pf_join, 0));
+  p->prefetch_pending = false;
+  p->xpar ^= 1;
   return MDT_OK;
 }
 
@@ -1915,7 +1997,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   }
   e = Tc05Epi{};
   e.bf16 = b.bf16; e.C = G + b.L.off[W1]; e.ldc = D; e.a_src = p->da1T; e.lda_src = ldB; e.db = G + b.L.off[B1];
-  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, m->xT, H, D, B, e, s, tc05_splits_dw(p, e, H, D, B, p->bn_dw, 3)));
+  MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da1T, p->xpar ? m->xT_1 : m->xT, H, D, B, e, s, tc05_splits_dw(p, e, H, D, B, p->bn_dw, 3)));
   TC_NOTE(p, "fc1_dW");
   if (fork) {                                     // join: the gradient buffer is complete once the side streams drain
     cudaStream_t st[3] = {sw, sw3, sw2x};
@@ -1925,6 +2007,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
       MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
     }
   }
+  MDT_TRY(tc05_join_prefetch(p, s));
   return MDT_OK;
 }
 
@@ -1967,9 +2050,11 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   if (const char* v = getenv("MDT_BN_DW1")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn1 = c; }
   Dw dw[4] = {
       {W4, B4, D, H, bn4, 0, &m->da4T, bn4 == bna ? &m->h3Ta : &m->h3T, p->da4T, p->W4T, D, w4_split ? "fc4_dW" : "fc4_dW_adam", 1},
-      {W3, B3, H, Z, 32, 1, &m->da3T, &m->zT, p->da3T, p->W3T, H, "fc3_dW_adam", 1},
+      // fc3's update writes the transpose into the W3^T set latent_bwd is NOT reading (CUDA-core latent path): see below
+      {W3, B3, H, Z, 32, 1, &m->da3T, &m->zT, p->da3T, p->simt_latent ? p->W3T_set[p->w3par ^ 1] : p->W3T, H, "fc3_dW_adam", 1},
       {W2X, B2X, 2 * Z, H, bna, 2, &m->dmlT, &m->h1Ta, p->dmlT, p->W2xT, 2 * Z, "fc2x_dW_adam", 1},
-      {W1, B1, H, D, bn1, 3, &m->da1T, bn1 == bna ? &m->xTa : &m->xT, p->da1T, nullptr, 0, "fc1_dW_adam", 1},
+      {W1, B1, H, D, bn1, 3, &m->da1T, bn1 == bna ? (p->xpar ? &m->xTa_1 : &m->xTa) : (p->xpar ? &m->xT_1 : &m->xT), p->da1T, nullptr, 0,
+       "fc1_dW_adam", 1},
   };
   Tc05Epi ed[4];
   int total_ctas = 0;
@@ -2037,17 +2122,24 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     // one costs latent_bwd its early launch.  All four updates start together once latent_bwd is done -- fc4's is
     // not on the critical path, the last of the other three is.
     const bool dw4_early = getenv("MDT_DW4_LATE") == nullptr;
+    // fc3's update could start with fc4's, right after fc4's input-gradient GEMM: its operands (da3^T, z^T) are ready,
+    // W3 has no reader left in this step, and the updated W3^T goes into the set latent_bwd is not reading.
+    // Measured: NOT a gain -- 60.0 vs 58.8 us/step (tf32x3), 48.3 vs 47.5 (bf16): its 4 CTAs and fc4's 91 hold SMs that
+    // latent_bwd and then fc1's update want.  Off by default (MDT_DW3_EARLY=1 turns it on).
+    const bool dw3_early = dw4_early && getenv("MDT_DW3_EARLY") != nullptr;
     if (dw4_early) {
-      MDT_TRY(after_main(sa, nullptr));           // E1: W4^T no longer needed, da3^T ready
+      MDT_TRY(after_main(sa, dw3_early ? sb : nullptr));   // E1: W4^T no longer needed, da3^T ready
       MDT_TRY(launch_dw(0, sa));
+      if (dw3_early) MDT_TRY(launch_dw(1, sb));
     }
-    MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3^T and W2x^T
+    MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3T_set[w3par] and W2x^T
     if (fork) {
       MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
-      for (cudaStream_t t : {sa, sb, sc, sd}) if (t != sa || !dw4_early) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
+      for (cudaStream_t t : {sa, sb, sc, sd})
+        if (!((t == sa && dw4_early) || (t == sb && dw3_early))) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
       ++nf;
     }
-    MDT_TRY(launch_dw(1, sb));
+    if (!dw3_early) MDT_TRY(launch_dw(1, sb));
     MDT_TRY(launch_dw(2, sd));
     // fc1's update is the longest of the three: it stays on the main stream, where it is launched programmatically
     // behind latent_bwd and has its set-up (barriers, TMEM, descriptor and parameter fetches: ~2.5 us for an
@@ -2084,6 +2176,8 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
       MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
     }
   }
+  if (p->simt_latent) p->w3par ^= 1;              // the next reader of W3^T takes the set this step's update wrote
+  MDT_TRY(tc05_join_prefetch(p, s));
   return MDT_OK;
 }
 

