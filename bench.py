@@ -606,7 +606,7 @@ def run_own(args):
             "arm": {"gemm_mode": args.gemm_mode,
                     "gemm_note": "tf32x3 = three tcgen05 kind::tf32 passes (hi*hi + hi*lo + lo*hi) with fp32 promotion: fp32-grade products, fp32 storage",
                     "cuda_graph": graph,
-                    "api": "mdt_train_steps: graphs of 8 steps each, the batch index advances in device memory",
+                    "api": "mdt_train_steps: graphs of 16 steps each, the batch index advances in device memory, each step fetches its successor's batch",
                     "l2": f"inputs cycle through a {POOL_BATCHES}-batch device pool ({POOL_BATCHES * B * D * 4 / 1e6:.0f} MB > 126 MB L2); "
                           "parameters and optimizer state are step-to-step resident by the nature of training",
                     "eps": "Philox in-kernel (torch-CUDA-compatible stream)"},

@@ -366,6 +366,52 @@ int check_batch(mdt_engine* e, int B) {
   return MDT_OK;
 }
 
+// Transitive reduction of a captured step graph.  Stream capture gives every kernel an edge from the previous node of
+// ITS stream: in a graph that holds several steps, a side-stream kernel of step j (a weight-gradient GEMM, the input
+// prefetch) thus depends on its step j-1 twin as well as on the main-stream kernel it was forked behind.  The first
+// edge is redundant (step j-1 was joined into the main stream long before), but a kernel node with two incoming edges
+// is not launched early on its programmatic one: measured, those kernels started 2.5-7 us late, which is why graphs of
+// several steps were no faster than single-step ones.  Removing every edge u -> v for which another path u ~> v exists
+// keeps the order (each kernel of the step waits for its programmatic predecessor before it reads or triggers anything,
+// so order is transitive along such paths too) and gives those kernels their single, programmatic edge back.
+int reduce_graph_edges(cudaGraph_t g, int* removed) {
+  *removed = 0;
+  size_t nn = 0, ne = 0;
+  MDT_CUDA(cudaGraphGetNodes(g, nullptr, &nn));
+  MDT_CUDA(cudaGraphGetEdges_v2(g, nullptr, nullptr, nullptr, &ne));
+  if (nn == 0 || ne == 0 || nn > 4096) return MDT_OK;
+  std::vector<cudaGraphNode_t> nodes(nn), from(ne), to(ne);
+  std::vector<cudaGraphEdgeData> data(ne);
+  MDT_CUDA(cudaGraphGetNodes(g, nodes.data(), &nn));
+  MDT_CUDA(cudaGraphGetEdges_v2(g, from.data(), to.data(), data.data(), &ne));
+  std::map<cudaGraphNode_t, int> id;
+  for (size_t i = 0; i < nn; ++i) id[nodes[i]] = (int)i;
+  std::vector<std::vector<int>> succ(nn);
+  for (size_t k = 0; k < ne; ++k) succ[id[from[k]]].push_back(id[to[k]]);
+  std::vector<char> seen(nn);
+  std::vector<int> stack;
+  for (size_t k = 0; k < ne; ++k) {
+    const int u = id[from[k]], v = id[to[k]];
+    // is v reachable from u without the direct edge?
+    std::fill(seen.begin(), seen.end(), 0);
+    stack.clear();
+    for (int w : succ[u]) if (w != v && !seen[w]) { seen[w] = 1; stack.push_back(w); }
+    bool redundant = false;
+    while (!stack.empty() && !redundant) {
+      const int w = stack.back(); stack.pop_back();
+      for (int y : succ[w]) {
+        if (y == v) { redundant = true; break; }
+        if (!seen[y]) { seen[y] = 1; stack.push_back(y); }
+      }
+    }
+    if (redundant) {
+      MDT_CUDA(cudaGraphRemoveDependencies_v2(g, &from[k], &to[k], &data[k], 1));
+      ++*removed;
+    }
+  }
+  return MDT_OK;
+}
+
 // Run `fn` through the CUDA-graph cache when enabled.
 template <class F>
 int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
@@ -386,6 +432,13 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
       return r;
     }
     if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+    static const bool reduce_on = getenv("MDT_NO_GRAPH_REDUCE") == nullptr;
+    if (reduce_on) {
+      int removed = 0;
+      const int rr = reduce_graph_edges(g, &removed);
+      if (rr != MDT_OK) { cudaGraphDestroy(g); return rr; }
+      if (getenv("MDT_GRAPH_DBG")) fprintf(stderr, "[mdt] graph kind %d B %d: %lld kernels, %d redundant edges removed\n", kind, B, kernels, removed);
+    }
     cudaGraphExec_t ex = nullptr;
     ce = cudaGraphInstantiate(&ex, g, 0);
     if (ce != cudaSuccess) { cudaGraphDestroy(g); return set_error(MDT_ERR_CUDA, "cudaGraphInstantiate: %s", cudaGetErrorString(ce)); }
@@ -994,7 +1047,7 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   p->src_pool = src->x_pool; p->src_images = src->x_pool ? nullptr : src->images_u8;
   p->src_indices = reinterpret_cast<const long long*>(src->indices);
   p->src_n_batches = src->n_batches; p->src_n_images = src->n_images;
-  static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 8;
+  static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 16;
   int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
   if (U > 1 && (U & 1)) ++U;                         // a multi-step graph must leave the two-set parities where it found them
   // graphs are specific to the source (its pointers are kernel arguments): a new source drops the cached ones

@@ -1,6 +1,8 @@
 """Phase timing of CTA (0,0) of every tcgen05 GEMM in one un-graphed training step (MDT_TC05_DBG=1)."""
 import os, sys, ctypes as C
 os.environ["MDT_TC05_DBG"] = "1"
+if os.environ.get("SOURCED", "0") == "1":
+    os.environ.setdefault("MDT_STEPS_PER_GRAPH", "2")
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 from multidisttorch_b200 import engine as E, _lib
