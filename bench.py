@@ -64,6 +64,8 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-eager", action="store_true", help="skip the torch-CUDA eager run of the reference step")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
+    ap.add_argument("--max-seconds", type=float, default=1200.0,
+                    help="watchdog: after this long rank 0 prints what it has (\"incomplete\" set) and every rank exits")
     ap.add_argument("--ref-worker", default="", help=argparse.SUPPRESS)
     ap.add_argument("--eager-worker", default="", help=argparse.SUPPRESS)
     return ap.parse_args()
@@ -386,8 +388,41 @@ def allreduce_section(ctx, args):
     return out
 
 
+_PARTIAL = {}          # rank 0: the JSON line as far as it is known (the watchdog prints it if the run stalls)
+
+
+def start_watchdog(seconds, rank):
+    import threading
+
+    def fire():
+        if rank == 0:
+            out = dict(_PARTIAL)
+            out["incomplete"] = f"watchdog: the run did not finish within {seconds:.0f} s; sections after the last key are missing"
+            if "metric" in out:
+                emit(out)
+        sys.stderr.write(f"[bench] rank {rank}: watchdog after {seconds:.0f} s, exiting\n")
+        sys.stderr.flush()
+        os._exit(0 if rank == 0 and "metric" in _PARTIAL else 4)
+
+    t = threading.Timer(seconds, fire)
+    t.daemon = True
+    t.start()
+    return t
+
+
+def section(name, fn, default=None):
+    """Optional part of the line: a failure is recorded under its key instead of losing the whole line."""
+    try:
+        return fn()
+    except Exception as exc:       # noqa: BLE001
+        import traceback
+        traceback.print_exc()
+        return {"error": f"{type(exc).__name__}: {str(exc)[:300]}"} if default is None else default
+
+
 def run_own(args):
     ctx = Ctx(args)
+    watchdog = start_watchdog(args.max_seconds, ctx.rank)
     torch, dist = ctx.torch, ctx.dist
     rank, world, device = ctx.rank, ctx.world, ctx.device
     from multidisttorch_b200 import synth
@@ -479,6 +514,13 @@ def run_own(args):
                   "step's loss is read by the host from the device-written mailbox; wall clock, max over ranks, median of regions",
            "sync_value": world * B / sync_s, "sync_ms_per_step": sync_s * 1e3}
 
+    if rank == 0:
+        _PARTIAL.update({
+            "metric": METRIC, "value": round(value, 1), "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "f32" if args.gemm_mode != "bf16" else "bf16", "gemm": args.gemm_mode, "data": "synthetic",
+            "config": config_of(world, B, H), "clocks": clk, "e2e": e2e, "ddp_parity": parity})
+
     # ---- per-kernel device time (un-graphed, event after each kernel) -> roofline of the dominant kernel
     roofline = None
     kernels = None
@@ -551,44 +593,58 @@ def run_own(args):
             ng = world // k
             groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]
             mine = groups[rank // k]
-            best = None
+            name = f"{ng}x{k}"
+
+            def one(mode, xch):
+                e2 = new_engine(mode, group=mine, seed=1234 + rank // k, **({"exchange": xch} if xch else {}))
+                try:
+                    if xch in ("p2p", "p2p_two_shot") and not e2.p2p:
+                        return None
+                    ms2, _, _, _ = timed_regions(ctx, e2, pool_enqueue(e2), short, W, 3)
+                    return round(world * B / (ms2 * 1e-3), 1)
+                finally:
+                    e2.close()
+
             per = {}
             for xch in ("p2p", "p2p_two_shot", "nccl"):
-                e2 = new_engine(args.gemm_mode, group=mine, seed=1234 + rank // k, exchange=xch)
-                if xch == "nccl" or e2.p2p:
-                    ms2, _, _, _ = timed_regions(ctx, e2, pool_enqueue(e2), short, W, 3)
-                    per[xch] = round(world * B / (ms2 * 1e-3), 1)
-                e2.close()
-            e2 = new_engine(args.gemm_mode, group=mine, seed=1234 + rank // k)      # the shipped (automatic) choice
-            ms2, _, _, _ = timed_regions(ctx, e2, pool_enqueue(e2), short, W, 3)
-            e2.close()
-            layouts[f"{ng}x{k}"] = round(world * B / (ms2 * 1e-3), 1)
-            exchanges[f"{ng}x{k}"] = per
+                v = section(f"exchanges/{name}/{xch}", lambda: one(args.gemm_mode, xch))
+                if v is not None:
+                    per[xch] = v
+            layouts[name] = section(f"layouts/{name}", lambda: one(args.gemm_mode, None))     # the shipped (automatic) choice
+            exchanges[name] = per
             if layouts_bf16 is not None:          # BASELINE config 4 names bf16 GEMMs (2 trials x 4-GPU groups at N = 8)
-                e3 = new_engine("bf16", group=mine, seed=1234 + rank // k)
-                ms3, _, _, _ = timed_regions(ctx, e3, pool_enqueue(e3), short, W, 3)
-                e3.close()
-                layouts_bf16[f"{ng}x{k}"] = round(world * B / (ms3 * 1e-3), 1)
+                layouts_bf16[name] = section(f"layouts_bf16/{name}", lambda: one("bf16", None))
             k *= 2
-        allreduce = allreduce_section(ctx, args)
+        if rank == 0:
+            _PARTIAL.update({"layouts": layouts, "layouts_bf16": layouts_bf16, "exchanges": exchanges})
+        allreduce = section("allreduce", lambda: allreduce_section(ctx, args))
+        if rank == 0:
+            _PARTIAL.update({"allreduce": allreduce})
         if world == 8:
-            config5 = run_config5(ctx, args, new_engine, peaks)
+            config5 = section("config5", lambda: run_config5(ctx, args, new_engine, peaks))
+            if rank == 0:
+                _PARTIAL.update({"config5": config5})
 
     total_launches = ctx.sum(launches)
 
     # ---- comparison lines at N = 1: the unchanged reference step on torch-CUDA eager, and the drop-in's compat path
     eager, compat = None, None
     if not args.no_eager:
-        eager = run_eager(ctx, args, B, H)
+        eager = section("torch_cuda_eager", lambda: run_eager(ctx, args, B, H))
+    script_e2e = None
     if world == 1 and not args.no_modes:
-        compat = run_compat(ctx, args, B, H, pool)
+        compat = section("compat_mode", lambda: run_compat(ctx, args, B, H, pool))
+        if not args.no_eager:
+            script_e2e = section("unchanged_script", lambda: run_unchanged_script(ctx, args))
+    if rank == 0:
+        _PARTIAL.update({"torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e})
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
         # rank 0 times the reference's CPU path on the host cores while the other ranks sleep on a store key (a NCCL
         # barrier would keep their host threads spinning on the cores being measured)
         if rank == 0:
-            cpu_baseline = run_reference(world, B, H, steps=None, warmup=5, seconds=args.cpu_seconds)["cpu_baseline"]
+            cpu_baseline = section("cpu_baseline", lambda: run_reference(world, B, H, steps=None, warmup=5, seconds=args.cpu_seconds)["cpu_baseline"])
         if world > 1:
             store = dist.distributed_c10d._get_default_store()
             if rank == 0:
@@ -617,9 +673,12 @@ def run_own(args):
             "gpu_launches_per_step": round(total_launches / (world * R * n_region), 2), "roofline": roofline,
             "cpu_baseline": cpu_baseline, "ddp_parity": parity, "layouts": layouts, "layouts_bf16": layouts_bf16,
             "exchanges": exchanges, "allreduce": allreduce, "config5": config5, "modes": modes,
-            "trials_per_gpu": multi_trial, "torch_cuda_eager": eager, "compat_mode": compat, "kernels": kernels,
+            "trials_per_gpu": multi_trial, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
+            "kernels": kernels,
         }
+        watchdog.cancel()
         emit(out)
+    watchdog.cancel()
     if world > 1:
         dist.barrier(device_ids=[ctx.local])
         dist.destroy_process_group()
@@ -843,6 +902,59 @@ def run_compat(ctx, args, B, H, pool):
     finally:
         if installed:
             dropin.uninstall()
+
+
+def run_unchanged_script(ctx, args):
+    """End to end: the reference's vae-hpo.py itself (oracle/_ref, executed unmodified with runpy), one trial, one
+    epoch over an MNIST-sized synthetic idx dataset (60,000 train + 10,000 test images), on this GPU -- once on plain
+    torch-CUDA with its PIL DataLoader, once with the drop-in active (engine behind DistributedDataParallel / Adam,
+    device-resident loader).  Reported: samples / (the script's own "Done. time")."""
+    import re
+    import struct
+    import numpy as np
+    script = os.path.join(ROOT, "oracle", "_ref", "vae-hpo.py")
+    if not os.path.exists(script):
+        return None
+    tmp = tempfile.mkdtemp(prefix="mdt_script_")
+    raw = os.path.join(tmp, "data", "MNIST", "raw")
+    os.makedirs(raw)
+    rs = np.random.RandomState(0)
+    for split, n in (("train", 60000), ("t10k", 10000)):
+        with open(os.path.join(raw, f"{split}-images-idx3-ubyte"), "wb") as f:
+            f.write(struct.pack(">IIII", 0x00000803, n, 28, 28))
+            f.write(rs.randint(0, 256, (n, 28, 28), dtype=np.uint8).tobytes())
+        with open(os.path.join(raw, f"{split}-labels-idx1-ubyte"), "wb") as f:
+            f.write(struct.pack(">II", 0x00000801, n))
+            f.write(rs.randint(0, 10, (n,), dtype=np.uint8).tobytes())
+    runner = ("import runpy, sys, torch; torch.manual_seed(1234); sys.argv = sys.argv[1:]; "
+              "runpy.run_path(sys.argv[0], run_name='__main__')")
+    out = {}
+    for name, dropin in (("plain_torch_cuda", "0"), ("dropin", "1")):
+        env = dict(os.environ)
+        for k in list(env):
+            if k.startswith("TORCHELASTIC") or k in _LAUNCHER_VARS:
+                env.pop(k)
+        env.update(OMPI_COMM_WORLD_SIZE="1", OMPI_COMM_WORLD_RANK="0", OMPI_COMM_WORLD_LOCAL_RANK="0", MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(24000 + os.getpid() % 20000 + (1 if dropin == "1" else 0)), MDT_DROPIN=dropin,
+                   CUDA_VISIBLE_DEVICES=str(ctx.local), NVIDIA_TF32_OVERRIDE="0", PYTHONPATH=ROOT + os.pathsep + env.get("PYTHONPATH", ""))
+        t0 = time.perf_counter()
+        p = subprocess.run([sys.executable, "-c", runner, script, "--ngroups", "1", "--epochs", "1", "--batch-size", "128"],
+                           env=env, cwd=tmp, capture_output=True, text=True, timeout=900)
+        wall = time.perf_counter() - t0
+        m = re.search(r"Done\. time: ([0-9.]+)", p.stdout)
+        if p.returncode != 0 or not m:
+            out[name] = {"error": (p.stderr or p.stdout)[-400:]}
+            continue
+        t = float(m.group(1))
+        losses = re.findall(r"(?:Average loss|Test set loss): ([0-9.]+)", p.stdout)
+        out[name] = {"samples_per_s": round(70000 / t, 1), "script_seconds": round(t, 3), "process_seconds": round(wall, 1),
+                     "avg_train_loss": float(losses[0]) if losses else None, "test_loss": float(losses[1]) if len(losses) > 1 else None,
+                     "engine": "-> B200 engine" in p.stdout, "device_loader": "device-resident loader" in p.stdout}
+    out["what"] = ("unchanged vae-hpo.py, --ngroups 1 --epochs 1 --batch-size 128, 60,000 + 10,000 synthetic MNIST-format images; "
+                   "samples/s = 70,000 / the script's own timer (train + test + sampling + PNG dumps)")
+    import shutil
+    shutil.rmtree(tmp, ignore_errors=True)
+    return out
 
 
 # --------------------------------------------------------------------------------------------

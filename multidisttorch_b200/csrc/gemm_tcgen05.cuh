@@ -1545,6 +1545,7 @@ struct Tc05Plan {
   float* W3T_set[2] = {nullptr, nullptr};
   int xpar = 0, w3par = 0;
   bool pipelined = false;        // set by mdt_train_steps around its enqueues: no prologue in the step, prefetch the next batch
+  bool no_prefetch = false;      // pipelined step whose successor's batch is fetched by the caller (host-buffer steps)
   bool prefetch_pending = false; // a prefetch was forked in this step and has not been joined yet
   cudaStream_t side_pf = nullptr;
   cudaEvent_t ev_pf_fork = nullptr, ev_pf_join = nullptr;
@@ -1829,7 +1830,7 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
     e1.bf16 = b.bf16; e1.Cb = b.bf16 ? p->h1_16 : nullptr; e1.ldcb = H;
     MDT_TRY(tc05_launch<EPI_BIAS_ACT>(p->bn_h, sp, xs ? m->x_1 : m->x, p->mW1, B, H, D, e1, s, tc05_splits(p, e1, B, H, D, p->bn_h)));
     TC_NOTE(p, "fc1_fwd");
-    if (pipe) {
+    if (pipe && !p->no_prefetch) {
       // the next step's batch goes into the other input set on a side stream, behind this step's first GEMM (whose
       // start implies the previous step, the last reader of that set, is complete); joined where the step joins its
       // weight-gradient streams

@@ -137,6 +137,11 @@ struct mdt_engine {
   cudaEvent_t ev_copied[kPreSlots] = {}, ev_used[kPreSlots] = {};
   bool pre_used[kPreSlots] = {};
   unsigned int pre_next = 0;
+  // host-buffer steps submitted while a step is in flight: the prologue of the new step (pinned x -> input set) runs
+  // on the copy stream, alternating between the two input sets of the tensor-core plan
+  cudaEvent_t ev_set_ready[2] = {}, ev_set_free[2] = {};
+  bool set_used[2] = {};
+  int host_set = 0;
   float sync_losses[64] = {};
   unsigned int sync_seq = 0;                       // losses of submitted steps on configurations without the mailbox
   unsigned int pub_expected = 0;                    // training steps enqueued so far that publish to the mailbox
@@ -578,8 +583,9 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
   struct ParityAfter {       // a replayed graph does not run the enqueue code that flips the parities: set them here
     mdt_engine* e; int x, w;
     ~ParityAfter() { if (e->tc) { e->tc->xpar = x; e->tc->w3par = w; e->tc->prefetch_pending = false; } }
-  } parity_after{e, piped ? (x0 ^ (steps & 1)) : 0, w3_flips ? (w0 ^ (steps & 1)) : w0};
-  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8) | (x0 << 20) | (w0 << 21);
+  } parity_after{e, piped && !e->tc->no_prefetch ? (x0 ^ (steps & 1)) : (piped ? x0 : 0), w3_flips ? (w0 ^ (steps & 1)) : w0};
+  const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8) | (x0 << 20) | (w0 << 21) |
+                 ((piped ? 1 : 0) << 22) | ((piped && e->tc->no_prefetch ? 1 : 0) << 23);
   if (e->tc) e->pub_expected = (e->pub_expected + (unsigned)steps) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
   if (e->tc && !e->sourced) e->cursor_expected = -1;                     // ... and moves the device-side batch cursor
@@ -739,7 +745,9 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
       if (cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking) != cudaSuccess)
         r = set_error(MDT_ERR_CUDA, "could not create the copy stream");
       for (int k = 0; k < mdt_engine::kPreSlots && r == MDT_OK; ++k) {
-        if (cudaMalloc(&e->x_pre[k], (size_t)e->Bmax * e->D * sizeof(float)) != cudaSuccess ||
+        if ((k < 2 && (cudaEventCreateWithFlags(&e->ev_set_ready[k], cudaEventDisableTiming) != cudaSuccess ||
+                       cudaEventCreateWithFlags(&e->ev_set_free[k], cudaEventDisableTiming) != cudaSuccess)) ||
+            cudaMalloc(&e->x_pre[k], (size_t)e->Bmax * e->D * sizeof(float)) != cudaSuccess ||
             cudaEventCreateWithFlags(&e->ev_copied[k], cudaEventDisableTiming) != cudaSuccess ||
             cudaEventCreateWithFlags(&e->ev_used[k], cudaEventDisableTiming) != cudaSuccess)
           r = set_error(MDT_ERR_CUDA, "could not create the host-input staging ring (%zu bytes per slot)",
@@ -769,6 +777,8 @@ void mdt_engine_destroy(mdt_engine* e) {
     if (e->x_pre[k]) cudaFree(e->x_pre[k]);
     if (e->ev_copied[k]) cudaEventDestroy(e->ev_copied[k]);
     if (e->ev_used[k]) cudaEventDestroy(e->ev_used[k]);
+    if (k < 2 && e->ev_set_ready[k]) cudaEventDestroy(e->ev_set_ready[k]);
+    if (k < 2 && e->ev_set_free[k]) cudaEventDestroy(e->ev_set_free[k]);
   }
   for (void* p : e->xch_opened) if (p) cudaIpcCloseMemHandle(p);
   if (e->xch) cudaFree(e->xch);
@@ -1050,6 +1060,11 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 16;
   int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
   if (U > 1 && (U & 1)) ++U;                         // a multi-step graph must leave the two-set parities where it found them
+  // NCCL with DDP's two buckets (large gradients): one step per graph, the form that has run on 4 and 8 GPUs since
+  // round 1 -- sixteen steps' worth of bucketed all-reduces in ONE capture failed inside ncclAllReduce ("unhandled
+  // cuda error") on 8 ranks at H = 4096
+  const bool nccl_step = e->gsize > 1 && !(e->p2p && !e->use_sgd && e->exchange != MDT_EXCHANGE_NCCL);
+  if (nccl_step && !e->one_bucket) U = 1;
   // graphs are specific to the source (its pointers are kernel arguments): a new source drops the cached ones
   const void* sig[4] = {src->x_pool, src->x_pool ? nullptr : (const void*)src->images_u8, src->indices,
                         reinterpret_cast<const void*>((uintptr_t)src->n_batches)};
@@ -1159,6 +1174,35 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
                         at.devicePointer != nullptr;
     cudaGetLastError();
     int slot = -1;
+    static const bool ahead_on = getenv("MDT_NO_PIPELINE") == nullptr;
+    const unsigned int last_pub = e->pub_expected;
+    const bool in_flight = last_pub != 0 && (unsigned int)(e->mailbox[last_pub & 63u] >> 32) != last_pub;
+    if (mapped && in_flight && ahead_on && e->opt_h2d_prefetch && e->copy_stream != nullptr && e->tc->simt_latent) {
+      // A step is still running: this step's prologue (pinned x, read in place over PCIe -> stage copy, x^T, bf16 copy)
+      // goes to the copy stream and into the input set the running step is NOT using; the step itself is then
+      // enqueued without a prologue kernel.  The transfer and the prologue hide behind the step in flight.
+      Tc05Plan* p = e->tc;
+      const int set = (e->host_set ^= 1);
+      if (e->set_used[set]) MDT_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_set_free[set], 0));
+      p->x_src = static_cast<const float*>(at.devicePointer);
+      int rc = tc05_prep(p, e->copy_stream, e->x_stage, batch, set, false, 0, "prep_xT_ahead", /*programmatic=*/false);
+      p->x_src = nullptr;
+      MDT_TRY(rc);
+      MDT_CUDA(cudaEventRecord(e->ev_set_ready[set], e->copy_stream));
+      MDT_CUDA(cudaStreamWaitEvent(e->stream, e->ev_set_ready[set], 0));
+      x = e->x_stage;
+      rc = stage_inputs(e, &x, batch, &eps, cudaMemcpyHostToDevice);      // eps only
+      if (rc == MDT_OK) {
+        p->pipelined = true; p->no_prefetch = true; p->xpar = set;
+        rc = train_step_device(e, x, batch, eps);
+        p->pipelined = false; p->no_prefetch = false;
+      }
+      MDT_TRY(rc);
+      MDT_CUDA(cudaEventRecord(e->ev_set_free[set], e->stream));
+      e->set_used[set] = true;
+      *ticket = e->pub_expected;
+      return MDT_OK;
+    }
     if (mapped) {
       e->tc->x_src = static_cast<const float*>(at.devicePointer);
       x = e->x_stage;                      // stage_inputs then only handles eps
@@ -1182,6 +1226,11 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
     if (slot >= 0) {                       // the slot is free again once this step (its prologue, really) has run
       MDT_CUDA(cudaEventRecord(e->ev_used[slot], e->stream));
       e->pre_used[slot] = true;
+    }
+    if (e->ev_set_free[0] != nullptr) {    // this step worked on input set 0
+      MDT_CUDA(cudaEventRecord(e->ev_set_free[0], e->stream));
+      e->set_used[0] = true;
+      e->host_set = 0;
     }
     *ticket = e->pub_expected;
     return MDT_OK;

@@ -3,14 +3,15 @@
 The reference varies only the number of epochs between its concurrent trials (``run(gid, batch_size, gid*2+1, group)``,
 ref:vae-hpo.py:202) and every rank writes into ``results-{rank}`` (ref:vae-hpo.py:107-118, 166-170), so the ranks of
 one group collide with nothing but also share nothing.  Here every trial group can get its own optimizer
-hyper-parameters, batch size, hidden width and epoch count from the environment, without touching the scripts:
+hyper-parameters and batch size from the environment, without touching the scripts:
 
-    MDT_HPO_LR=1e-3,3e-4  MDT_HPO_BETA1=0.9,0.8  MDT_HPO_BETA2=0.999  MDT_HPO_EPS=1e-8
-    MDT_HPO_BATCH=128,256  MDT_HPO_HIDDEN=400  MDT_HPO_EPOCHS=1,3
+    MDT_HPO_LR=1e-3,3e-4  MDT_HPO_BETA1=0.9,0.8  MDT_HPO_BETA2=0.999  MDT_HPO_EPS=1e-8  MDT_HPO_BATCH=128,256
 
 Each variable is a comma-separated list indexed by the trial's group id (wrapping around), so one value applies to all
-trials.  ``multidisttorch_b200.dropin`` consults :func:`trial_config` when it stands in for ``optim.Adam`` of a trial;
-callers of the engine API use it directly.  :func:`results_dir` gives one directory per (group, rank-in-group).
+trials.  ``multidisttorch_b200.dropin`` consults :func:`trial_config` when it stands in for ``optim.Adam`` of a trial
+(lr, betas, eps) and for the trial's training ``DataLoader`` (batch size); callers of the engine API use it directly.
+(Hidden width and epoch count are fixed by the script's own ``class VAE`` and ``for epoch`` loop, ref:vae-hpo.py:20-27,
+159: nothing outside the script can vary them, so they are not part of this surface.)
 """
 import os
 from dataclasses import dataclass
@@ -49,8 +50,6 @@ class TrialConfig:
     beta2: float = 0.999
     eps: float = 1e-8
     batch_size: int = 128
-    hidden: int = 400
-    epochs: int = 1
 
     @property
     def betas(self):
@@ -58,8 +57,7 @@ class TrialConfig:
 
 
 _FIELDS = {"lr": ("MDT_HPO_LR", float), "beta1": ("MDT_HPO_BETA1", float), "beta2": ("MDT_HPO_BETA2", float),
-           "eps": ("MDT_HPO_EPS", float), "batch_size": ("MDT_HPO_BATCH", int), "hidden": ("MDT_HPO_HIDDEN", int),
-           "epochs": ("MDT_HPO_EPOCHS", int)}
+           "eps": ("MDT_HPO_EPS", float), "batch_size": ("MDT_HPO_BATCH", int)}
 
 
 def _pick(raw, conv, gid, name):
@@ -84,8 +82,8 @@ def trial_config(group_id, env=None, **defaults):
     cfg = TrialConfig(group_id=gid, **kw)
     if not (cfg.lr > 0 and 0 <= cfg.beta1 < 1 and 0 <= cfg.beta2 < 1 and cfg.eps > 0):
         raise ValueError(f"invalid Adam hyper-parameters for trial {gid}: {cfg}")
-    if cfg.batch_size <= 0 or cfg.hidden <= 0 or cfg.hidden % 4 or cfg.epochs < 0:
-        raise ValueError(f"invalid shape hyper-parameters for trial {gid}: {cfg} (hidden must be a multiple of 4)")
+    if cfg.batch_size <= 0:
+        raise ValueError(f"invalid batch size for trial {gid}: {cfg}")
     return cfg
 
 
@@ -93,13 +91,3 @@ def overridden(env=None):
     """True if any MDT_HPO_* variable is set."""
     env = os.environ if env is None else env
     return any(name in env for name, _ in _FIELDS.values())
-
-
-def results_dir(group_id, group_rank=0, root=".", create=True):
-    """``results-g{group}`` for group-rank 0, ``results-g{group}-r{rank}`` for the others: one directory per trial
-    member instead of the reference's world-rank keyed ``results-{rank}``."""
-    name = f"results-g{int(group_id)}" + ("" if int(group_rank) == 0 else f"-r{int(group_rank)}")
-    path = os.path.join(root, name)
-    if create:
-        os.makedirs(path, exist_ok=True)
-    return path

@@ -29,8 +29,21 @@ def run_world(world, tag, mode, extra_env=None):
         env.update(extra_env or {})
         procs.append(subprocess.Popen([sys.executable, os.path.join(HERE, "_gpu_ddp_worker.py"), tag, mode, out], env=env,
                                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
-    logs = [p.communicate(timeout=600)[0] for p in procs]
-    assert [p.returncode for p in procs] == [0] * world, "\n".join(l[-1500:] for l in logs)
+    # fail fast: the moment one rank exits non-zero its peers (blocked in a collective or a barrier) are killed, and the
+    # whole world gets 240 s -- a hang must not hold N GPUs for long
+    import time
+    t0 = time.time()
+    while time.time() - t0 < 240:
+        codes = [p.poll() for p in procs]
+        if all(c is not None for c in codes) or any(c not in (None, 0) for c in codes):
+            break
+        time.sleep(0.5)
+    time.sleep(1.0)
+    for p in procs:
+        if p.poll() is None:
+            p.kill()
+    logs = [p.communicate()[0] for p in procs]
+    assert [p.returncode for p in procs] == [0] * world, "\n".join(f"--- rank {r} (rc {p.returncode})\n{l[-1500:]}" for r, (p, l) in enumerate(zip(procs, logs)))
 
 
 def need(n):

@@ -52,7 +52,18 @@ def run_script(tmp_path, world, ngroups, dropin):
         procs.append(subprocess.Popen([sys.executable, "-c", RUNNER, SCRIPT, "--ngroups", str(ngroups), "--epochs", "1",
                                        "--batch-size", "128"], env=env, cwd=str(tmp_path), stdout=subprocess.PIPE,
                                       stderr=subprocess.STDOUT, text=True))
-    logs = [p.communicate(timeout=900)[0] for p in procs]
+    import time
+    t0 = time.time()
+    while time.time() - t0 < 300:
+        codes = [p.poll() for p in procs]
+        if all(c is not None for c in codes) or any(c not in (None, 0) for c in codes):
+            break
+        time.sleep(0.5)
+    time.sleep(1.0)
+    for p in procs:
+        if p.poll() is None:
+            p.kill()
+    logs = [p.communicate()[0] for p in procs]
     assert [p.returncode for p in procs] == [0] * world, "\n".join(l[-3000:] for l in logs)
     return logs
 
@@ -70,6 +81,7 @@ def test_unchanged_vae_hpo_through_the_dropin_matches_plain_torch_cuda(tmp_path,
     plain = run_script(tmp_path, world, 1, dropin=False)
     ours = run_script(tmp_path, world, 1, dropin=True)
     assert "-> B200 engine" in ours[0], ours[0][-2000:]
+    assert "device-resident loader" in ours[0], ours[0][-2000:]      # the script's MNIST DataLoaders were taken over too
     if world > 1:
         assert "gradient exchange: peer memory" in ours[0] or "gradient exchange: NCCL" in ours[0]
     a, b = losses_of(plain[0]), losses_of(ours[0])
