@@ -294,7 +294,8 @@ def ddp_parity(ctx, args, gemm_modes):
     if ctx.world >= 8:
         cases += [("ddp_1x8_b16", 8), ("ddp_2x4_b128", 8)]
     # stated tolerances (relative): loss / parameters after the golden's steps
-    TOL = {"tf32x3": (1e-5, 5e-4), "bf16": (2e-3, 1e-1)}
+    # measured on 2 x B200 (1x2 golden, 5 steps): tf32x3 loss 1.1e-7 / parameters 2.0e-7, bf16 1.7e-5 / 1.4e-2
+    TOL = {"tf32x3": (5e-6, 2e-5), "bf16": (6e-4, 1e-1)}
     report, ok = {}, True
     for tag, w in cases:
         g = dict(np.load(os.path.join(ROOT, "tests", "golden", f"{tag}.npz"), allow_pickle=False))

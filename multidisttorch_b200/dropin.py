@@ -28,6 +28,7 @@ import os
 
 import torch
 import torch.distributed as dist
+import torch.utils.data as _tud
 from torch import nn
 
 from .engine import REF_NAMES, VAEEngine
@@ -392,9 +393,8 @@ def install():
     ddp, adam = _make_shims(_ORIG["ddp"], _ORIG["adam"])
     torch.nn.parallel.DistributedDataParallel = ddp
     torch.optim.Adam = adam
-    import torch.utils.data
-    _ORIG["loader"] = torch.utils.data.DataLoader
-    torch.utils.data.DataLoader = _make_loader_shim(_ORIG["loader"])
+    _ORIG["loader"] = _tud.DataLoader
+    _tud.DataLoader = _make_loader_shim(_ORIG["loader"])
     return True
 
 
@@ -404,5 +404,4 @@ def uninstall():
     torch.nn.parallel.DistributedDataParallel = _ORIG.pop("ddp")
     torch.optim.Adam = _ORIG.pop("adam")
     if "loader" in _ORIG:
-        import torch.utils.data
-        torch.utils.data.DataLoader = _ORIG.pop("loader")
+        _tud.DataLoader = _ORIG.pop("loader")

@@ -23,8 +23,11 @@ def _write_idx(path, arr):
 
 def test_device_batches_equal_dataloader_batches_and_training_matches(tmp_path):
     from torchvision import datasets, transforms
+    from multidisttorch_b200 import dropin
     from multidisttorch_b200.data import DeviceDataset
     from multidisttorch_b200.engine import VAEEngine
+    dropin.uninstall()          # this test compares against torch's OWN DataLoader (an earlier `import utils` may have
+                                # put the device-resident loader in its place)
 
     raw = tmp_path / "MNIST" / "raw"
     raw.mkdir(parents=True)
