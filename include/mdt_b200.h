@@ -204,6 +204,15 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
                                uint32_t* ticket);
 int mdt_train_step_host_wait(mdt_engine* e, uint32_t ticket, float* loss_host);
 
+/* A chunk of 1..16 consecutive host batches in one call: x_host is [n_steps][batch][in_dim] (pinned memory makes the
+ * copy asynchronous).  The chunk is DMA'd into one half of a device ring on the copy stream -- behind the chunk that is
+ * still training -- and its steps run as one CUDA graph; every step publishes its loss to the mailbox as usual.
+ * *first_ticket is the ticket of the chunk's first step, the others follow consecutively (wait for each with
+ * mdt_train_step_host_wait).  What a DataLoader with a prefetch depth of one chunk gives ref:vae-hpo.py:64-73.
+ * x_host must stay untouched until the chunk's first ticket has been waited for.  At most two chunks in flight.
+ * The first call allocates the ring (2 x 16 x max_batch x in_dim floats). */
+int mdt_train_steps_host_submit(mdt_engine* e, const float* x_host, int batch, int n_steps, uint32_t* first_ticket);
+
 /* Forward + loss only (the eval loop), ref:vae-hpo.py:101-105. */
 int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out,
                   float* recon);

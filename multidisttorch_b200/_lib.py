@@ -58,6 +58,7 @@ _PROTOS = {
     "mdt_engine_set_sm_share": (C.c_int, [_P, C.c_int]),
     "mdt_train_step_host_submit": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_uint32)]),
     "mdt_train_step_host_wait": (C.c_int, [_P, C.c_uint32, C.POINTER(C.c_float)]),
+    "mdt_train_steps_host_submit": (C.c_int, [_P, _P, C.c_int, C.c_int, C.POINTER(C.c_uint32)]),
     "mdt_eval_step": (C.c_int, [_P, _P, C.c_int, _P, _P, _P]),
     "mdt_decode": (C.c_int, [_P, _P, C.c_int, _P]),
     "mdt_engine_workspace": (C.c_int, [_P, C.c_char_p, C.POINTER(_P), C.POINTER(C.c_int)]),

@@ -139,6 +139,13 @@ struct mdt_engine {
   unsigned int pre_next = 0;
   // host-buffer steps submitted while a step is in flight: the prologue of the new step (pinned x -> input set) runs
   // on the copy stream, alternating between the two input sets of the tensor-core plan
+  // mdt_train_steps_host_submit: chunks of up to kHostChunk host batches land in the two halves of a device ring
+  static constexpr int kHostChunk = 16;
+  float* x_ring = nullptr;
+  cudaEvent_t ev_ring_copied[2] = {}, ev_ring_free[2] = {};
+  bool ring_used[2] = {};
+  unsigned int ring_next = 0;
+  bool tail_no_prefetch = false;                    // the last step of the current mdt_train_steps call fetches nothing
   cudaEvent_t ev_set_ready[2] = {}, ev_set_free[2] = {};
   bool set_used[2] = {};
   int host_set = 0;
@@ -568,7 +575,7 @@ int enqueue_fwd_loss_bwd(mdt_engine* e, const float* x, int B, const float* eps)
 }
 
 // `steps` > 1 (mdt_train_steps only): that many consecutive steps in ONE graph.
-int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, int steps = 1) {
+int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, int steps = 1, bool tail_no_prefetch = false) {
   e->last_B = B;
   if (B == 0 && e->gsize > 1)   // the peers of a group would wait for this rank's gradient: refuse instead of hanging them
     return set_error(MDT_ERR_INVALID, "an empty batch on one rank of a %d-rank trial group would stall its peers", e->gsize);
@@ -583,9 +590,15 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
   struct ParityAfter {       // a replayed graph does not run the enqueue code that flips the parities: set them here
     mdt_engine* e; int x, w;
     ~ParityAfter() { if (e->tc) { e->tc->xpar = x; e->tc->w3par = w; e->tc->prefetch_pending = false; } }
-  } parity_after{e, piped && !e->tc->no_prefetch ? (x0 ^ (steps & 1)) : (piped ? x0 : 0), w3_flips ? (w0 ^ (steps & 1)) : w0};
+  } parity_after{e, piped && !e->tc->no_prefetch ? (x0 ^ ((steps - (tail_no_prefetch ? 1 : 0)) & 1)) : (piped ? x0 : 0),
+                 w3_flips ? (w0 ^ (steps & 1)) : w0};
   const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8) | (x0 << 20) | (w0 << 21) |
-                 ((piped ? 1 : 0) << 22) | ((piped && e->tc->no_prefetch ? 1 : 0) << 23);
+                 ((piped ? 1 : 0) << 22) | ((piped && e->tc->no_prefetch ? 1 : 0) << 23) | ((piped && tail_no_prefetch ? 1 : 0) << 24);
+  struct TailGuard {         // single-step graphs: the step itself is the tail
+    Tc05Plan* p; bool saved, on;
+    ~TailGuard() { if (on) p->no_prefetch = saved; }
+  } tail_guard{e->tc, e->tc ? e->tc->no_prefetch : false, piped && tail_no_prefetch && steps == 1};
+  if (tail_guard.on) e->tc->no_prefetch = true;
   if (e->tc) e->pub_expected = (e->pub_expected + (unsigned)steps) & 0x7fffffffu;   // every tensor-core training step publishes
                                                                          // (sequence, loss) once: publish_loss()
   if (e->tc && !e->sourced) e->cursor_expected = -1;                     // ... and moves the device-side batch cursor
@@ -610,7 +623,14 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
       return enqueue_adam(e, gscale, true);
     };
     return run_cached(e, kbase + 9, B, fl, [&]() -> int {
-      for (int i = 0; i < steps; ++i) MDT_TRY(one());
+      for (int i = 0; i < steps; ++i) {
+        const bool tail = piped && tail_no_prefetch && i == steps - 1;
+        const bool saved = e->tc->no_prefetch;
+        if (tail) e->tc->no_prefetch = true;
+        const int rc = one();
+        e->tc->no_prefetch = saved;
+        MDT_TRY(rc);
+      }
       return MDT_OK;
     });
   }
@@ -781,6 +801,11 @@ void mdt_engine_destroy(mdt_engine* e) {
     if (k < 2 && e->ev_set_free[k]) cudaEventDestroy(e->ev_set_free[k]);
   }
   for (void* p : e->xch_opened) if (p) cudaIpcCloseMemHandle(p);
+  if (e->x_ring) cudaFree(e->x_ring);
+  for (int k = 0; k < 2; ++k) {
+    if (e->ev_ring_copied[k]) cudaEventDestroy(e->ev_ring_copied[k]);
+    if (e->ev_ring_free[k]) cudaEventDestroy(e->ev_ring_free[k]);
+  }
   if (e->xch) cudaFree(e->xch);
   if (e->slab) cudaFree(e->slab);
   if (e->loss_pinned) cudaFreeHost(e->loss_pinned);
@@ -1095,7 +1120,7 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   e->sourced = true;
   for (int done = 0; done < n_steps && rc == MDT_OK;) {
     const int u = (n_steps - done >= U) ? U : 1;
-    rc = train_step_device(e, e->x_stage, batch, nullptr, u);
+    rc = train_step_device(e, e->x_stage, batch, nullptr, u, e->tail_no_prefetch && done + u == n_steps);
     done += u;
   }
   e->sourced = false;
@@ -1104,7 +1129,7 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   if (rc != MDT_OK) e->primed = false;
   MDT_TRY(rc);
   e->cursor_expected = first_batch + n_steps;
-  e->primed = piped;
+  e->primed = piped && !e->tail_no_prefetch;
   e->primed_cursor = first_batch + n_steps;
   if (losses_out != nullptr) {
     const unsigned int lo = seq0 & (kLossHist - 1u);
@@ -1284,6 +1309,43 @@ int mdt_train_step_host(mdt_engine* e, const float* x_host, int batch, const flo
   uint32_t ticket = 0;
   MDT_TRY(mdt_train_step_host_submit(e, x_host, batch, eps_host_or_null, &ticket));
   return mdt_train_step_host_wait(e, ticket, loss_host);
+}
+
+int mdt_train_steps_host_submit(mdt_engine* e, const float* x_host, int batch, int n_steps, uint32_t* first_ticket) {
+  MDT_TRY(check_batch(e, batch));
+  MDT_CHECK(x_host && first_ticket && batch > 0, "bad argument");
+  MDT_CHECK(n_steps >= 1 && n_steps <= mdt_engine::kHostChunk, "n_steps %d outside [1, %d]", n_steps, mdt_engine::kHostChunk);
+  if (e->tc == nullptr || e->mailbox == nullptr || e->copy_stream == nullptr)
+    return set_error(MDT_ERR_UNSUPPORTED, "mdt_train_steps_host_submit needs a tensor-core gemm_mode (its losses come back through the mailbox)");
+  constexpr int C = mdt_engine::kHostChunk;
+  if (e->x_ring == nullptr) {     // first use: the ring (2 x 16 batches of max_batch rows) and its events
+    MDT_CUDA(cudaMalloc(&e->x_ring, (size_t)2 * C * e->Bmax * e->D * sizeof(float)));
+    for (int k = 0; k < 2; ++k) {
+      MDT_CUDA(cudaEventCreateWithFlags(&e->ev_ring_copied[k], cudaEventDisableTiming));
+      MDT_CUDA(cudaEventCreateWithFlags(&e->ev_ring_free[k], cudaEventDisableTiming));
+    }
+  }
+  const int half = (int)(e->ring_next++ & 1u);
+  const size_t bstride = (size_t)batch * e->D;
+  float* dst = e->x_ring + (size_t)half * C * bstride;
+  if (e->ring_used[half]) MDT_CUDA(cudaStreamWaitEvent(e->copy_stream, e->ev_ring_free[half], 0));
+  MDT_CUDA(cudaMemcpyAsync(dst, x_host, (size_t)n_steps * bstride * sizeof(float), cudaMemcpyHostToDevice, e->copy_stream));
+  MDT_CUDA(cudaEventRecord(e->ev_ring_copied[half], e->copy_stream));
+  MDT_CUDA(cudaStreamWaitEvent(e->stream, e->ev_ring_copied[half], 0));
+  // the ring is one pool of 2 x 16 batches of this batch size; the chunk's last step fetches nothing (what follows it
+  // in the ring may still be on its way over PCIe)
+  mdt_batch_source src{};
+  src.x_pool = e->x_ring;
+  src.n_batches = 2 * C;
+  const unsigned int t0 = (e->pub_expected + 1u) & 0x7fffffffu;
+  e->tail_no_prefetch = true;
+  const int rc = mdt_train_steps(e, &src, batch, (int64_t)half * C, n_steps, nullptr);
+  e->tail_no_prefetch = false;
+  MDT_TRY(rc);
+  MDT_CUDA(cudaEventRecord(e->ev_ring_free[half], e->stream));
+  e->ring_used[half] = true;
+  *first_ticket = t0;
+  return MDT_OK;
 }
 
 int mdt_eval_step(mdt_engine* e, const float* x, int batch, const float* eps_or_null, float* loss_out, float* recon) {

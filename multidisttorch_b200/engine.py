@@ -267,6 +267,17 @@ class VAEEngine:
         self._inflight[t.value] = (x, eps_host)          # keep the buffers alive while the device may read them
         return t.value
 
+    def submit_host_chunk(self, x_host):
+        """mdt_train_steps_host_submit: ``x_host`` = [n, B, D] host batches (n <= 16, pinned for an asynchronous copy);
+        returns the tickets of the n steps.  Keep ``x_host`` untouched until the first ticket has been waited for."""
+        n, B = x_host.shape[0], x_host.shape[1]
+        assert x_host.dtype == torch.float32 and x_host.is_contiguous() and x_host.numel() == n * B * self.D
+        t = C.c_uint32()
+        check(self.lib.mdt_train_steps_host_submit(self._h, _ptr(x_host), B, n, C.byref(t)))
+        self._inflight = getattr(self, "_inflight", {})
+        self._inflight[t.value] = (x_host, None)
+        return [(t.value + i) & 0x7fffffff for i in range(n)]
+
     def wait_host(self, ticket):
         """Second half: the loss of the step ``submit_host`` returned ``ticket`` for."""
         out = C.c_float()

@@ -100,3 +100,24 @@ def test_sgd_steps_match_the_oracle(E, mode, kw):
             assert rel_l2(m[k], tr.m[k]) < 2e-4, (k, rel_l2(m[k], tr.m[k]))
     assert eng.state()[0] == 4
     eng.close()
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+def test_host_chunks_equal_synchronous_host_steps(E, mode):
+    """mdt_train_steps_host_submit: chunks of host batches (ragged last chunk, two chunks in flight) give, step for step,
+    the losses and final parameters of the synchronous mdt_train_step_host loop."""
+    B, n = 48, 41
+    xs = torch.rand(n, B, 784, generator=torch.Generator().manual_seed(8)).pin_memory()
+    a, b = pair(E, mode, B)
+    want = [a.train_step_host(xs[i]) for i in range(n)]
+    tickets = []
+    got = []
+    for lo in range(0, n, 16):
+        tickets.append(b.submit_host_chunk(xs[lo:lo + 16]))
+        if len(tickets) == 2:                           # keep one chunk in flight ahead
+            got += [b.wait_host(t) for t in tickets.pop(0)]
+    for ch in tickets:
+        got += [b.wait_host(t) for t in ch]
+    assert got == want
+    assert torch.equal(a.params, b.params) and a.state() == b.state()
+    a.close(); b.close()
