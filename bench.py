@@ -427,7 +427,7 @@ def run_own(args):
     torch, dist = ctx.torch, ctx.dist
     rank, world, device = ctx.rank, ctx.world, ctx.device
     from multidisttorch_b200 import synth
-    from multidisttorch_b200.engine import VAEEngine, train_step_many
+    from multidisttorch_b200.engine import TrialGroup, VAEEngine, train_step_many
 
     B, H, K = args.batch, args.hidden, args.steps
     W = max(args.warmup, 3)
@@ -585,9 +585,11 @@ def run_own(args):
             modes[m] = round(world * B / (msm * 1e-3), 1)
             em.close()
     # ---- SURVEY section 8f-3 (next row): several independent trials per GPU
-    multi_trial = None
+    multi_trial, multi_trial_grouped = None, None
     if world == 1 and not args.no_modes:
         multi_trial = {"1": round(value, 1)}
+        multi_trial_grouped = {"1": round(value, 1),
+                               "what": "T trials in lock-step, one launch per layer over a table of the trials' arguments (mdt_group_train_steps)"}
         for T in (2, 4, 8):
             engs = [new_engine(args.gemm_mode, seed=2000 + t) for t in range(T)]
             Km = max(short, MIN_TIMED_STEPS)
@@ -602,6 +604,25 @@ def run_own(args):
                 torch.cuda.synchronize()
                 ts.append(time.perf_counter() - t0)
             multi_trial[str(T)] = round(T * B * Km / statistics.median(ts), 1)
+
+            def grouped():
+                # the same T trials with ONE launch per layer (mdt_group_train_steps), 16 steps per graph
+                grp = TrialGroup(engs)
+                try:
+                    grp.train_steps([pool] * T, 0, 2 * W)
+                    tg = []
+                    for r_ in range(3):
+                        torch.cuda.synchronize()
+                        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                        ev0.record(engs[0].stream)
+                        grp.train_steps([pool] * T, (2 * W + r_ * Km) % POOL_BATCHES, Km)
+                        ev1.record(engs[0].stream)
+                        engs[0].synchronize()
+                        tg.append(ev0.elapsed_time(ev1) * 1e-3)
+                    return round(T * B * Km / statistics.median(tg), 1)
+                finally:
+                    grp.close()
+            multi_trial_grouped[str(T)] = section(f"trials_per_gpu_grouped/{T}", grouped)
             for e_ in engs:
                 e_.close()
 
@@ -697,7 +718,7 @@ def run_own(args):
             "gpu_launches_per_step": round(total_launches / (world * R * n_region), 2), "roofline": roofline,
             "cpu_baseline": cpu_baseline, "ddp_parity": parity, "layouts": layouts, "layouts_bf16": layouts_bf16,
             "exchanges": exchanges, "allreduce": allreduce, "config5": config5, "modes": modes,
-            "trials_per_gpu": multi_trial, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
+            "trials_per_gpu": multi_trial, "trials_per_gpu_grouped": multi_trial_grouped, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
             "kernels": kernels,
         }
         watchdog.cancel()

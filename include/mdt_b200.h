@@ -184,6 +184,19 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
  * mdt_train_step on each engine; it exists to take the per-call host overhead out of the HPO driver's loop.
  * Replaces: nothing in the reference (it runs one trial per rank, ref:vae-hpo.py:200-202). */
 int mdt_train_step_many(mdt_engine* const* engines, const float* const* xs, int n_trials, int batch);
+/* The same for whole training loops, with ONE launch per layer for all trials (SURVEY section 8f-3 as specified): a
+ * group of T single-rank Adam trials of identical shape on one GPU is stepped in lock-step; every kernel of the step
+ * runs once over a table of the T trials' tensor maps and arguments (grid.y resp. grid.x = trial x tiles), inside CUDA
+ * graphs of 16 steps on trial 0's streams.  srcs[t] is trial t's device-resident batch source (all with the same
+ * n_batches); step i of the call trains every trial on its batch (first_batch + i) % n_batches.  Each trial keeps its
+ * own parameters, optimizer state, Philox stream, loss ring and mailbox; results are bit-identical to stepping the
+ * trial alone with mdt_engine_set_sm_share(T).  Small-model regime only (hidden < 2048, max_batch <= 512).
+ * Replaces: the per-group loop of ref:vae-hpo.py:200-202 for trials that share a GPU. */
+typedef struct mdt_group mdt_group;
+int mdt_group_create(mdt_engine* const* engines, int n_trials, mdt_group** out);
+int mdt_group_train_steps(mdt_group* g, const mdt_batch_source* srcs, int batch, int64_t first_batch, int n_steps);
+void mdt_group_destroy(mdt_group* g);
+
 /* (new, no reference counterpart) Size this engine's kernels -- K-split counts, CTAs per launch -- for 1/n_sharing of
  * the GPU's SMs, for callers that run several trials on one GPU themselves (own threads / streams).  Default 1.
  * mdt_train_step_many applies max(n_trials, this value) for the duration of its call. */

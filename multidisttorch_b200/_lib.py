@@ -54,6 +54,9 @@ _PROTOS = {
     "mdt_adam_step": (C.c_int, [_P, C.c_float]),
     "mdt_train_step": (C.c_int, [_P, _P, C.c_int, _P, _P]),
     "mdt_train_step_many": (C.c_int, [C.POINTER(_P), C.POINTER(_P), C.c_int, C.c_int]),
+    "mdt_group_create": (C.c_int, [C.POINTER(_P), C.c_int, C.POINTER(_P)]),
+    "mdt_group_train_steps": (C.c_int, [_P, C.POINTER(mdt_batch_source), C.c_int, C.c_int64, C.c_int]),
+    "mdt_group_destroy": (None, [_P]),
     "mdt_train_step_host": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_float)]),
     "mdt_engine_set_sm_share": (C.c_int, [_P, C.c_int]),
     "mdt_train_step_host_submit": (C.c_int, [_P, _P, C.c_int, _P, C.POINTER(C.c_uint32)]),

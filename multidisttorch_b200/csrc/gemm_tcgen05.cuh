@@ -21,6 +21,7 @@
 #include <cuda_bf16.h>
 
 #include <map>
+#include <vector>
 
 #include "common.cuh"
 #include "latent.cuh"
@@ -430,7 +431,7 @@ __device__ __forceinline__ void tc05_prefetch_adam(const Tc05Epi& ep, int m0, in
 
 template <int BN, int kEpi>
 __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int ldt, int m0, int n0, int M, int N, int et,
-                                              float* red, const Tc05Pre<BN>& pre, int it_rank, int it_ns) {
+                                              float* red, const Tc05Pre<BN>& pre, int it_rank, int it_ns, int by) {
   // it_rank / it_ns: in a split-K cluster the tile's epilogue passes (RPP rows each) are shared out among the CTAs --
   // this CTA holds the summed rows of, and runs, the passes i with i % it_ns == it_rank.  (0, 1) = the whole tile.
   const int lane = et & 31, ew = et >> 5;
@@ -605,7 +606,7 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
     // of the partials is done by the Adam kernel (finalize_loss), after a kernel boundary -- no fence / ticket here.
     // A tile owns gridDim.z consecutive slots (one per split); without the cluster exchange only slot 0 is used.
     if (et == 0) {
-      float* slot = ep.bce_partials + (size_t)(blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z;
+      float* slot = ep.bce_partials + (size_t)(by * gridDim.x + blockIdx.x) * gridDim.z;
       slot[it_ns == 1 ? 0 : it_rank] = ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
       if (it_ns == 1)
         for (unsigned z = 1; z < gridDim.z; ++z) slot[z] = 0.f;
@@ -709,10 +710,10 @@ __device__ __forceinline__ void tc05_epilogue(const Tc05Epi& ep, float* T, int l
 // ------------------------------------------------------------------------------------------------
 // the kernel
 // ------------------------------------------------------------------------------------------------
+// `by`: index of the 128-row tile (blockIdx.y, or blockIdx.y modulo the tiles of one trial in the grouped launch)
 template <int BN, bool kSplit, int kEpi>
-__global__ void __launch_bounds__(tc_threads(kSplit), 1)
-tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
-                 int K, Tc05Epi ep) {
+__device__ __forceinline__ void tc05_gemm_body(const CUtensorMap* const tmap_a_p, const CUtensorMap* const tmap_b_p, int M, int N,
+                                               int K, const Tc05Epi& ep, const int by) {
   using S = Tc05Smem<BN, kSplit>;
   // SWIZZLE_128B needs 1024-byte aligned tiles.  The kernel has no static shared memory, so the dynamic window
   // starts at offset 0; keeping `smem` a plain shared-space array (no integer re-alignment) lets the compiler
@@ -721,7 +722,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const uint32_t smem_base = ptx::smem_u32(smem);
   if ((smem_base & 1023u) != 0) __trap();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int n0 = blockIdx.x * BN, m0 = blockIdx.y * kTcBM;
+  const int n0 = blockIdx.x * BN, m0 = by * kTcBM;
   // split-K: gridDim.z CTAs share one output tile, each streaming a contiguous range of k-blocks
   // elements of K per k-block: one 128-byte swizzle row = 32 fp32 (tf32 kinds) or 64 bf16 (kind::f16)
   const int kbk = (!kSplit && ep.bf16) ? 2 * kTcBK : kTcBK;
@@ -729,7 +730,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int kb_per_split = (total_kb + (int)gridDim.z - 1) / (int)gridDim.z;
   const int kb0 = (int)blockIdx.z * kb_per_split;
   const int num_kb = min(kb_per_split, total_kb - kb0);      // >= 1 (the host picks gridDim.z accordingly)
-  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == (ep.cluster ? 0 : gridDim.z - 1);
+  const bool dbg = ep.dbg != nullptr && blockIdx.x == 0 && by == 0 && blockIdx.z == (ep.cluster ? 0 : gridDim.z - 1);
 #define TC_STAMP(i) do { if (dbg) ep.dbg[i] = clock64(); } while (0)
   if (threadIdx.x == 0) {
     TC_STAMP(0);
@@ -750,8 +751,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
   const int kTmemCols = (kSplit && ep.a_tmem) ? 512 : kTmemAccCols;   // power of two >= 2 BN + 4 * 64
 
   if (threadIdx.x == 0) {
-    ptx::prefetch_tmap(&tmap_a);
-    ptx::prefetch_tmap(&tmap_b);
+    ptx::prefetch_tmap(tmap_a_p);
+    ptx::prefetch_tmap(tmap_b_p);
     for (int s = 0; s < S::STAGES; ++s) {
       ptx::mbar_init(bar_full + 8 * s, 1);
       ptx::mbar_init(bar_split + 8 * s, kTcEpiThreads / 32);   // one arrival per splitter warp
@@ -781,8 +782,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     for (int kb = 0; kb < pre_kb; ++kb) {
       const uint32_t sa = smem_base + kb * S::STAGE;
       ptx::mbar_expect_tx(bar_full + 8 * kb, S::HB);
-      if (ep.pre_a) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kbk, m0, bar_full + 8 * kb);
-      if (ep.pre_b) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kbk, n0, bar_full + 8 * kb);
+      if (ep.pre_a) ptx::tma_load_2d(sa, tmap_a_p, (kb0 + kb) * kbk, m0, bar_full + 8 * kb);
+      if (ep.pre_b) ptx::tma_load_2d(sa + S::A_BYTES, tmap_b_p, (kb0 + kb) * kbk, n0, bar_full + 8 * kb);
     }
   }
   Tc05Pre<BN> pre;
@@ -808,8 +809,8 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           ptx::mbar_wait(bar_empty + 8 * s, ph ^ 1);
           ptx::mbar_expect_tx(bar_full + 8 * s, S::HB);
         }
-        if (!(early && ep.pre_a)) ptx::tma_load_2d(sa, &tmap_a, (kb0 + kb) * kbk, m0, bar_full + 8 * s);
-        if (!(early && ep.pre_b)) ptx::tma_load_2d(sa + S::A_BYTES, &tmap_b, (kb0 + kb) * kbk, n0, bar_full + 8 * s);
+        if (!(early && ep.pre_a)) ptx::tma_load_2d(sa, tmap_a_p, (kb0 + kb) * kbk, m0, bar_full + 8 * s);
+        if (!(early && ep.pre_b)) ptx::tma_load_2d(sa + S::A_BYTES, tmap_b_p, (kb0 + kb) * kbk, n0, bar_full + 8 * s);
       }
       TC_STAMP(2);
     }
@@ -1064,7 +1065,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       constexpr int ITERS_E = F4 / kTcEpiThreads;
       const uint32_t ns = gridDim.z, rank = blockIdx.z;
       ptx::cluster_sync_all();
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && by == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
       if (kDist) {
         for (int i = (int)rank; i < ITERS_E; i += (int)ns) {
           const int f = i * kTcEpiThreads + et;
@@ -1096,14 +1097,14 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
         }
       }
       ptx::cluster_sync_all();
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && by == 0 && rank == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
       run_epilogue = kDist || rank == 0;
     } else if (gridDim.z > 1) {
       // Deterministic split-K reduction: every split parks its partial tile in the workspace; the CTA that takes the
       // last ticket of the tile adds the partials in split order (independent of arrival order) and runs the epilogue.
       constexpr int F4 = kTcBM * BN / 4;                       // float4 per tile
       constexpr int PER = (F4 + kTcEpiThreads - 1) / kTcEpiThreads;
-      const int tile_id = blockIdx.y * gridDim.x + blockIdx.x;
+      const int tile_id = by * gridDim.x + blockIdx.x;
       const int nsplit = gridDim.z;
       float4* const ws = reinterpret_cast<float4*>(ep.ws) + (size_t)tile_id * nsplit * F4;
       float4* const mine = ws + (size_t)blockIdx.z * F4;
@@ -1124,7 +1125,7 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
       ptx::bar_sync_epi();
       run_epilogue = red[8] != 0.f;
       if (run_epilogue) {
-        if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
+        if (ep.dbg && et == 0 && blockIdx.x == 0 && by == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[9] = (long long)g; }
         float4 acc[PER];
 #pragma unroll
         for (int i = 0; i < PER; ++i) acc[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -1151,12 +1152,12 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
           if (f < F4) *reinterpret_cast<float4*>(T + (f / (BN / 4)) * S::TILE_LD + (f % (BN / 4)) * 4) = acc[i];
         }
         ptx::bar_sync_epi();
-        if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
+        if (ep.dbg && et == 0 && blockIdx.x == 0 && by == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[10] = (long long)g; }
       }
     }
     if (run_epilogue) {
-      tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre, it_rank, it_ns);
-      if (ep.dbg && et == 0 && blockIdx.x == 0 && blockIdx.y == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[11] = (long long)g; }
+      tc05_epilogue<BN, kEpi>(ep, T, S::TILE_LD, m0, n0, M, N, et, red, pre, it_rank, it_ns, by);
+      if (ep.dbg && et == 0 && blockIdx.x == 0 && by == 0) { unsigned long long g; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(g)); ep.dbg[11] = (long long)g; }
     }
     if (et == 0) TC_STAMP(7);
   }
@@ -1178,6 +1179,37 @@ tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_consta
     }
   }
 #undef TC_STAMP
+}
+
+template <int BN, bool kSplit, int kEpi>
+__global__ void __launch_bounds__(tc_threads(kSplit), 1)
+tc05_gemm_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, int M, int N,
+                 int K, Tc05Epi ep) {
+  tc05_gemm_body<BN, kSplit, kEpi>(&tmap_a, &tmap_b, M, N, K, ep, (int)blockIdx.y);
+}
+
+// Grouped launch: the same GEMM of T independent trials in ONE launch.  blockIdx.y = trial * tiles_m + tile;
+// tensor maps and epilogue arguments of trial t come from table[t] in global memory (written by the host when the
+// group's graph is built); the epilogue arguments are copied into shared memory once per CTA.
+struct alignas(64) Tc05GroupEntry {
+  CUtensorMap a, b;
+  Tc05Epi ep;
+};
+constexpr int kTcGroupEpiOff = 512;     // byte offset of the Tc05Epi copy behind the barrier block (1280 bytes are reserved there)
+static_assert(sizeof(Tc05Epi) % 4 == 0 && kTcGroupEpiOff + sizeof(Tc05Epi) <= 256 + 1024, "Tc05Epi copy must fit behind the barriers");
+
+template <int BN, bool kSplit, int kEpi>
+__global__ void __launch_bounds__(tc_threads(kSplit), 1)
+tc05_gemm_group_kernel(const Tc05GroupEntry* __restrict__ table, int tiles_m, int M, int N, int K) {
+  using S = Tc05Smem<BN, kSplit>;
+  extern __shared__ __align__(1024) uint8_t smem[];
+  const int trial = (int)blockIdx.y / tiles_m, by = (int)blockIdx.y - trial * tiles_m;
+  const Tc05GroupEntry* const en = table + trial;
+  uint32_t* const dst = reinterpret_cast<uint32_t*>(smem + S::BAR_OFF + kTcGroupEpiOff);
+  const uint32_t* const src = reinterpret_cast<const uint32_t*>(&en->ep);
+  for (int i = threadIdx.x; i < (int)(sizeof(Tc05Epi) / 4); i += blockDim.x) dst[i] = src[i];
+  __syncthreads();
+  tc05_gemm_body<BN, kSplit, kEpi>(&en->a, &en->b, M, N, K, *reinterpret_cast<const Tc05Epi*>(dst), by);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1272,13 +1304,13 @@ struct PrepArgs {
   int cursor_add;      // 1: this launch fetches the NEXT step's batch while the current step runs (see Tc05Plan::pipelined)
 };
 
-__global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
+__device__ __forceinline__ void prep_body(const PrepArgs& a, const int bx, const int gx) {
   pdl_wait();
   pdl_trigger();
-  if ((int)blockIdx.x < a.tr_blocks) {
+  if (bx < a.tr_blocks) {
     __shared__ float t[32][33];
     TrJob job = a.tr.job[0];
-    const int tile = (int)blockIdx.x;
+    const int tile = bx;
     const int r0 = (tile / job.tiles_c) * 32, c0 = (tile % job.tiles_c) * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const bool sourced = a.pool != nullptr || a.images != nullptr;
@@ -1309,8 +1341,8 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
     return;
   }
   const unsigned long long seed = a.st->philox_seed, offset = a.st->philox_offset;
-  const int nb = (int)gridDim.x - a.tr_blocks;
-  for (long long i = (long long)((int)blockIdx.x - a.tr_blocks) * blockDim.x + threadIdx.x; i < a.n_eps;
+  const int nb = gx - a.tr_blocks;
+  for (long long i = (long long)(bx - a.tr_blocks) * blockDim.x + threadIdx.x; i < a.n_eps;
        i += (long long)nb * blockDim.x)
     a.eps_out[i] = torch_cuda_randn_elem(seed, offset, i, a.S);
   __syncthreads();
@@ -1322,6 +1354,14 @@ __global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) {
       __threadfence();
     }
   }
+}
+
+__global__ void __launch_bounds__(256) prep_kernel(PrepArgs a) { prep_body(a, (int)blockIdx.x, (int)gridDim.x); }
+// Grouped launch: blockIdx.x = trial * blocks_per_trial + block; arguments of trial t in table[t].
+__global__ void __launch_bounds__(256) prep_group_kernel(const PrepArgs* __restrict__ table, int blocks_per_trial) {
+  const int trial = (int)blockIdx.x / blocks_per_trial;
+  const PrepArgs a = table[trial];
+  prep_body(a, (int)blockIdx.x - trial * blocks_per_trial, blocks_per_trial);
 }
 
 inline int tr_add(TrArgs& a, int& blocks, const float* in, void* out, int R, int C, int ld_in, int ld_out, bool out_is16 = false,
@@ -1337,6 +1377,51 @@ inline int tr_add(TrArgs& a, int& blocks, const float* in, void* out, int R, int
 // ------------------------------------------------------------------------------------------------
 // host side: tensor maps, launchers, the per-engine plan
 // ------------------------------------------------------------------------------------------------
+// ------------------------------------------------------------------------------------------------
+// Launch recorder (grouped launches of several trials).  While a recorder is installed, the step's enqueue
+// code launches nothing: every kernel launch and every event record / stream wait is appended to the recorder instead.
+// The group (mdt_api.cu) records the same step for each of its trials, checks that the T records are congruent, and
+// replays ONE of them with every launch replaced by the grouped kernel over a table of the T trials' arguments.
+// ------------------------------------------------------------------------------------------------
+struct TcOp {
+  enum Kind { GEMM, LAT_FWD, LAT_BWD, PREP, EV_RECORD, STREAM_WAIT } kind;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev = nullptr;
+  // GEMM
+  int bn = 0, split = 0, epi = 0, M = 0, N = 0, K = 0, nsplit = 1, use_clusters = 0;
+  CUtensorMap a{}, b{};
+  Tc05Epi ep{};
+  // latent kernels / prologue
+  LatentFwdArgs lf{};
+  LatentBwdArgs lb{};
+  int sc = 0;
+  PrepArgs pa{};
+  int blocks = 0, programmatic = 1;
+};
+struct TcRecorder {
+  std::vector<TcOp> ops;
+};
+inline TcRecorder*& tc_recorder() {
+  static thread_local TcRecorder* r = nullptr;
+  return r;
+}
+inline cudaError_t tc_event_record(cudaEvent_t ev, cudaStream_t s) {
+  if (TcRecorder* r = tc_recorder()) {
+    TcOp op; op.kind = TcOp::EV_RECORD; op.ev = ev; op.stream = s;
+    r->ops.push_back(op);
+    return cudaSuccess;
+  }
+  return cudaEventRecord(ev, s);
+}
+inline cudaError_t tc_stream_wait(cudaStream_t s, cudaEvent_t ev) {
+  if (TcRecorder* r = tc_recorder()) {
+    TcOp op; op.kind = TcOp::STREAM_WAIT; op.ev = ev; op.stream = s;
+    r->ops.push_back(op);
+    return cudaSuccess;
+  }
+  return cudaStreamWaitEvent(s, ev, 0);
+}
+
 typedef CUresult (*PFN_mdt_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                         const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                         CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -1396,10 +1481,16 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   }
   dim3 grid((N + BN - 1) / BN, (M + kTcBM - 1) / kTcBM, nsplit);
   Tc05Epi epd = ep;
-  epd.dbg = tc05_dbg_buffer();
-  if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   // split-K: the splits of a tile exchange their partials through distributed shared memory when they fit one cluster
   const bool use_clusters = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+  if (TcRecorder* r = tc_recorder()) {
+    TcOp op; op.kind = TcOp::GEMM; op.stream = s; op.bn = BN; op.split = kSplit ? 1 : 0; op.epi = kEpi;
+    op.M = M; op.N = N; op.K = K; op.nsplit = nsplit; op.use_clusters = use_clusters ? 1 : 0; op.a = a; op.b = b; op.ep = epd;
+    r->ops.push_back(op);
+    return MDT_OK;
+  }
+  epd.dbg = tc05_dbg_buffer();
+  if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   // MDT_A_TMEM=1: TF32X3 with the A operand in tensor memory (see Tc05Epi::a_tmem).  Correct, and measured equal in
   // speed to the shared-memory form (57.4 vs 57.5 us/step): the ~1000-cycle k-block is not bound by the MMAs'
   // shared-memory reads of A.  Off by default; read per launch (launches happen at graph capture).
@@ -1557,7 +1648,10 @@ struct Tc05Plan {
   cudaEvent_t ev_join = nullptr, ev_join2 = nullptr, ev_join3 = nullptr, ev_join4 = nullptr;
 };
 
-#define TC_NOTE(p, label) MDT_TRY((p)->b.note((p)->b.note_ctx, label))
+#define TC_NOTE(p, label)                                                       \
+  do {                                                                          \
+    if (tc_recorder() == nullptr) MDT_TRY((p)->b.note((p)->b.note_ctx, label)); \
+  } while (0)
 
 inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
   const Tc05Buffers& b = p->b;
@@ -1786,6 +1880,11 @@ inline int tc05_prep(Tc05Plan* p, cudaStream_t s, const float* x, int B, int set
     torch_randn_policy(pa.n_eps, b.sm_count, b.max_threads_sm, &pa.S, &pa.offset_inc);
     blocks += (int)((pa.n_eps + 255) / 256);
   }
+  if (TcRecorder* r = tc_recorder()) {
+    TcOp op; op.kind = TcOp::PREP; op.stream = s; op.pa = pa; op.blocks = blocks; op.programmatic = programmatic ? 1 : 0;
+    r->ops.push_back(op);
+    return MDT_OK;
+  }
   if (programmatic) {
     MDT_CUDA(launch_pdl(prep_kernel, dim3(blocks), dim3(256), 0, s, pa));
   } else {
@@ -1834,12 +1933,12 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       // the next step's batch goes into the other input set on a side stream, behind this step's first GEMM (whose
       // start implies the previous step, the last reader of that set, is complete); joined where the step joins its
       // weight-gradient streams
-      MDT_CUDA(cudaEventRecord(p->ev_pf_fork, s));
-      MDT_CUDA(cudaStreamWaitEvent(p->side_pf, p->ev_pf_fork, 0));
+      MDT_CUDA(tc_event_record(p->ev_pf_fork, s));
+      MDT_CUDA(tc_stream_wait(p->side_pf, p->ev_pf_fork));
       // NOT a programmatic launch: its blocks would be resident from this GEMM's start, parked in the dependency wait
       // on the SMs the next kernel of the step needs for its own early start (measured: latent_fwd entered 3 us late)
       MDT_TRY(tc05_prep(p, p->side_pf, x, B, xs ^ 1, false, 1, "prefetch_xT", /*programmatic=*/false));
-      MDT_CUDA(cudaEventRecord(p->ev_pf_join, p->side_pf));
+      MDT_CUDA(tc_event_record(p->ev_pf_join, p->side_pf));
       p->prefetch_pending = true;
     }
     if (p->simt_latent) {
@@ -1852,7 +1951,14 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       la.bf16 = b.bf16; la.h3b = b.bf16 ? p->h3_16 : nullptr;
       la.dbg = tc05_dbg_buffer();
       if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
-      MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, tc05_sms(p)), s));
+      if (TcRecorder* r = tc_recorder()) {
+        TcOp op; op.kind = TcOp::LAT_FWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p));
+        la.dbg = nullptr; la.nchunks = (B + op.sc - 1) / op.sc; la.first_live_pass = 1; la.first_pass = 1;
+        op.lf = la;
+        r->ops.push_back(op);
+      } else {
+        MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, tc05_sms(p)), s));
+      }
       TC_NOTE(p, "latent_fwd");
     } else {
     Tc05Epi e2{};
@@ -1916,7 +2022,14 @@ inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
   la.B = B; la.Z = b.Z; la.bf16 = b.bf16;
   la.dbg = tc05_dbg_buffer();
   if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
-  MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true), s));
+  if (TcRecorder* r = tc_recorder()) {
+    TcOp op; op.kind = TcOp::LAT_BWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p), /*backward=*/true);
+    la.dbg = nullptr; la.nchunks = (B + op.sc - 1) / op.sc; la.first_live_pass = 1; la.first_pass = 1;
+    op.lb = la;
+    r->ops.push_back(op);
+  } else {
+    MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true), s));
+  }
   TC_NOTE(p, "latent_bwd");
   return MDT_OK;
 }
@@ -1925,7 +2038,7 @@ inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
 // step after this one works on the other input set.
 inline int tc05_join_prefetch(Tc05Plan* p, cudaStream_t s) {
   if (!p->prefetch_pending) return MDT_OK;
-  MDT_CUDA(cudaStreamWaitEvent(s, p->ev_pf_join, 0));
+  MDT_CUDA(tc_stream_wait(s, p->ev_pf_join));
   p->prefetch_pending = false;
   p->xpar ^= 1;
   return MDT_OK;
@@ -1948,8 +2061,8 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   int nf = 0;
   auto fork_to = [&](cudaStream_t t) -> int {    // everything enqueued on `s` so far is visible to later work on `t`
     if (!fork) return MDT_OK;
-    MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
-    MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
+    MDT_CUDA(tc_event_record(p->ev_fork[nf], s));
+    MDT_CUDA(tc_stream_wait(t, p->ev_fork[nf]));
     ++nf;
     return MDT_OK;
   };
@@ -2004,8 +2117,8 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
     cudaStream_t st[3] = {sw, sw3, sw2x};
     cudaEvent_t ev[3] = {p->ev_join, p->ev_join2, p->ev_join4};
     for (int i = 0; i < 3; ++i) {
-      MDT_CUDA(cudaEventRecord(ev[i], st[i]));
-      MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+      MDT_CUDA(tc_event_record(ev[i], st[i]));
+      MDT_CUDA(tc_stream_wait(s, ev[i]));
     }
   }
   MDT_TRY(tc05_join_prefetch(p, s));
@@ -2035,9 +2148,9 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   int nf = 0;
   auto after_main = [&](cudaStream_t t1, cudaStream_t t2) -> int {   // later work on t1 (and t2) sees `s` so far
     if (!fork) return MDT_OK;
-    MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
-    MDT_CUDA(cudaStreamWaitEvent(t1, p->ev_fork[nf], 0));
-    if (t2) MDT_CUDA(cudaStreamWaitEvent(t2, p->ev_fork[nf], 0));
+    MDT_CUDA(tc_event_record(p->ev_fork[nf], s));
+    MDT_CUDA(tc_stream_wait(t1, p->ev_fork[nf]));
+    if (t2) MDT_CUDA(tc_stream_wait(t2, p->ev_fork[nf]));
     ++nf;
     return MDT_OK;
   };
@@ -2105,7 +2218,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   if (w4_split) at.total_tickets = total_ctas;
   auto launch_dw = [&](int i, cudaStream_t st) -> int {
     MDT_TRY(tc05_launch<EPI_GRADW>(dw[i].bn, sp, *dw[i].a, *dw[i].bm, dw[i].M, dw[i].N, B, ed[i], st, dw[i].ns));
-    MDT_TRY(b.note(b.note_ctx, dw[i].label));
+    if (tc_recorder() == nullptr) MDT_TRY(b.note(b.note_ctx, dw[i].label));
     if (i == 0 && w4_split) {
       MDT_CUDA(launch_pdl(adam_tile_kernel, dim3(at_blocks), dim3(256), 0, st, at));
       MDT_TRY(b.note(b.note_ctx, "fc4_adam"));
@@ -2135,9 +2248,9 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     }
     MDT_TRY(tc05_latent_bwd(p, s, B));            // reads W3T_set[w3par] and W2x^T
     if (fork) {
-      MDT_CUDA(cudaEventRecord(p->ev_fork[nf], s));
+      MDT_CUDA(tc_event_record(p->ev_fork[nf], s));
       for (cudaStream_t t : {sa, sb, sc, sd})
-        if (!((t == sa && dw4_early) || (t == sb && dw3_early))) MDT_CUDA(cudaStreamWaitEvent(t, p->ev_fork[nf], 0));
+        if (!((t == sa && dw4_early) || (t == sb && dw3_early))) MDT_CUDA(tc_stream_wait(t, p->ev_fork[nf]));
       ++nf;
     }
     if (!dw3_early) MDT_TRY(launch_dw(1, sb));
@@ -2173,8 +2286,8 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     cudaStream_t st[4] = {sa, sb, sc, sd};
     cudaEvent_t ev[4] = {p->ev_join, p->ev_join2, p->ev_join3, p->ev_join4};
     for (int i = 0; i < 4; ++i) {
-      MDT_CUDA(cudaEventRecord(ev[i], st[i]));
-      MDT_CUDA(cudaStreamWaitEvent(s, ev[i], 0));
+      MDT_CUDA(tc_event_record(ev[i], st[i]));
+      MDT_CUDA(tc_stream_wait(s, ev[i]));
     }
   }
   if (p->simt_latent) p->w3par ^= 1;              // the next reader of W3^T takes the set this step's update wrote

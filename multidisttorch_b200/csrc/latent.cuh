@@ -247,8 +247,10 @@ __device__ __forceinline__ void lat_load_rows(const float* __restrict__ src, int
 }
 
 // ZQ: compile-time bound on Z / 4 (5 for Z <= 20, 8 for Z <= 32); the real Z is a run-time argument.
+// bx / gx: this CTA's index and the CTA count of ITS trial (blockIdx.x / gridDim.x, or their per-trial parts in the
+// grouped launch of several trials)
 template <int SC, int ZQ>
-__global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a) {
+__device__ __forceinline__ void latent_fwd_body(const LatentFwdArgs& a, const int bx, const int gx) {
   extern __shared__ __align__(16) float lat_smem[];
   float* sA = lat_smem;                               // [SC][H]
   __shared__ __align__(16) float sML[SC * kLatMaxOut];
@@ -271,7 +273,7 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
   unsigned long long ph_seed = 0, ph_off = 0;
   if (gen_eps) { ph_seed = a.st->philox_seed; ph_off = a.st->philox_offset; }
   {
-    const int m0 = blockIdx.x * SC, ns = min(SC, a.B - m0);
+    const int m0 = bx * SC, ns = min(SC, a.B - m0);
     if ((int)threadIdx.x < ns * Z)
       e_pre = gen_eps ? torch_cuda_randn_elem(ph_seed, ph_off, (long long)m0 * Z + threadIdx.x, a.philox_S)
                       : lat_ldg(a.eps_in + (size_t)m0 * Z + threadIdx.x);
@@ -290,8 +292,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
     lat_stamp_go(a.dbg);
   }
   bool first = true;
-  const int chunk_end = live ? a.nchunks : min(a.nchunks, (int)blockIdx.x + 1);
-  for (int chunk = blockIdx.x; chunk < chunk_end; chunk += gridDim.x) {
+  const int chunk_end = live ? a.nchunks : min(a.nchunks, bx + 1);
+  for (int chunk = bx; chunk < chunk_end; chunk += gx) {
     const int m0 = chunk * SC, ns = live ? min(SC, a.B - m0) : 0;   // dry run: every store is predicated off by ns = 0
     if (live) lat_load_rows<SC>(a.h1, H, m0, ns, sA);
     if (!fw_ok) lat_load_dot_w<OPW>(fw, a.W2x, H, 2 * Z, 0, a.b2x);
@@ -357,10 +359,10 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
   }
   lat_stamp(a.dbg, 5);
   kl = block_sum(kl, red);
-  if (threadIdx.x == 0) a.kl_partials[blockIdx.x] = kl;
+  if (threadIdx.x == 0) a.kl_partials[bx] = kl;
   if (gen_eps && threadIdx.x == 0) {                  // every block has read the offset by the time the last ticket is taken
     __threadfence();
-    if (atomicAdd(&a.st->ticket_reparam, 1u) == gridDim.x - 1) {
+    if (atomicAdd(&a.st->ticket_reparam, 1u) == (unsigned)gx - 1u) {
       a.st->philox_offset = ph_off + a.philox_inc;
       a.st->ticket_reparam = 0;
       __threadfence();
@@ -371,7 +373,19 @@ __global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a
 }
 
 template <int SC, int ZQ>
-__global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a) {
+__global__ void __launch_bounds__(kLatThreads) latent_fwd_kernel(LatentFwdArgs a) {
+  latent_fwd_body<SC, ZQ>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+// Grouped launch: blockIdx.x = trial * blocks_per_trial + block; arguments of trial t in table[t].
+template <int SC, int ZQ>
+__global__ void __launch_bounds__(kLatThreads) latent_fwd_group_kernel(const LatentFwdArgs* __restrict__ table, int blocks_per_trial) {
+  const int trial = (int)blockIdx.x / blocks_per_trial;
+  const LatentFwdArgs a = table[trial];
+  latent_fwd_body<SC, ZQ>(a, (int)blockIdx.x - trial * blocks_per_trial, blocks_per_trial);
+}
+
+template <int SC, int ZQ>
+__device__ __forceinline__ void latent_bwd_body(const LatentBwdArgs& a, const int bx, const int gx) {
   extern __shared__ __align__(16) float lat_smem[];
   float* sA = lat_smem;                               // [SC][H]
   __shared__ __align__(16) float sDZ[SC * 32];
@@ -386,7 +400,7 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
   // per-sample inputs of the first chunk (all written by forward kernels of this step, long complete)
   float kmu_pre = 0.f, klv_pre = 0.f, es_pre = 0.f, mk_pre[1][SC];
   {
-    const int m0 = blockIdx.x * SC, ns = min(SC, a.B - m0);
+    const int m0 = bx * SC, ns = min(SC, a.B - m0);
     if ((int)threadIdx.x < ns * Z) {
       const int s = threadIdx.x / Z, j = threadIdx.x - s * Z;
       const size_t m = (size_t)(m0 + s);
@@ -413,8 +427,8 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
     lat_stamp_go(a.dbg);
   }
   bool first = true;
-  const int chunk_end = live ? a.nchunks : min(a.nchunks, (int)blockIdx.x + 1);
-  for (int chunk = blockIdx.x; chunk < chunk_end; chunk += gridDim.x) {
+  const int chunk_end = live ? a.nchunks : min(a.nchunks, bx + 1);
+  for (int chunk = bx; chunk < chunk_end; chunk += gx) {
     const int m0 = chunk * SC, ns = live ? min(SC, a.B - m0) : 0;
     if (live) lat_load_rows<SC>(a.da3, H, m0, ns, sA);
     if (!fw_ok) lat_load_dot_w<OPW>(fw, a.W3T, H, Z, 0);
@@ -474,6 +488,17 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a
   }
   lat_stamp(a.dbg, 6);
   lat_stamp_end(a.dbg);
+}
+
+template <int SC, int ZQ>
+__global__ void __launch_bounds__(kLatThreads) latent_bwd_kernel(LatentBwdArgs a) {
+  latent_bwd_body<SC, ZQ>(a, (int)blockIdx.x, (int)gridDim.x);
+}
+template <int SC, int ZQ>
+__global__ void __launch_bounds__(kLatThreads) latent_bwd_group_kernel(const LatentBwdArgs* __restrict__ table, int blocks_per_trial) {
+  const int trial = (int)blockIdx.x / blocks_per_trial;
+  const LatentBwdArgs a = table[trial];
+  latent_bwd_body<SC, ZQ>(a, (int)blockIdx.x - trial * blocks_per_trial, blocks_per_trial);
 }
 
 // Samples per CTA.  A CTA takes a whole SM (512 threads x 128 registers), and the kernels only pay off when all their

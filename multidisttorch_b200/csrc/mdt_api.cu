@@ -1449,6 +1449,332 @@ int mdt_engine_profile_step(mdt_engine* e, const float* x, int batch, int iters,
   return MDT_OK;
 }
 
+}  // extern "C" (re-opened below)
+
+// =================================================================== grouped trials
+// T independent trials of the same shape on ONE GPU, stepped in lock-step with ONE launch per layer: every kernel of
+// the step is launched once over a table of the T trials' tensor maps / arguments (grid.y resp. grid.x = trial x
+// tiles).  The step's enqueue code is reused unchanged: it is run once per trial under a launch recorder, the T records
+// are checked for congruence, and one of them is replayed with grouped launches inside a CUDA graph capture.
+struct mdt_group {
+  std::vector<mdt_engine*> eng;
+  struct Graph { cudaGraphExec_t exec = nullptr; void* tables = nullptr; long long kernels = 0; };
+  std::map<std::tuple<int, int, int>, Graph> graphs;      // (batch, steps, flags)
+  const void* src_sig[2] = {nullptr, nullptr};
+};
+
+namespace {
+
+template <int kEpi>
+int group_gemm_launch_e(bool split, const Tc05GroupEntry* table, int tiles_m, int T, const TcOp& op, int cluster) {
+  using SS = Tc05Smem<32, false>;
+  using ST = Tc05Smem<32, true>;
+  const dim3 grid((op.N + 31) / 32, tiles_m * T, op.nsplit);
+  const size_t smem = split ? (size_t)ST::TOTAL : (size_t)SS::TOTAL;
+  const dim3 block(tc_threads(split));
+  cudaError_t ce;
+  if (split) {
+    static bool attr = false;
+    if (!attr) { MDT_CUDA(cudaFuncSetAttribute(tc05_gemm_group_kernel<32, true, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, ST::TOTAL)); attr = true; }
+    ce = cluster ? launch_pdl_cluster(tc05_gemm_group_kernel<32, true, kEpi>, grid, block, smem, op.stream, (unsigned)op.nsplit, table, tiles_m, op.M, op.N, op.K)
+                 : launch_pdl(tc05_gemm_group_kernel<32, true, kEpi>, grid, block, smem, op.stream, table, tiles_m, op.M, op.N, op.K);
+  } else {
+    static bool attr = false;
+    if (!attr) { MDT_CUDA(cudaFuncSetAttribute(tc05_gemm_group_kernel<32, false, kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, SS::TOTAL)); attr = true; }
+    ce = cluster ? launch_pdl_cluster(tc05_gemm_group_kernel<32, false, kEpi>, grid, block, smem, op.stream, (unsigned)op.nsplit, table, tiles_m, op.M, op.N, op.K)
+                 : launch_pdl(tc05_gemm_group_kernel<32, false, kEpi>, grid, block, smem, op.stream, table, tiles_m, op.M, op.N, op.K);
+  }
+  MDT_CUDA(ce);
+  return MDT_OK;
+}
+
+int group_gemm_launch(const Tc05GroupEntry* table, int tiles_m, int T, const TcOp& op, int cluster) {
+  switch (op.epi) {
+    case EPI_BIAS_ACT: return group_gemm_launch_e<EPI_BIAS_ACT>(op.split != 0, table, tiles_m, T, op, cluster);
+    case EPI_SIGMOID_BCE: return group_gemm_launch_e<EPI_SIGMOID_BCE>(op.split != 0, table, tiles_m, T, op, cluster);
+    case EPI_RELU_MASK: return group_gemm_launch_e<EPI_RELU_MASK>(op.split != 0, table, tiles_m, T, op, cluster);
+    case EPI_GRADW: return group_gemm_launch_e<EPI_GRADW>(op.split != 0, table, tiles_m, T, op, cluster);
+    default: return set_error(MDT_ERR_UNSUPPORTED, "grouped launch: epilogue %d is not part of the fused step", op.epi);
+  }
+}
+
+template <class K, class A>
+int group_latent_launch(K kernel, const A* table, int bpt, int T, size_t smem, cudaStream_t s) {
+  MDT_CHECK(smem <= 48 * 1024, "grouped latent kernel: %zu bytes of shared memory", smem);
+  MDT_CUDA(launch_pdl(kernel, dim3(bpt * T), dim3(kLatThreads), smem, s, table, bpt));
+  return MDT_OK;
+}
+
+int group_lat_fwd(const LatentFwdArgs* table, const TcOp& op, int T) {
+  const int bpt = latent_grid(op.lf.B, op.sc);
+  const size_t smem = (size_t)op.sc * op.lf.H * sizeof(float);
+  const bool z5 = op.lf.Z <= 20;
+  if (op.sc == 1) return z5 ? group_latent_launch(latent_fwd_group_kernel<1, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_fwd_group_kernel<1, 8>, table, bpt, T, smem, op.stream);
+  if (op.sc == 2) return z5 ? group_latent_launch(latent_fwd_group_kernel<2, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_fwd_group_kernel<2, 8>, table, bpt, T, smem, op.stream);
+  return z5 ? group_latent_launch(latent_fwd_group_kernel<4, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_fwd_group_kernel<4, 8>, table, bpt, T, smem, op.stream);
+}
+int group_lat_bwd(const LatentBwdArgs* table, const TcOp& op, int T) {
+  const int bpt = latent_grid(op.lb.B, op.sc);
+  const size_t smem = (size_t)op.sc * op.lb.H * sizeof(float);
+  const bool z5 = op.lb.Z <= 20;
+  if (op.sc == 1) return z5 ? group_latent_launch(latent_bwd_group_kernel<1, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_bwd_group_kernel<1, 8>, table, bpt, T, smem, op.stream);
+  if (op.sc == 2) return z5 ? group_latent_launch(latent_bwd_group_kernel<2, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_bwd_group_kernel<2, 8>, table, bpt, T, smem, op.stream);
+  return z5 ? group_latent_launch(latent_bwd_group_kernel<4, 5>, table, bpt, T, smem, op.stream) : group_latent_launch(latent_bwd_group_kernel<4, 8>, table, bpt, T, smem, op.stream);
+}
+
+// One trial's record of `steps` pipelined fused-Adam steps (what train_step_device enqueues for a single-rank group).
+int group_record(mdt_engine* e, int B, int steps, bool tail_no_prefetch, TcRecorder* rec) {
+  Tc05Plan* p = e->tc;
+  tc_recorder() = rec;
+  int rc = MDT_OK;
+  for (int i = 0; i < steps && rc == MDT_OK; ++i) {
+    const bool saved = p->no_prefetch;
+    if (tail_no_prefetch && i == steps - 1) p->no_prefetch = true;
+    rc = tc05_forward(p, e->stream, e->x_stage, B, nullptr, false, /*fuse_loss=*/true);
+    if (rc == MDT_OK) rc = tc05_backward_fused_adam(p, e->stream, B);
+    p->no_prefetch = saved;
+  }
+  tc_recorder() = nullptr;
+  return rc;
+}
+
+size_t group_table_bytes(const TcOp& op, int T) {
+  size_t one = 0;
+  switch (op.kind) {
+    case TcOp::GEMM: one = sizeof(Tc05GroupEntry); break;
+    case TcOp::LAT_FWD: one = sizeof(LatentFwdArgs); break;
+    case TcOp::LAT_BWD: one = sizeof(LatentBwdArgs); break;
+    case TcOp::PREP: one = sizeof(PrepArgs); break;
+    default: return 0;
+  }
+  return align_up(one * T, 256);
+}
+
+}  // namespace
+
+extern "C" {
+
+int mdt_group_create(mdt_engine* const* engines, int n_trials, mdt_group** out) {
+  MDT_CHECK(engines && out && n_trials >= 1 && n_trials <= 64, "bad argument");
+  mdt_engine* e0 = engines[0];
+  for (int t = 0; t < n_trials; ++t) {
+    mdt_engine* e = engines[t];
+    MDT_CHECK(e != nullptr && e->bound && e->tc != nullptr, "trial %d: engine missing, unbound or not on the tensor-core path", t);
+    MDT_CHECK(e->gsize == 1 && !e->use_sgd && e->opt_fused_adam, "trial %d: grouped launches cover single-rank Adam trials", t);
+    MDT_CHECK(e->D == e0->D && e->H == e0->H && e->Z == e0->Z && e->Bmax == e0->Bmax && e->cfg.gemm_mode == e0->cfg.gemm_mode &&
+                  e->device == e0->device, "trial %d differs from trial 0 in shape, batch limit, gemm_mode or device", t);
+    MDT_CHECK(e->tc->simt_latent && e->tc->bn_h == 32 && e->tc->bn_fc4 == 32 && e->tc->bn_dwa == 32,
+              "grouped launches cover the small-model regime (CUDA-core latent path, 32-wide tiles: hidden < 2048, max_batch <= 512)");
+  }
+  mdt_group* g = new mdt_group();
+  g->eng.assign(engines, engines + n_trials);
+  *out = g;
+  return MDT_OK;
+}
+
+void mdt_group_destroy(mdt_group* g) {
+  if (!g) return;
+  if (!g->eng.empty()) cudaStreamSynchronize(g->eng[0]->stream);
+  for (auto& kv : g->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.tables) cudaFree(kv.second.tables); }
+  delete g;
+}
+
+int mdt_group_train_steps(mdt_group* g, const mdt_batch_source* srcs, int batch, int64_t first_batch, int n_steps) {
+  MDT_CHECK(g && srcs && batch > 0 && n_steps >= 0 && first_batch >= 0, "bad argument");
+  const int T = (int)g->eng.size();
+  mdt_engine* e0 = g->eng[0];
+  cudaStream_t s0 = e0->stream;
+  if (n_steps == 0) return MDT_OK;
+  for (int t = 0; t < T; ++t) {
+    MDT_TRY(check_batch(g->eng[t], batch));
+    MDT_CHECK(srcs[t].n_batches > 0 && srcs[t].n_batches == srcs[0].n_batches, "every trial's source must hold the same number of batches");
+    MDT_CHECK(srcs[t].x_pool != nullptr || (srcs[t].images_u8 != nullptr && srcs[t].indices != nullptr && srcs[t].n_images > 0),
+              "trial %d: the batch source needs x_pool, or images_u8 + indices + n_images", t);
+  }
+  // the trials' other streams must not be mid-flight: everything of the group runs on trial 0's streams
+  for (int t = 1; t < T; ++t) MDT_CUDA(cudaStreamSynchronize(g->eng[t]->stream));
+  // sources are baked into the captured tables: a new set of sources drops the cached graphs
+  const void* sig[2] = {srcs[0].x_pool ? (const void*)srcs[0].x_pool : (const void*)srcs[0].images_u8,
+                        srcs[T - 1].x_pool ? (const void*)srcs[T - 1].x_pool : (const void*)srcs[T - 1].images_u8};
+  if (memcmp(sig, g->src_sig, sizeof(sig)) != 0) {
+    MDT_CUDA(cudaStreamSynchronize(s0));
+    for (auto& kv : g->graphs) { cudaGraphExecDestroy(kv.second.exec); if (kv.second.tables) cudaFree(kv.second.tables); }
+    g->graphs.clear();
+    memcpy(g->src_sig, sig, sizeof(sig));
+    for (mdt_engine* e : g->eng) e->primed = false;
+  }
+  // per-trial device state: batch cursor where the call starts, first batch staged
+  for (int t = 0; t < T; ++t) {
+    mdt_engine* e = g->eng[t];
+    Tc05Plan* p = e->tc;
+    p->sm_share = T;
+    p->src_pool = srcs[t].x_pool; p->src_images = srcs[t].x_pool ? nullptr : srcs[t].images_u8;
+    p->src_indices = reinterpret_cast<const long long*>(srcs[t].indices);
+    p->src_n_batches = srcs[t].n_batches; p->src_n_images = srcs[t].n_images;
+    if (e->cursor_expected < 0 || (e->cursor_expected - first_batch) % srcs[t].n_batches != 0) {
+      const long long c = first_batch;
+      MDT_CUDA(cudaMemcpy(&e->st->x_cursor, &c, sizeof(c), cudaMemcpyHostToDevice));
+    }
+    const bool primed = e->primed && e->primed_cursor >= 0 && (e->primed_cursor - first_batch) % srcs[t].n_batches == 0 &&
+                        p->xpar == g->eng[0]->tc->xpar;
+    if (!primed) {
+      p->xpar = g->eng[0]->tc->xpar;
+      MDT_TRY(tc05_prep(p, s0, e->x_stage, batch, p->xpar, false, 0, "prep_xT"));      // on trial 0's stream: ordered before the graphs
+    }
+    p->w3par = (t == 0) ? p->w3par : p->w3par;
+    e->last_B = batch;
+  }
+  // the W3^T parity must agree across the trials (they are stepped in lock-step from here on); bring stragglers in line
+  for (int t = 1; t < T; ++t)
+    if (g->eng[t]->tc->w3par != e0->tc->w3par) {
+      g->eng[t]->tc->w3par = e0->tc->w3par;
+      MDT_TRY(tc05_weight_shadows(g->eng[t]->tc, s0));
+    }
+  int rc = MDT_OK;
+  const int U = 16;
+  for (int done = 0; done < n_steps && rc == MDT_OK;) {
+    const int u = (n_steps - done >= U) ? U : 1;
+    const int x0 = e0->tc->xpar, w0 = e0->tc->w3par;
+    const auto key = std::make_tuple(batch, u, x0 | (w0 << 1));
+    auto it = g->graphs.find(key);
+    if (it == g->graphs.end()) {
+      // 1. record the u steps once per trial
+      std::vector<TcRecorder> recs(T);
+      for (int t = 0; t < T && rc == MDT_OK; ++t) {
+        Tc05Plan* p = g->eng[t]->tc;
+        p->xpar = x0; p->w3par = w0; p->pipelined = true; p->prefetch_pending = false;
+        rc = group_record(g->eng[t], batch, u, false, &recs[t]);
+        p->pipelined = false;
+      }
+      if (rc != MDT_OK) break;
+      const std::vector<TcOp>& ops = recs[0].ops;
+      size_t bytes = 0;
+      for (int t = 1; t < T; ++t)
+        if (recs[t].ops.size() != ops.size()) { rc = set_error(MDT_ERR_STATE, "grouped launch: trial %d recorded %zu operations, trial 0 %zu", t, recs[t].ops.size(), ops.size()); break; }
+      if (rc != MDT_OK) break;
+      for (const TcOp& op : ops) bytes += group_table_bytes(op, T);
+      // 2. build the tables (host), upload once
+      std::vector<char> host(bytes);
+      void* dev = nullptr;
+      MDT_CUDA(cudaMalloc(&dev, bytes ? bytes : 256));
+      std::vector<size_t> off(ops.size(), 0);
+      size_t cur = 0;
+      for (size_t i = 0; i < ops.size() && rc == MDT_OK; ++i) {
+        const TcOp& op = ops[i];
+        off[i] = cur;
+        for (int t = 0; t < T; ++t) {
+          const TcOp& ot = recs[t].ops[i];
+          const bool same = ot.kind == op.kind && ot.bn == op.bn && ot.split == op.split && ot.epi == op.epi && ot.M == op.M && ot.N == op.N &&
+                            ot.K == op.K && ot.nsplit == op.nsplit && ot.sc == op.sc && ot.blocks == op.blocks;
+          if (!same) { rc = set_error(MDT_ERR_STATE, "grouped launch: operation %zu of trial %d is not congruent with trial 0's", i, t); break; }
+          char* dst = host.data() + cur;
+          if (op.kind == TcOp::GEMM) {
+            if (op.bn != 32) { rc = set_error(MDT_ERR_UNSUPPORTED, "grouped launch: BLOCK_N %d", op.bn); break; }
+            Tc05GroupEntry en{};
+            en.a = ot.a; en.b = ot.b; en.ep = ot.ep; en.ep.dbg = nullptr;
+            memcpy(dst + (size_t)t * sizeof(Tc05GroupEntry), &en, sizeof(en));
+          } else if (op.kind == TcOp::LAT_FWD) {
+            memcpy(dst + (size_t)t * sizeof(LatentFwdArgs), &ot.lf, sizeof(LatentFwdArgs));
+          } else if (op.kind == TcOp::LAT_BWD) {
+            memcpy(dst + (size_t)t * sizeof(LatentBwdArgs), &ot.lb, sizeof(LatentBwdArgs));
+          } else if (op.kind == TcOp::PREP) {
+            memcpy(dst + (size_t)t * sizeof(PrepArgs), &ot.pa, sizeof(PrepArgs));
+          }
+        }
+        cur += group_table_bytes(op, T);
+      }
+      // cluster form of a split GEMM: decided for the whole (T x tiles) grid, written into every trial's entry
+      std::vector<int> cluster(ops.size(), 0);
+      for (size_t i = 0; i < ops.size() && rc == MDT_OK; ++i) {
+        const TcOp& op = ops[i];
+        if (op.kind != TcOp::GEMM) continue;
+        cluster[i] = (op.nsplit > 1 && op.nsplit <= 8 && op.use_clusters) ? 1 : 0;
+        const int tiles = ((op.N + 31) / 32) * ((op.M + kTcBM - 1) / kTcBM) * T;
+        if (cluster[i] && tiles * op.nsplit > e0->dev->sm_count) cluster[i] = 0;      // clusters must all be co-resident
+        for (int t = 0; t < T; ++t)
+          reinterpret_cast<Tc05GroupEntry*>(host.data() + off[i])[t].ep.cluster = cluster[i];
+      }
+      if (rc == MDT_OK && bytes) {
+        cudaError_t ce = cudaMemcpy(dev, host.data(), bytes, cudaMemcpyHostToDevice);
+        if (ce != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "grouped launch: table upload: %s", cudaGetErrorString(ce));
+      }
+      if (rc != MDT_OK) { cudaFree(dev); break; }
+      // 3. replay trial 0's record with grouped launches inside a capture
+      cudaGraph_t graph = nullptr;
+      long long kernels = 0;
+      MDT_CUDA(cudaStreamBeginCapture(s0, cudaStreamCaptureModeRelaxed));
+      for (size_t i = 0; i < ops.size() && rc == MDT_OK; ++i) {
+        const TcOp& op = ops[i];
+        char* tab = static_cast<char*>(dev) + off[i];
+        cudaError_t ce = cudaSuccess;
+        switch (op.kind) {
+          case TcOp::EV_RECORD: ce = cudaEventRecord(op.ev, op.stream); break;
+          case TcOp::STREAM_WAIT: ce = cudaStreamWaitEvent(op.stream, op.ev, 0); break;
+          case TcOp::GEMM:
+            rc = group_gemm_launch(reinterpret_cast<const Tc05GroupEntry*>(tab), (op.M + kTcBM - 1) / kTcBM, T, op, cluster[i]);
+            ++kernels;
+            break;
+          case TcOp::LAT_FWD: rc = group_lat_fwd(reinterpret_cast<const LatentFwdArgs*>(tab), op, T); ++kernels; break;
+          case TcOp::LAT_BWD: rc = group_lat_bwd(reinterpret_cast<const LatentBwdArgs*>(tab), op, T); ++kernels; break;
+          case TcOp::PREP:
+            if (op.programmatic) ce = launch_pdl(prep_group_kernel, dim3(op.blocks * T), dim3(256), 0, op.stream, reinterpret_cast<const PrepArgs*>(tab), op.blocks);
+            else prep_group_kernel<<<dim3(op.blocks * T), dim3(256), 0, op.stream>>>(reinterpret_cast<const PrepArgs*>(tab), op.blocks);
+            if (ce == cudaSuccess) ce = cudaGetLastError();
+            ++kernels;
+            break;
+        }
+        if (ce != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "grouped launch: %s", cudaGetErrorString(ce));
+      }
+      cudaError_t ce = cudaStreamEndCapture(s0, &graph);
+      if (rc == MDT_OK && ce != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "grouped launch: cudaStreamEndCapture: %s", cudaGetErrorString(ce));
+      if (rc == MDT_OK) {
+        int removed = 0;
+        rc = reduce_graph_edges(graph, &removed);
+      }
+      mdt_group::Graph entry;
+      if (rc == MDT_OK && cudaGraphInstantiate(&entry.exec, graph, 0) != cudaSuccess) rc = set_error(MDT_ERR_CUDA, "grouped launch: cudaGraphInstantiate failed");
+      if (graph) cudaGraphDestroy(graph);
+      if (rc != MDT_OK) { cudaFree(dev); break; }
+      entry.tables = dev; entry.kernels = kernels;
+      it = g->graphs.emplace(key, entry).first;
+    }
+    MDT_CUDA(cudaGraphLaunch(it->second.exec, s0));
+    // host-side bookkeeping of every trial, as if it had been stepped alone
+    for (int t = 0; t < T; ++t) {
+      mdt_engine* e = g->eng[t];
+      e->launch_count += it->second.kernels;
+      e->pub_expected = (e->pub_expected + (unsigned)u) & 0x7fffffffu;
+      e->tc->xpar = x0 ^ (u & 1); e->tc->w3par = w0 ^ (u & 1); e->tc->prefetch_pending = false;
+    }
+    done += u;
+  }
+  for (int t = 0; t < T; ++t) {
+    mdt_engine* e = g->eng[t];
+    Tc05Plan* p = e->tc;
+    p->sm_share = e->sm_share_pending;
+    p->src_pool = nullptr; p->src_images = nullptr; p->src_indices = nullptr;
+    e->cursor_expected = rc == MDT_OK ? first_batch + n_steps : -1;
+    e->primed = rc == MDT_OK;
+    e->primed_cursor = first_batch + n_steps;
+    // the step graphs of the engine itself were captured for other SM shares / streams: nothing to invalidate, they are keyed
+  }
+  // the trials' own streams must see the group's work as done before they are used again
+  if (rc == MDT_OK && T > 1) {
+    cudaEvent_t ev = e0->ev_set_free[0] ? e0->ev_set_free[0] : nullptr;
+    if (ev != nullptr) {
+      MDT_CUDA(cudaEventRecord(ev, s0));
+      for (int t = 1; t < T; ++t) MDT_CUDA(cudaStreamWaitEvent(g->eng[t]->stream, ev, 0));
+    } else {
+      MDT_CUDA(cudaStreamSynchronize(s0));
+    }
+  }
+  return rc;
+}
+
+}  // extern "C"
+
+extern "C" {
+
 // ------------------------------------------------------------------ stand-alone kernels
 
 int mdt_adam_flat(float* p, const float* g, float* m, float* v, size_t n, const mdt_adam* h, int64_t step,

@@ -365,6 +365,46 @@ def train_step_many(engines, xs):
     check(_lib.load().mdt_train_step_many(hs, ps, n, xs[0].shape[0]))
 
 
+class TrialGroup:
+    """T single-rank trials of one shape on one GPU, stepped in lock-step with ONE launch per layer (mdt_group_*,
+    SURVEY 8f-3).  The engines stay usable on their own; each keeps its parameters, state and losses."""
+
+    def __init__(self, engines):
+        self.engines = list(engines)
+        self.lib = _lib.load()
+        n = len(self.engines)
+        hs = (C.c_void_p * n)(*[e._h for e in self.engines])
+        g = C.c_void_p()
+        check(self.lib.mdt_group_create(hs, n, C.byref(g)))
+        self._g = g
+
+    def train_steps(self, pools, first_batch, n_steps):
+        """pools: one [n_batches, B, D] device tensor per trial (the same tensor may be given to several trials)."""
+        n = len(self.engines)
+        assert len(pools) == n
+        B = pools[0].shape[1]
+        srcs = (mdt_batch_source * n)()
+        for t, pl in enumerate(pools):
+            assert pl.dtype == torch.float32 and pl.is_contiguous() and pl.shape[1] == B
+            srcs[t] = mdt_batch_source(pl.data_ptr(), None, None, pl.shape[0], 0)
+        self._keep = pools
+        check(self.lib.mdt_group_train_steps(self._g, srcs, B, first_batch, n_steps))
+
+    def synchronize(self):
+        self.engines[0].synchronize()
+
+    def close(self):
+        if getattr(self, "_g", None) is not None:
+            self.lib.mdt_group_destroy(self._g)
+            self._g = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
 def adam_flat(p, g, m, v, step, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, grad_scale=1.0):
     h = mdt_adam(lr, betas[0], betas[1], eps)
     check(_lib.load().mdt_adam_flat(_ptr(p), _ptr(g), _ptr(m), _ptr(v), p.numel(), C.byref(h), step, grad_scale,

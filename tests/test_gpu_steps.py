@@ -121,3 +121,39 @@ def test_host_chunks_equal_synchronous_host_steps(E, mode):
     assert got == want
     assert torch.equal(a.params, b.params) and a.state() == b.state()
     a.close(); b.close()
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+@pytest.mark.parametrize("T", [2, 3])
+def test_grouped_trials_equal_trials_stepped_alone(E, mode, T):
+    """T trials stepped with ONE launch per layer (mdt_group_train_steps) end bit-identical to the same
+    trials stepped alone with their kernels sized for 1/T of the SMs, and keep their own losses / Philox streams."""
+    B = 128
+    pools = [torch.rand(5, B, 784, generator=torch.Generator().manual_seed(40 + t)).cuda() for t in range(T)]
+    grouped, alone = [], []
+    for t in range(T):
+        for lst in (grouped, alone):
+            e = E.VAEEngine(max_batch=B, gemm_mode=mode)
+            e.load_segments(O.init_params(500 + t))
+            e.set_rng(600 + t, 0)
+            lst.append(e)
+        alone[-1].set_sm_share(T)
+    grp = E.TrialGroup(grouped)
+    n = 21                                              # one 16-step graph + 5 single steps
+    grp.train_steps(pools, 2, n)
+    grp.train_steps(pools, (2 + n) % 5, 3)              # continues where it stopped
+    grp.synchronize()
+    for t in range(T):
+        alone[t].train_steps(pools[t], 2, n + 3)
+        alone[t].synchronize(); grouped[t].synchronize()
+        assert torch.equal(grouped[t].params, alone[t].params), t
+        assert torch.equal(grouped[t].exp_avg_sq, alone[t].exp_avg_sq), t
+        assert grouped[t].state() == alone[t].state() == (n + 3, 4 * (n + 3))
+    # the engines of a group remain usable on their own afterwards
+    l0 = float(grouped[0].train_step(pools[0][0], None).item())
+    l1 = float(alone[0].train_step(pools[0][0], None).item())
+    alone[0].set_sm_share(1)
+    assert np.isfinite(l0) and abs(l0 - l1) <= 1e-5 * abs(l1)
+    grp.close()
+    for e in grouped + alone:
+        e.close()
