@@ -585,9 +585,10 @@ def run_own(args):
             modes[m] = round(world * B / (msm * 1e-3), 1)
             em.close()
     # ---- SURVEY section 8f-3 (next row): several independent trials per GPU
-    multi_trial, multi_trial_grouped = None, None
+    multi_trial, multi_trial_grouped, multi_trial_streams = None, None, None
     if world == 1 and not args.no_modes:
         multi_trial = {"1": round(value, 1)}
+        multi_trial_streams = {"1": round(value, 1), "what": "T independent mdt_train_steps loops, one stream per trial, 16-step graphs"}
         multi_trial_grouped = {"1": round(value, 1),
                                "what": "T trials in lock-step, one launch per layer over a table of the trials' arguments (mdt_group_train_steps)"}
         for T in (2, 4, 8):
@@ -623,6 +624,28 @@ def run_own(args):
                 finally:
                     grp.close()
             multi_trial_grouped[str(T)] = section(f"trials_per_gpu_grouped/{T}", grouped)
+
+            def streams():
+                # T independent mdt_train_steps loops (graphs of 16 pipelined steps), one stream per trial, kernels sized
+                # for 1/T of the SMs: the trials drift apart and fill each other's idle SMs
+                for e_ in engs:
+                    e_.set_sm_share(T)
+                try:
+                    for e_ in engs:
+                        e_.train_steps(pool, 0, 2 * W)
+                    ts_ = []
+                    for r_ in range(3):
+                        torch.cuda.synchronize()
+                        t0_ = time.perf_counter()
+                        for e_ in engs:
+                            e_.train_steps(pool, (2 * W + r_ * Km) % POOL_BATCHES, Km)
+                        torch.cuda.synchronize()
+                        ts_.append(time.perf_counter() - t0_)
+                    return round(T * B * Km / statistics.median(ts_), 1)
+                finally:
+                    for e_ in engs:
+                        e_.set_sm_share(1)
+            multi_trial_streams[str(T)] = section(f"trials_per_gpu_streams/{T}", streams)
             for e_ in engs:
                 e_.close()
 
@@ -718,7 +741,7 @@ def run_own(args):
             "gpu_launches_per_step": round(total_launches / (world * R * n_region), 2), "roofline": roofline,
             "cpu_baseline": cpu_baseline, "ddp_parity": parity, "layouts": layouts, "layouts_bf16": layouts_bf16,
             "exchanges": exchanges, "allreduce": allreduce, "config5": config5, "modes": modes,
-            "trials_per_gpu": multi_trial, "trials_per_gpu_grouped": multi_trial_grouped, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
+            "trials_per_gpu": multi_trial, "trials_per_gpu_grouped": multi_trial_grouped, "trials_per_gpu_streams": multi_trial_streams, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
             "kernels": kernels,
         }
         watchdog.cancel()
