@@ -300,6 +300,10 @@ def ddp_parity(ctx, args, gemm_modes):
     for tag, w in cases:
         g = dict(np.load(os.path.join(ROOT, "tests", "golden", f"{tag}.npz"), allow_pickle=False))
         ng, B, n_steps = int(g["ngroups"]), int(g["B"]), int(g["n_steps"])
+        shift = int(g["seed_shift"]) if "seed_shift" in g else 0
+        # a run with a ReLU pre-activation within fp32 rounding of zero cannot pin parameters tightly (one flipped mask
+        # moves a weight row by O(lr): measured 2.9e-3 on W1); the fixture records its smallest |pre-activation|
+        fragile = "relu_margin" in g and float(g["relu_margin"]) < 1.5e-6
         k = w // ng
         groups = [dist.new_group(ranks=list(range(k * gi, k * gi + k))) for gi in range(ng)]   # every rank creates every group
         entry = {}
@@ -316,7 +320,7 @@ def ddp_parity(ctx, args, gemm_modes):
                         eng.load_segments(synth.init_params(synth.PARAM_SEED + gid if grank == 0 else 999 + ctx.rank))
                         eng.broadcast_params()
                         for t in range(n_steps):
-                            x, eps = synth.make_batch(synth.batch_seed(t, ctx.rank), B)
+                            x, eps = synth.make_batch(synth.batch_seed(t, ctx.rank) + shift, B)
                             loss = float(eng.train_step(torch.from_numpy(x).to(ctx.device), torch.from_numpy(eps).to(ctx.device)).item())
                             want = float(g[f"losses.rank{ctx.rank}"][t])
                             res[1] = max(float(res[1]), abs(loss - want) / abs(want))
@@ -329,7 +333,8 @@ def ddp_parity(ctx, args, gemm_modes):
                         dist.all_gather(gathered, flat, group=groups[gid])
                         same = all(torch.equal(gathered[0], t_) for t_ in gathered)
                         timed_out = eng.exchange_status()[1]
-                        if not same or timed_out or not (res[1] <= TOL[mode][0]) or not (res[2] <= TOL[mode][1]):
+                        ptol = max(TOL[mode][1], 1e-2) if fragile else TOL[mode][1]
+                        if not same or timed_out or not (res[1] <= TOL[mode][0]) or not (res[2] <= ptol):
                             res[0] = 1
                         eng.close()
                     except Exception as exc:       # keep every rank in the collective below
@@ -340,10 +345,15 @@ def ddp_parity(ctx, args, gemm_modes):
                 ok = ok and not failed
                 entry[f"{mode}/{xch}"] = {"status": "FAIL" if failed else "ok", "max_loss_rel": float(f"{res[1].item():.3g}"),
                                           "max_param_rel": float(f"{res[2].item():.3g}")}
+        if fragile:
+            entry["relu_margin"] = float(g["relu_margin"])
+            entry["param_rel_bound"] = 1e-2
         report[tag.replace("ddp_", "")] = entry
     report["tolerance"] = {m: {"loss_rel": TOL[m][0], "param_rel": TOL[m][1]} for m in gemm_modes}
     report["checks"] = ("per-step loss of every rank and final parameters of every group vs the reference's DDP run; "
-                        "parameters bit-identical across the ranks of a group; no expired peer wait")
+                        "parameters bit-identical across the ranks of a group; no expired peer wait.  A fixture that records a "
+                        "ReLU pre-activation within 1.5e-6 of zero (relu_margin) gets the parameter bound 1e-2: the mask of that "
+                        "unit depends on the fp32 summation order")
     return report, ok
 
 

@@ -325,7 +325,7 @@ def worker_ddp(args):
         losses = []
         with EpsInjector(torch) as inj:
             for t in range(args.steps):
-                x, eps = O.make_batch(batch_seed(t, wr), args.batch, dims)
+                x, eps = O.make_batch(batch_seed(t, wr) + args.seed_shift, args.batch, dims)
                 data = torch.from_numpy(x).view(args.batch, 1, 28, 28)
                 inj.queue.append(torch.from_numpy(eps))
                 opt.zero_grad()
@@ -349,7 +349,7 @@ def worker_ddp(args):
     dist.destroy_process_group()
 
 
-def spawn(world, ngroups, steps, batch, port):
+def spawn(world, ngroups, steps, batch, port, seed_shift=0):
     tmp = tempfile.mkdtemp(prefix="mdt_golden_")
     procs = []
     for r in range(world):
@@ -357,15 +357,23 @@ def spawn(world, ngroups, steps, batch, port):
         env.update(OMPI_COMM_WORLD_SIZE=str(world), OMPI_COMM_WORLD_RANK=str(r), MASTER_PORT=str(port),
                    MASTER_ADDR="127.0.0.1", DDP_BACKEND="gloo", OMP_NUM_THREADS="2")
         procs.append(subprocess.Popen([sys.executable, os.path.abspath(__file__), "--worker", "--ngroups", str(ngroups),
-                                       "--steps", str(steps), "--batch", str(batch), "--tmp", tmp], env=env))
+                                       "--steps", str(steps), "--batch", str(batch), "--tmp", tmp,
+                                       "--seed-shift", str(seed_shift)], env=env))
     for p in procs:
         assert p.wait(timeout=600) == 0
     return [dict(np.load(os.path.join(tmp, f"rank{r}.npz"), allow_pickle=False)) for r in range(world)]
 
 
-def run_ddp(world, ngroups, steps, batch, tag, port):
-    ranks = spawn(world, ngroups, steps, batch, port)
-    out = {"world": world, "ngroups": ngroups, "B": batch, "n_steps": steps}
+def run_ddp(world, ngroups, steps, batch, tag, port, seed_shift=0):
+    """seed_shift moves the data seeds of a case.  ReLU is discontinuous: a pre-activation within fp32 rounding of zero
+    has a mask that depends on the summation order, and one flipped unit moves a row of W1 / W3 by O(lr) within a few
+    Adam steps (the first ddp_2x2_b16 fixture had |a1| = 3.4e-8 and the GPU differed from it by 2.9e-3 on W1 while its
+    losses agreed to 2e-7).  Small cases are therefore generated from seeds whose smallest |pre-activation| (fc1 and
+    fc3, every rank, every step; recorded as `relu_margin`) is >= 1.5e-6; for the 3072-sample 2x4 case no such seed
+    exists statistically, and its consumers use the looser parameter bound when `relu_margin` is below that."""
+    ranks = spawn(world, ngroups, steps, batch, port, seed_shift)
+    out = {"world": world, "ngroups": ngroups, "B": batch, "n_steps": steps, "seed_shift": seed_shift}
+    margin = 1.0
     k = world // ngroups
     for gid in range(ngroups):
         members = list(range(k * gid, k * gid + k))
@@ -380,15 +388,22 @@ def run_ddp(world, ngroups, steps, batch, tag, port):
         # oracle check (full tensors)
         orc = O.Trainer(O.init_params(PARAM_SEED + gid), O.Dims())
         for t in range(steps):
-            lo, _ = orc.step([O.make_batch(batch_seed(t, r), batch) for r in members])
+            for r in members:
+                x_, eps_ = O.make_batch(batch_seed(t, r) + seed_shift, batch)
+                act_ = O.forward(orc.p, x_, eps_)
+                a1_ = x_ @ orc.p["W1"].T + orc.p["b1"]
+                a3_ = act_["z"] @ orc.p["W3"].T + orc.p["b3"]
+                margin = min(margin, float(np.abs(a1_).min()), float(np.abs(a3_).min()))
+            lo, _ = orc.step([O.make_batch(batch_seed(t, r) + seed_shift, batch) for r in members])
             for i, r in enumerate(members):
                 ref_l = float(ranks[r]["losses"][t])
                 assert abs(lo[i] - ref_l) <= 2e-6 * abs(ref_l), (tag, gid, t, r, lo[i], ref_l)
         for name in O.SEGMENTS:
             e = rel_l2(orc.p[name], ranks[members[0]][f"paramN.{name}"])
             assert e < 1e-5, (tag, gid, name, e)
+    out["relu_margin"] = np.float64(margin)
     np.savez_compressed(os.path.join(GOLD, f"{tag}.npz"), **out)
-    print(f"[golden] {tag}: ok")
+    print(f"[golden] {tag}: ok (smallest |pre-activation| {margin:.2e})")
 
 
 def run_api(port):
@@ -440,6 +455,7 @@ def main():
     ap.add_argument("--steps", type=int, default=0)
     ap.add_argument("--batch", type=int, default=0)
     ap.add_argument("--tmp", default="")
+    ap.add_argument("--seed-shift", type=int, default=0)
     ap.add_argument("--only", default="")
     args = ap.parse_args()
     if args.worker:
@@ -459,9 +475,9 @@ def main():
         run_step_edge("step_edge_b8")
     if "ddp" in todo:
         run_ddp(2, 1, 5, 32, "ddp_1x2_b32", 29610)
-        run_ddp(4, 2, 3, 16, "ddp_2x2_b16", 29620)
-        run_ddp(4, 1, 3, 32, "ddp_1x4_b32", 29650)
-        run_ddp(8, 1, 3, 16, "ddp_1x8_b16", 29660)
+        run_ddp(4, 2, 3, 16, "ddp_2x2_b16", 29620, seed_shift=300000)
+        run_ddp(4, 1, 3, 32, "ddp_1x4_b32", 29650, seed_shift=1500000)
+        run_ddp(8, 1, 3, 16, "ddp_1x8_b16", 29660, seed_shift=200000)
         run_ddp(8, 2, 3, 128, "ddp_2x4_b128", 29670)             # BASELINE config 4: 2 trials x 4 ranks, 512/group
     if "api" in todo:
         run_api(29640)

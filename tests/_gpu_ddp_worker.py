@@ -36,9 +36,14 @@ def main():
     # (loss, parameters after the golden's 3-5 steps); the same bounds as bench.py's ddp_parity
     # measured on 2 x B200 (1x2 golden, 5 steps): tf32x3 loss 1.1e-7 / parameters 2.0e-7, bf16 1.7e-5 / 1.4e-2
     tol = {"fp32": (5e-6, 2e-5), "tf32x3": (5e-6, 2e-5), "tf32": (2e-3, 1e-1), "bf16": (6e-4, 1e-1)}[mode]
+    # A fixture whose run holds a ReLU pre-activation within fp32 rounding of zero (relu_margin; oracle/make_golden.py
+    # run_ddp) cannot pin parameters tightly: one flipped mask moves a weight row by O(lr).  Measured: 2.9e-3 on W1.
+    shift = int(g["seed_shift"]) if "seed_shift" in g else 0
+    if "relu_margin" in g and float(g["relu_margin"]) < 1.5e-6 and mode in ("fp32", "tf32x3"):
+        tol = (tol[0], 1e-2)
     res = {"rank": rank, "gid": gid, "losses": []}
     for t in range(n):
-        x, eps = O.make_batch(batch_seed(t, rank), B)
+        x, eps = O.make_batch(batch_seed(t, rank) + shift, B)
         loss = float(eng.train_step(torch.from_numpy(x).cuda(), torch.from_numpy(eps).cuda()).item())
         ref = float(g[f"losses.rank{rank}"][t])
         assert abs(loss - ref) <= tol[0] * abs(ref), (tag, mode, rank, t, loss, ref)

@@ -84,12 +84,13 @@ def test_step_with_logits_on_the_bce_corners():
 def test_ddp_groups_match_reference(tag):
     g = load(tag)
     world, ng, B, n = (int(g[k]) for k in ("world", "ngroups", "B", "n_steps"))
+    shift = int(g["seed_shift"]) if "seed_shift" in g else 0
     k = world // ng
     for gid in range(ng):
         members = list(range(k * gid, k * gid + k))
         tr = O.Trainer(O.init_params(PARAM_SEED + gid))
         for t in range(n):
-            losses, _ = tr.step([O.make_batch(batch_seed(t, r), B) for r in members])
+            losses, _ = tr.step([O.make_batch(batch_seed(t, r) + shift, B) for r in members])
             for i, r in enumerate(members):
                 ref = float(g[f"losses.rank{r}"][t])
                 assert abs(losses[i] - ref) <= TOL_LOSS * abs(ref), (tag, gid, t, r)
