@@ -659,10 +659,17 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
       return enqueue_adam_p2p(e, gscale);
     });
   }
-  if (!e->opt_nccl_in_graph) {   // MDT_NCCL_GRAPH=0: NCCL outside the graphs
-    MDT_TRY(run_cached(e, /*kind=*/1, B, fl, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); }));
+  // NCCL outside the graphs: forward + backward as one graph, the all-reduces enqueued eagerly, the optimizer as a second
+  // graph.  Taken for MDT_NCCL_GRAPH=0 and for DDP's two-bucket form in groups of more than 4 ranks: captured, the
+  // 12.8 + 13.9 MB all-reduces of H = 4096 fail inside ncclAllReduce on 8 ranks ("unhandled cuda error"; the same calls
+  // succeed eagerly, and captured on 4 ranks), and at that size a step is long enough not to care about two launches.
+  if (!e->opt_nccl_in_graph || (!e->one_bucket && e->gsize > 4)) {
+    e->defer_buckets = true;     // no all-reduce inside the captured backward
+    const int rc1 = run_cached(e, kbase + 1, B, fl, [&]() -> int { return enqueue_fwd_loss_bwd(e, x, B, eps); });
+    e->defer_buckets = false;
+    MDT_TRY(rc1);
     MDT_TRY(finish_allreduce(e));
-    return run_cached(e, /*kind=*/2, B, fl & ~1, [&]() -> int { return enqueue_adam(e, gscale, true); });
+    return run_cached(e, kbase + 2, B, fl & ~1, [&]() -> int { return enqueue_adam(e, gscale, true); });
   }
   // one graph for the whole step, the group's NCCL all-reduces included (bucket 0 overlaps the rest of backward)
   return run_cached(e, kbase + 6, B, fl, [&]() -> int {
