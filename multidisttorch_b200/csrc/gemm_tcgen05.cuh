@@ -1378,6 +1378,54 @@ inline int tr_add(TrArgs& a, int& blocks, const float* in, void* out, int R, int
 // host side: tensor maps, launchers, the per-engine plan
 // ------------------------------------------------------------------------------------------------
 // ------------------------------------------------------------------------------------------------
+// Diagnostic switches (MDT_* environment variables).  They are read ONCE, when an engine's tensor-core plan is created
+// (tc05_create), into the plan; the enqueue entry points install the plan's copy for the launch helpers below, which
+// have no plan argument.  Nothing on the launch path calls getenv.
+// ------------------------------------------------------------------------------------------------
+struct TcKnobs {
+  bool splitk = true;          // MDT_NO_SPLITK=1 clears
+  bool cluster_splitk = true;  // MDT_NO_CLUSTER_SPLITK=1 clears: split-K partials through a workspace instead of DSMEM
+  bool a_tmem = false;         // MDT_A_TMEM=1: TF32X3 with the A operand in tensor memory
+  int min_kb = 0;              // MDT_MIN_KB_PER_SPLIT (0: 3 with clusters, 4 without)
+  int max_splits = 0;          // MDT_MAX_SPLITS (0: no extra cap)
+  bool w4_split = false;       // MDT_W4_SPLIT=1: fc4's Adam update as a separate tile kernel
+  int bn_dw4 = 0, bn_dw1 = 0;  // MDT_BN_DW4 / MDT_BN_DW1: tile width of fc4's / fc1's fused-Adam GEMM
+  bool dw4_late = false;       // MDT_DW4_LATE=1: all four updates start together after latent_bwd
+  bool dw3_early = false;      // MDT_DW3_EARLY=1: fc3's update starts with fc4's
+  bool dw1_side = false;       // MDT_DW1_SIDE=1: fc1's update on a side stream
+  int latent_sc = 0;           // MDT_LATENT_SC: samples per CTA of the CUDA-core latent kernels (1 / 2 / 4; 0: choose)
+  static TcKnobs from_env() {
+    TcKnobs k;
+    k.splitk = getenv("MDT_NO_SPLITK") == nullptr;
+    k.cluster_splitk = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+    if (const char* v = getenv("MDT_A_TMEM")) k.a_tmem = v[0] == '1';
+    if (const char* v = getenv("MDT_MIN_KB_PER_SPLIT")) k.min_kb = atoi(v);
+    if (const char* v = getenv("MDT_MAX_SPLITS")) k.max_splits = atoi(v);
+    k.w4_split = getenv("MDT_W4_SPLIT") != nullptr;
+    if (const char* v = getenv("MDT_BN_DW4")) k.bn_dw4 = atoi(v);
+    if (const char* v = getenv("MDT_BN_DW1")) k.bn_dw1 = atoi(v);
+    k.dw4_late = getenv("MDT_DW4_LATE") != nullptr;
+    k.dw3_early = getenv("MDT_DW3_EARLY") != nullptr;
+    k.dw1_side = getenv("MDT_DW1_SIDE") != nullptr;
+    if (const char* v = getenv("MDT_LATENT_SC")) k.latent_sc = atoi(v);
+    return k;
+  }
+};
+inline const TcKnobs*& tc_knobs_ptr() {
+  static thread_local const TcKnobs* k = nullptr;
+  return k;
+}
+inline const TcKnobs& tc_knobs() {
+  static const TcKnobs defaults{};       // launches outside any plan (none today) get the built-in defaults
+  return tc_knobs_ptr() ? *tc_knobs_ptr() : defaults;
+}
+struct TcKnobScope {
+  const TcKnobs* prev;
+  explicit TcKnobScope(const TcKnobs* k) : prev(tc_knobs_ptr()) { tc_knobs_ptr() = k; }
+  ~TcKnobScope() { tc_knobs_ptr() = prev; }
+};
+
+// ------------------------------------------------------------------------------------------------
 // Launch recorder (grouped launches of several trials).  While a recorder is installed, the step's enqueue
 // code launches nothing: every kernel launch and every event record / stream wait is appended to the recorder instead.
 // The group (mdt_api.cu) records the same step for each of its trials, checks that the T records are congruent, and
@@ -1482,7 +1530,7 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   dim3 grid((N + BN - 1) / BN, (M + kTcBM - 1) / kTcBM, nsplit);
   Tc05Epi epd = ep;
   // split-K: the splits of a tile exchange their partials through distributed shared memory when they fit one cluster
-  const bool use_clusters = getenv("MDT_NO_CLUSTER_SPLITK") == nullptr;
+  const bool use_clusters = tc_knobs().cluster_splitk;
   if (TcRecorder* r = tc_recorder()) {
     TcOp op; op.kind = TcOp::GEMM; op.stream = s; op.bn = BN; op.split = kSplit ? 1 : 0; op.epi = kEpi;
     op.M = M; op.N = N; op.K = K; op.nsplit = nsplit; op.use_clusters = use_clusters ? 1 : 0; op.a = a; op.b = b; op.ep = epd;
@@ -1492,10 +1540,8 @@ inline int tc05_launch_t(const CUtensorMap& a, const CUtensorMap& b, int M, int 
   epd.dbg = tc05_dbg_buffer();
   if (epd.dbg) epd.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   // MDT_A_TMEM=1: TF32X3 with the A operand in tensor memory (see Tc05Epi::a_tmem).  Correct, and measured equal in
-  // speed to the shared-memory form (57.4 vs 57.5 us/step): the ~1000-cycle k-block is not bound by the MMAs'
-  // shared-memory reads of A.  Off by default; read per launch (launches happen at graph capture).
-  const char* at = getenv("MDT_A_TMEM");
-  epd.a_tmem = (kSplit && at != nullptr && at[0] == '1') ? 1 : 0;
+  // speed to the shared-memory form (57.4 vs 57.5 us/step): the k-block is not bound by the MMAs' shared-memory reads of A.
+  epd.a_tmem = (kSplit && tc_knobs().a_tmem) ? 1 : 0;
   epd.cluster = (nsplit > 1 && nsplit <= 8 && use_clusters) ? 1 : 0;
   if (epd.cluster) {
     // a cluster needs its CTAs on SMs of one GPC at the same time: when the tiles do not all fit as co-resident
@@ -1531,16 +1577,16 @@ inline int tc05_pick_splits(int M, int N, int K, int bn, int sm_count, const Tc0
   const int kbk = ep.bf16 ? 2 * kTcBK : kTcBK;
   const int total_kb = (K + kbk - 1) / kbk;
   // at least 3 k-blocks per split (4 without the cluster exchange, whose reduction costs ~1.5 us less: measured)
-  const int min_kb = getenv("MDT_MIN_KB_PER_SPLIT") ? atoi(getenv("MDT_MIN_KB_PER_SPLIT"))
-                                                           : (getenv("MDT_NO_CLUSTER_SPLITK") ? 4 : 3);
+  const TcKnobs& kn = tc_knobs();
+  const int min_kb = kn.min_kb > 0 ? kn.min_kb : (kn.cluster_splitk ? 3 : 4);
   int want = total_kb / (min_kb > 0 ? min_kb : 4);
   const int cap = sm_count / tiles;
   if (want > cap) want = cap;
   if (want > 8) want = 8;
-  if (const char* v = getenv("MDT_MAX_SPLITS")) { const int c = atoi(v); if (want > c) want = c; }
+  if (kn.max_splits > 0 && want > kn.max_splits) want = kn.max_splits;
   // Prefer a split count whose clusters are all co-resident (a cluster lives inside one GPC: ~sm_count/8 SMs), as long
   // as that costs at most one split level -- otherwise the launch falls back to the workspace exchange.
-  if (getenv("MDT_NO_CLUSTER_SPLITK") == nullptr && want >= 2) {
+  if (kn.cluster_splitk && want >= 2) {
     const int gpc = sm_count / 8;
     int w = want;
     while (w > 1 && tiles > 8 * (gpc / w)) --w;
@@ -1640,6 +1686,7 @@ struct Tc05Plan {
   bool prefetch_pending = false; // a prefetch was forked in this step and has not been joined yet
   cudaStream_t side_pf = nullptr;
   cudaEvent_t ev_pf_fork = nullptr, ev_pf_join = nullptr;
+  TcKnobs knobs;       // the MDT_* diagnostic switches as they stood when the plan was created
   int preload = 1;     // issue weight-operand TMA loads before the dependency wait (MDT_NO_PRELOAD=1 turns it off)
   PrepArgs last_prep{};
   bool prep_launched = false;
@@ -1689,14 +1736,15 @@ inline void tc05_loss_partials(const Tc05Plan* p, int B, const float** a, int* n
   *a = p->bce_partials;
   // one slot per (fc4 tile, K-split): same split count as tc05_forward's launch of fc4
   int ns = 1;
-  if (!getenv("MDT_NO_SPLITK")) {
+  TcKnobScope knob_scope(&p->knobs);
+  if (p->knobs.splitk) {
     Tc05Epi e{};
     e.ws = p->ws; e.ws_counters = p->ws_counters; e.bf16 = p->b.bf16 ? 1 : 0;
     ns = tc05_pick_splits(B, D, p->b.H, p->bn_fc4, tc05_sms(p), e, Tc05Plan::kWsFloats);
   }
   *na = ((D + p->bn_fc4 - 1) / p->bn_fc4) * ((B + kTcBM - 1) / kTcBM) * ns;
   *b = p->kl_partials;
-  *nb = p->simt_latent ? latent_grid(B, latent_pick_sc(B, tc05_sms(p))) : (B + p->bn_skinny - 1) / p->bn_skinny;
+  *nb = p->simt_latent ? latent_grid(B, latent_pick_sc(B, tc05_sms(p), false, p->knobs.latent_sc)) : (B + p->bn_skinny - 1) / p->bn_skinny;
 }
 
 inline void tc05_destroy(Tc05Plan* p) {
@@ -1738,6 +1786,7 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
   p->bn_skinny = b.Bmax > 1024 ? 64 : (b.Bmax > 256 ? 32 : 16);
   if (const char* v = getenv("MDT_BN_SKINNY")) { const int c = atoi(v); if (c == 16 || c == 32 || c == 64) p->bn_skinny = c; }
   p->preload = getenv("MDT_NO_PRELOAD") == nullptr ? 1 : 0;
+  p->knobs = TcKnobs::from_env();
   const size_t ldB = p->ldB, D = b.D, H = b.H, Z = b.Z;
   struct Item { float** ptr; size_t n; };
   Item items[] = {{&p->xT, D * ldB}, {&p->h1T, H * ldB}, {&p->zT, Z * ldB}, {&p->h3T, H * ldB}, {&p->da4T, D * ldB},
@@ -1836,7 +1885,7 @@ inline int tc05_act_maps(Tc05Plan* p, int B, Tc05ActMaps** out) {
 
 // Split-K factor for a main-stream GEMM of the step (they run one after another, so they share the workspace).
 inline int tc05_splits(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
-  if (getenv("MDT_NO_SPLITK")) return 1;
+  if (!p->knobs.splitk) return 1;
   e.ws = p->ws;
   e.ws_counters = p->ws_counters;
   return tc05_pick_splits(M, N, K, bn, tc05_sms(p), e, Tc05Plan::kWsFloats);
@@ -1845,7 +1894,7 @@ inline int tc05_splits(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn) {
 // Same for the weight-gradient GEMMs, which run on the side stream concurrently with the main-stream GEMMs and
 // therefore own a separate workspace and ticket range.
 inline int tc05_splits_dw(Tc05Plan* p, Tc05Epi& e, int M, int N, int K, int bn, int slot = 0) {
-  if (getenv("MDT_NO_SPLITK")) return 1;
+  if (!p->knobs.splitk) return 1;
   // up to four weight-gradient GEMMs can be in flight at once (one side stream each): every slot owns 4 MB of workspace
   e.ws = p->ws_dw + (size_t)slot * (Tc05Plan::kWsFloats / 2);
   e.ws_counters = p->ws_counters + 2048 + slot * 1024;
@@ -1901,6 +1950,7 @@ inline int tc05_prep(Tc05Plan* p, cudaStream_t s, const float* x, int B, int set
 // otherwise fc4 stops at recon (mdt_forward / eval / decode) and the stand-alone loss kernel may follow.
 inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, const float* eps_in, bool decode_only,
                         bool fuse_loss) {
+  TcKnobScope knob_scope(&p->knobs);
   const Tc05Buffers& b = p->b;
   const bool sp = b.split3;
   const int D = b.D, H = b.H, Z = b.Z;
@@ -1952,12 +2002,12 @@ inline int tc05_forward(Tc05Plan* p, cudaStream_t s, const float* x, int B, cons
       la.dbg = tc05_dbg_buffer();
       if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
       if (TcRecorder* r = tc_recorder()) {
-        TcOp op; op.kind = TcOp::LAT_FWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p));
+        TcOp op; op.kind = TcOp::LAT_FWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p), false, p->knobs.latent_sc);
         la.dbg = nullptr; la.nchunks = (B + op.sc - 1) / op.sc; la.first_live_pass = 1; la.first_pass = 1;
         op.lf = la;
         r->ops.push_back(op);
       } else {
-        MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, tc05_sms(p)), s));
+        MDT_CUDA(launch_latent_fwd(la, latent_pick_sc(B, tc05_sms(p), false, p->knobs.latent_sc), s));
       }
       TC_NOTE(p, "latent_fwd");
     } else {
@@ -2023,12 +2073,12 @@ inline int tc05_latent_bwd(Tc05Plan* p, cudaStream_t s, int B) {
   la.dbg = tc05_dbg_buffer();
   if (la.dbg) la.dbg += 16 * (tc05_dbg_launch_index()++ % 32);
   if (TcRecorder* r = tc_recorder()) {
-    TcOp op; op.kind = TcOp::LAT_BWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p), /*backward=*/true);
+    TcOp op; op.kind = TcOp::LAT_BWD; op.stream = s; op.sc = latent_pick_sc(B, tc05_sms(p), /*backward=*/true, p->knobs.latent_sc);
     la.dbg = nullptr; la.nchunks = (B + op.sc - 1) / op.sc; la.first_live_pass = 1; la.first_pass = 1;
     op.lb = la;
     r->ops.push_back(op);
   } else {
-    MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true), s));
+    MDT_CUDA(launch_latent_bwd(la, latent_pick_sc(B, tc05_sms(p), /*backward=*/true, p->knobs.latent_sc), s));
   }
   TC_NOTE(p, "latent_bwd");
   return MDT_OK;
@@ -2046,6 +2096,7 @@ inline int tc05_join_prefetch(Tc05Plan* p, cudaStream_t s) {
 
 // Backward from da4 / da4^T and dml_kl: fills the flat gradient buffer (weights and biases).
 inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
+  TcKnobScope knob_scope(&p->knobs);
   const Tc05Buffers& b = p->b;
   const bool sp = b.split3;
   const int D = b.D, H = b.H, Z = b.Z, ldB = p->ldB;
@@ -2136,6 +2187,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
 // (one stream each: an update is bound by the SM<->L2 bandwidth of the SMs its tiles run on, so the four should not
 // queue behind each other; narrow tiles -- bn_dwa -- spread each update over more SMs).  The CTA that takes the step's last ticket advances the optimizer state and sums the loss partials.
 inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
+  TcKnobScope knob_scope(&p->knobs);
   const Tc05Buffers& b = p->b;
   const bool sp = b.split3;
   const int D = b.D, H = b.H, Z = b.Z, ldB = p->ldB;
@@ -2157,11 +2209,11 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
   struct Dw { int seg_w, seg_b, M, N, bn, slot; const CUtensorMap *a, *bm; const float* a_src; float* pT; int ldpT; const char* label; int ns; };
   // MDT_W4_SPLIT=1: fc4's update runs apart from its weight-gradient GEMM (adam_tile_kernel, see there)
   // (measured: 60.5 vs 57.4 us/step -- the update's 325 small blocks crowd the SMs the other GEMMs need; kept as a knob)
-  const bool w4_split = getenv("MDT_W4_SPLIT") != nullptr && !b.bf16;
+  const bool w4_split = p->knobs.w4_split && !b.bf16;
   int bn4 = w4_split ? p->bn_dw : bna;
-  if (const char* v = getenv("MDT_BN_DW4")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn4 = c; }
+  if (p->knobs.bn_dw4 == p->bn_dw || p->knobs.bn_dw4 == bna) bn4 = p->knobs.bn_dw4;
   int bn1 = bna;
-  if (const char* v = getenv("MDT_BN_DW1")) { const int c = atoi(v); if (c == p->bn_dw || c == bna) bn1 = c; }
+  if (p->knobs.bn_dw1 == p->bn_dw || p->knobs.bn_dw1 == bna) bn1 = p->knobs.bn_dw1;
   Dw dw[4] = {
       {W4, B4, D, H, bn4, 0, &m->da4T, bn4 == bna ? &m->h3Ta : &m->h3T, p->da4T, p->W4T, D, w4_split ? "fc4_dW" : "fc4_dW_adam", 1},
       // fc3's update writes the transpose into the W3^T set latent_bwd is NOT reading (CUDA-core latent path): see below
@@ -2235,12 +2287,12 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     // No event between fc4's input-gradient GEMM and latent_bwd: a full (event) dependent next to the programmatic
     // one costs latent_bwd its early launch.  All four updates start together once latent_bwd is done -- fc4's is
     // not on the critical path, the last of the other three is.
-    const bool dw4_early = getenv("MDT_DW4_LATE") == nullptr;
+    const bool dw4_early = !p->knobs.dw4_late;
     // fc3's update could start with fc4's, right after fc4's input-gradient GEMM: its operands (da3^T, z^T) are ready,
     // W3 has no reader left in this step, and the updated W3^T goes into the set latent_bwd is not reading.
     // Measured: NOT a gain -- 60.0 vs 58.8 us/step (tf32x3), 48.3 vs 47.5 (bf16): its 4 CTAs and fc4's 91 hold SMs that
     // latent_bwd and then fc1's update want.  Off by default (MDT_DW3_EARLY=1 turns it on).
-    const bool dw3_early = dw4_early && getenv("MDT_DW3_EARLY") != nullptr;
+    const bool dw3_early = dw4_early && p->knobs.dw3_early;
     if (dw4_early) {
       MDT_TRY(after_main(sa, dw3_early ? sb : nullptr));   // E1: W4^T no longer needed, da3^T ready
       MDT_TRY(launch_dw(0, sa));
@@ -2258,7 +2310,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     // fc1's update is the longest of the three: it stays on the main stream, where it is launched programmatically
     // behind latent_bwd and has its set-up (barriers, TMEM, descriptor and parameter fetches: ~2.5 us for an
     // event-launched kernel) done before latent_bwd finishes
-    MDT_TRY(launch_dw(3, getenv("MDT_DW1_SIDE") ? sc : s));
+    MDT_TRY(launch_dw(3, p->knobs.dw1_side ? sc : s));
     if (!dw4_early) MDT_TRY(launch_dw(0, sa));
   } else {
     MDT_TRY(after_main(sa, nullptr));             // E1: W4^T no longer needed, da3^T ready
@@ -2299,6 +2351,8 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
 inline int tc05_linear(const float* x, const float* w, const float* bias, int M, int N, int K, int act, bool split,
                        float* y, cudaStream_t s) {
   MDT_CHECK(K % 4 == 0 && N % 4 == 0, "tcgen05 mdt_linear needs K %% 4 == 0 and N %% 4 == 0 (16-byte rows), got K=%d N=%d", K, N);
+  const TcKnobs knobs = TcKnobs::from_env();     // stand-alone call: no plan, the switches as they stand now
+  TcKnobScope knob_scope(&knobs);
   CUtensorMap ma, mb;
   const int bn = (N > 32) ? 64 : 32;
   MDT_TRY(tc05_encode(&ma, x, M, K, K, kTcBM));

@@ -42,7 +42,7 @@ struct LatentFwdArgs {
   int B, Z, nchunks;
   long long* dbg;                     // optional phase stamps (MDT_TC05_DBG=1), same slot layout as the GEMM kernel's
   int first_live_pass;                // always 1 (a run-time value, so the compiler cannot specialise the two passes)
-  int first_pass;                     // 1: live pass only; 0: a dry run first (MDT_LATENT_DRY=1, for measurements)
+  int first_pass;                     // 1: live pass only; 0: a dry run first (a measurement aid; the launchers pass 1)
 };
 
 struct LatentBwdArgs {
@@ -278,7 +278,7 @@ __device__ __forceinline__ void latent_fwd_body(const LatentFwdArgs& a, const in
       e_pre = gen_eps ? torch_cuda_randn_elem(ph_seed, ph_off, (long long)m0 * Z + threadIdx.x, a.philox_S)
                       : lat_ldg(a.eps_in + (size_t)m0 * Z + threadIdx.x);
   }
-  // (The pass loop below can start with a dry run of the same code before the dependency wait -- MDT_LATENT_DRY=1 --
+  // (The pass loop below can start with a dry run of the same code before the dependency wait -- first_pass = 0 --
   // to pull the instructions into the caches early.  Measured: no gain, the kernel is not fetch-bound; left as a knob.)
   float kl = 0.f;
   bool fw_ok = true;
@@ -506,8 +506,9 @@ __global__ void __launch_bounds__(kLatThreads) latent_bwd_group_kernel(const Lat
 // GPU with fc1's ~78 CTAs, backward with fc4's input-gradient GEMM and then with the 91 CTAs of fc4's weight-gradient
 // GEMM on the side stream -- measured at B = 128: forward 4.2 / 3.3 / 4.6 us for 1 / 2 / 4 samples per CTA, backward
 // 12.3 / 10.0 / 4.2 us (with 1 or 2 the last CTAs queue behind the weight-gradient GEMM).
-inline int latent_pick_sc(int B, int sm_count, bool backward = false) {
-  if (const char* v = getenv("MDT_LATENT_SC")) { const int c = atoi(v); if (c == 1 || c == 2 || c == 4) return c; }
+// `forced`: MDT_LATENT_SC as read when the plan was created (0 = choose)
+inline int latent_pick_sc(int B, int sm_count, bool backward = false, int forced = 0) {
+  if (forced == 1 || forced == 2 || forced == 4) return forced;
   const int room = backward ? sm_count / 3 : sm_count / 2;
   return B <= room ? 1 : (B <= 2 * room ? 2 : 4);
 }
@@ -534,7 +535,7 @@ inline cudaError_t launch_latent_fwd_z(const LatentFwdArgs& a, int sc, dim3 grid
 inline cudaError_t launch_latent_fwd(LatentFwdArgs a, int sc, cudaStream_t s) {
   a.nchunks = (a.B + sc - 1) / sc;
   a.first_live_pass = 1;
-  a.first_pass = getenv("MDT_LATENT_DRY") ? 0 : 1;
+  a.first_pass = 1;      // (0 would add a dry run of the pass before the dependency wait: measured no gain, see latent_fwd_kernel)
   const dim3 grid(latent_grid(a.B, sc));
   const size_t smem = (size_t)sc * a.H * sizeof(float);
   return a.Z <= 20 ? launch_latent_fwd_z<5>(a, sc, grid, smem, s) : launch_latent_fwd_z<8>(a, sc, grid, smem, s);
@@ -550,7 +551,7 @@ inline cudaError_t launch_latent_bwd_z(const LatentBwdArgs& a, int sc, dim3 grid
 inline cudaError_t launch_latent_bwd(LatentBwdArgs a, int sc, cudaStream_t s) {
   a.nchunks = (a.B + sc - 1) / sc;
   a.first_live_pass = 1;
-  a.first_pass = getenv("MDT_LATENT_DRY") ? 0 : 1;
+  a.first_pass = 1;      // (0 would add a dry run of the pass before the dependency wait: measured no gain, see latent_fwd_kernel)
   const dim3 grid(latent_grid(a.B, sc));
   const size_t smem = (size_t)sc * a.H * sizeof(float);
   return a.Z <= 20 ? launch_latent_bwd_z<5>(a, sc, grid, smem, s) : launch_latent_bwd_z<8>(a, sc, grid, smem, s);

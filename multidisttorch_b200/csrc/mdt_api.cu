@@ -116,6 +116,8 @@ struct mdt_engine {
   int sm_share_pending = 1;
   // diagnostic switches, read from the environment once when the engine is created
   bool opt_fused_adam = true, opt_nccl_in_graph = true, opt_zerocopy = true, opt_h2d_prefetch = true;
+  bool opt_pipeline = true, opt_graph_reduce = true, opt_graph_dbg = false;
+  int opt_steps_per_graph = 16;
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
   volatile unsigned int* err_word = nullptr;        // pinned word the exchange kernels set when a peer never answered
   float* loss_hist = nullptr;                       // device ring of the last kLossHist per-step losses
@@ -444,12 +446,11 @@ int run_cached(mdt_engine* e, int kind, int B, int flag, F fn) {
       return r;
     }
     if (ce != cudaSuccess) return set_error(MDT_ERR_CUDA, "cudaStreamEndCapture: %s", cudaGetErrorString(ce));
-    static const bool reduce_on = getenv("MDT_NO_GRAPH_REDUCE") == nullptr;
-    if (reduce_on) {
+    if (e->opt_graph_reduce) {
       int removed = 0;
       const int rr = reduce_graph_edges(g, &removed);
       if (rr != MDT_OK) { cudaGraphDestroy(g); return rr; }
-      if (getenv("MDT_GRAPH_DBG")) fprintf(stderr, "[mdt] graph kind %d B %d: %lld kernels, %d redundant edges removed\n", kind, B, kernels, removed);
+      if (e->opt_graph_dbg) fprintf(stderr, "[mdt] graph kind %d B %d: %lld kernels, %d redundant edges removed\n", kind, B, kernels, removed);
     }
     cudaGraphExec_t ex = nullptr;
     ce = cudaGraphInstantiate(&ex, g, 0);
@@ -724,6 +725,10 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   e->opt_nccl_in_graph = !(getenv("MDT_NCCL_GRAPH") && getenv("MDT_NCCL_GRAPH")[0] == '0');
   e->opt_zerocopy = getenv("MDT_NO_ZEROCOPY") == nullptr;
   e->opt_h2d_prefetch = getenv("MDT_NO_H2D_PREFETCH") == nullptr;
+  e->opt_pipeline = getenv("MDT_NO_PIPELINE") == nullptr;
+  e->opt_graph_reduce = getenv("MDT_NO_GRAPH_REDUCE") == nullptr;
+  e->opt_graph_dbg = getenv("MDT_GRAPH_DBG") != nullptr;
+  if (const char* v = getenv("MDT_STEPS_PER_GRAPH")) e->opt_steps_per_graph = atoi(v);
   e->exchange = cfg->exchange;
   if (const char* v = getenv("MDT_P2P_TWO_SHOT_FROM")) e->two_shot_from = atoi(v);
   if (const char* v = getenv("MDT_P2P_TWO_SHOT_BYTES")) e->two_shot_bytes = atoll(v);
@@ -1089,8 +1094,7 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   p->src_pool = src->x_pool; p->src_images = src->x_pool ? nullptr : src->images_u8;
   p->src_indices = reinterpret_cast<const long long*>(src->indices);
   p->src_n_batches = src->n_batches; p->src_n_images = src->n_images;
-  static const int unroll_env = getenv("MDT_STEPS_PER_GRAPH") ? atoi(getenv("MDT_STEPS_PER_GRAPH")) : 16;
-  int U = unroll_env < 1 ? 1 : (unroll_env > 32 ? 32 : unroll_env);
+  int U = e->opt_steps_per_graph < 1 ? 1 : (e->opt_steps_per_graph > 32 ? 32 : e->opt_steps_per_graph);
   if (U > 1 && (U & 1)) ++U;                         // a multi-step graph must leave the two-set parities where it found them
   // NCCL with DDP's two buckets (large gradients): one step per graph, the form that has run on 4 and 8 GPUs since
   // round 1 -- sixteen steps' worth of bucketed all-reduces in ONE capture failed inside ncclAllReduce ("unhandled
@@ -1117,8 +1121,7 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   // Pipelined steps (CUDA-core latent path): no prologue kernel inside the step -- each step fetches its successor's
   // batch into the other input set while it runs.  Only the first step of a call that does not continue the previous
   // one needs its batch fetched up front.
-  static const bool pipeline_on = getenv("MDT_NO_PIPELINE") == nullptr;
-  const bool piped = pipeline_on && p->simt_latent && !e->prof_on;
+  const bool piped = e->opt_pipeline && p->simt_latent && !e->prof_on;
   if (piped) {
     const bool primed = e->primed && same_src && e->primed_cursor >= 0 && (e->primed_cursor - first_batch) % src->n_batches == 0;
     if (!primed) rc = tc05_prep(p, e->stream, e->x_stage, batch, p->xpar, false, 0, "prep_xT");
@@ -1206,7 +1209,7 @@ int mdt_train_step_host_submit(mdt_engine* e, const float* x_host, int batch, co
                         at.devicePointer != nullptr;
     cudaGetLastError();
     int slot = -1;
-    static const bool ahead_on = getenv("MDT_NO_PIPELINE") == nullptr;
+    const bool ahead_on = e->opt_pipeline;
     const unsigned int last_pub = e->pub_expected;
     const bool in_flight = last_pub != 0 && (unsigned int)(e->mailbox[last_pub & 63u] >> 32) != last_pub;
     if (mapped && in_flight && ahead_on && e->opt_h2d_prefetch && e->copy_stream != nullptr && e->tc->simt_latent) {
