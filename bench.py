@@ -64,7 +64,7 @@ def parse_args():
     ap.add_argument("--no-parity", action="store_true")
     ap.add_argument("--no-eager", action="store_true", help="skip the torch-CUDA eager run of the reference step")
     ap.add_argument("--cpu-seconds", type=float, default=10.0, help="budget of the cpu_baseline sample")
-    ap.add_argument("--max-seconds", type=float, default=1200.0,
+    ap.add_argument("--max-seconds", type=float, default=600.0,
                     help="watchdog: after this long rank 0 prints what it has (\"incomplete\" set) and every rank exits")
     ap.add_argument("--ref-worker", default="", help=argparse.SUPPRESS)
     ap.add_argument("--eager-worker", default="", help=argparse.SUPPRESS)
