@@ -93,6 +93,10 @@ struct StepState {
   long long x_cursor;                // mdt_train_steps: index of the batch the NEXT step reads from the caller's pool /
                                      // index table; advanced once per published step
   float* loss_hist;                  // ring of kLossHist per-step losses (slot = (published step count - 1) % kLossHist)
+  long long x_cursor_pf;             // index of the next batch the staging kernel fetches AHEAD (pipelined steps).  Only
+                                     // staging kernels write it, so its value does not depend on whether the running
+                                     // step has already published (and advanced x_cursor) when the fetch executes
+  unsigned int ticket_prep;          // "last block done" counter of the staging kernel (self-resetting)
 };
 constexpr unsigned int kLossHist = 4096;
 

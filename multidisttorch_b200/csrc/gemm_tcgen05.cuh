@@ -1314,10 +1314,14 @@ __device__ __forceinline__ void prep_body(const PrepArgs& a, const int bx, const
     const int r0 = (tile / job.tiles_c) * 32, c0 = (tile % job.tiles_c) * 32;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
     const bool sourced = a.pool != nullptr || a.images != nullptr;
-    long long bidx = 0;
+    long long bidx = 0, cur_next = 0;
     if (sourced) {
-      bidx = (a.st->x_cursor + a.cursor_add) % a.n_batches;
+      // this step's batch (x_cursor), or -- fetched ahead while a step runs -- the one after the last staged batch
+      // (x_cursor_pf): the running step's last CTA advances x_cursor at an unknown time relative to this kernel
+      const long long cur = a.cursor_add ? a.st->x_cursor_pf : a.st->x_cursor;
+      bidx = cur % a.n_batches;
       if (a.pool != nullptr) job.in = a.pool + (size_t)bidx * job.R * job.C;
+      cur_next = cur + 1;
     }
 #pragma unroll
     for (int i = ty; i < 32; i += 8) {
@@ -1338,6 +1342,14 @@ __device__ __forceinline__ void prep_body(const PrepArgs& a, const int bx, const
     }
     __syncthreads();
     tr_store_tile(job, t, r0, c0, tx, ty);
+    if (sourced && threadIdx.x == 0) {       // every block has read its cursor by the time the last ticket is taken
+      __threadfence();
+      if (atomicAdd(&a.st->ticket_prep, 1u) == (unsigned)a.tr_blocks - 1u) {
+        a.st->x_cursor_pf = cur_next;
+        a.st->ticket_prep = 0;
+        __threadfence();
+      }
+    }
     return;
   }
   const unsigned long long seed = a.st->philox_seed, offset = a.st->philox_offset;
