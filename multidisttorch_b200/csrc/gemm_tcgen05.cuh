@@ -1698,6 +1698,14 @@ struct Tc05Plan {
   bool prefetch_pending = false; // a prefetch was forked in this step and has not been joined yet
   cudaStream_t side_pf = nullptr;
   cudaEvent_t ev_pf_fork = nullptr, ev_pf_join = nullptr;
+  // Steps whose optimizer is a separate kernel (DDP groups, SGD): the transposed weight shadows it has to refresh are
+  // first read by the NEXT step's fc4 input-gradient GEMM, four kernels into that step.  Inside a multi-step graph the
+  // refresh therefore runs on a side stream and is joined right before that GEMM instead of sitting between the
+  // optimizer and the next step's first GEMM (fp32-operand modes only: bf16 also refreshes the operand copies the very
+  // next GEMM reads).  The last step of a capture refreshes in line.
+  cudaStream_t side_wt = nullptr;
+  cudaEvent_t ev_wt_fork = nullptr, ev_wt_join = nullptr;
+  bool defer_shadows = false, shadows_pending = false;
   TcKnobs knobs;       // the MDT_* diagnostic switches as they stood when the plan was created
   int preload = 1;     // issue weight-operand TMA loads before the dependency wait (MDT_NO_PRELOAD=1 turns it off)
   PrepArgs last_prep{};
@@ -1734,7 +1742,24 @@ inline int tc05_weight_shadows(Tc05Plan* p, cudaStream_t s) {
   return MDT_OK;
 }
 
-inline int tc05_params_changed(Tc05Plan* p, cudaStream_t s) { return tc05_weight_shadows(p, s); }
+inline int tc05_params_changed(Tc05Plan* p, cudaStream_t s) {
+  if (p->defer_shadows && !p->b.bf16) {
+    MDT_CUDA(tc_event_record(p->ev_wt_fork, s));
+    MDT_CUDA(tc_stream_wait(p->side_wt, p->ev_wt_fork));
+    MDT_TRY(tc05_weight_shadows(p, p->side_wt));
+    MDT_CUDA(tc_event_record(p->ev_wt_join, p->side_wt));
+    p->shadows_pending = true;
+    return MDT_OK;
+  }
+  return tc05_weight_shadows(p, s);
+}
+// Before the first kernel of a step that reads a transposed weight shadow.
+inline int tc05_join_shadows(Tc05Plan* p, cudaStream_t s) {
+  if (!p->shadows_pending) return MDT_OK;
+  MDT_CUDA(tc_stream_wait(s, p->ev_wt_join));
+  p->shadows_pending = false;
+  return MDT_OK;
+}
 
 inline int tc05_sms(const Tc05Plan* p) {
   const int n = p->b.sm_count / (p->sm_share > 0 ? p->sm_share : 1);
@@ -1763,6 +1788,9 @@ inline void tc05_destroy(Tc05Plan* p) {
   if (!p) return;
   if (p->side) cudaStreamDestroy(p->side);
   if (p->side_pf) cudaStreamDestroy(p->side_pf);
+  if (p->side_wt) cudaStreamDestroy(p->side_wt);
+  if (p->ev_wt_fork) cudaEventDestroy(p->ev_wt_fork);
+  if (p->ev_wt_join) cudaEventDestroy(p->ev_wt_join);
   if (p->ev_pf_fork) cudaEventDestroy(p->ev_pf_fork);
   if (p->ev_pf_join) cudaEventDestroy(p->ev_pf_join);
   for (cudaStream_t st : {p->side2, p->side3, p->side4}) if (st) cudaStreamDestroy(st);
@@ -1826,7 +1854,10 @@ inline int tc05_create(const Tc05Buffers* bufs, cudaStream_t s, Tc05Plan** out) 
     for (auto& it : items16) { *it.ptr = reinterpret_cast<__nv_bfloat16*>(q); q += (it.n * sizeof(__nv_bfloat16) + 255) / 256 * 256; }
   p->x_stage_set[0] = b.x_stage; p->xT_set[0] = p->xT; p->W3T_set[0] = p->W3T; p->x16_set[0] = p->x16;
   int r = MDT_OK;
-  if (cudaStreamCreateWithFlags(&p->side_pf, cudaStreamNonBlocking) != cudaSuccess ||
+  if (cudaStreamCreateWithFlags(&p->side_wt, cudaStreamNonBlocking) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_wt_fork, cudaEventDisableTiming) != cudaSuccess ||
+      cudaEventCreateWithFlags(&p->ev_wt_join, cudaEventDisableTiming) != cudaSuccess ||
+      cudaStreamCreateWithFlags(&p->side_pf, cudaStreamNonBlocking) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_pf_fork, cudaEventDisableTiming) != cudaSuccess ||
       cudaEventCreateWithFlags(&p->ev_pf_join, cudaEventDisableTiming) != cudaSuccess)
     r = set_error(MDT_ERR_CUDA, "prefetch stream");
@@ -2137,6 +2168,7 @@ inline int tc05_backward(Tc05Plan* p, cudaStream_t s, const float* x, int B) {
   MDT_TRY(tc05_launch<EPI_GRADW>(p->bn_dw, sp, m->da4T, m->h3T, D, H, B, e, sw, tc05_splits_dw(p, e, D, H, B, p->bn_dw)));
   TC_NOTE(p, "fc4_dW");
   if (b.bucket_ready) MDT_TRY(b.bucket_ready(b.note_ctx, 0, sw));   // fc4.weight + fc4.bias gradients: DDP's first bucket
+  MDT_TRY(tc05_join_shadows(p, s));               // W4^T (and, further down, W3^T / W2x^T) refreshed by the previous step
   e = Tc05Epi{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update
@@ -2289,6 +2321,7 @@ inline int tc05_backward_fused_adam(Tc05Plan* p, cudaStream_t s, int B) {
     }
     return MDT_OK;
   };
+  MDT_TRY(tc05_join_shadows(p, s));
   Tc05Epi e{};
   e.C = b.da3; e.ldc = H; e.CT = p->da3T; e.ldct = ldB; e.mask = b.h3; e.ldmask = H;
   e.pre_b = p->preload;                          // W4^T: the shadow was last written by the previous step's update

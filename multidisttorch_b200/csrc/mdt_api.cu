@@ -590,7 +590,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
   const bool w3_flips = e->tc != nullptr && e->tc->simt_latent && e->gsize == 1 && e->opt_fused_adam && !e->use_sgd;
   struct ParityAfter {       // a replayed graph does not run the enqueue code that flips the parities: set them here
     mdt_engine* e; int x, w;
-    ~ParityAfter() { if (e->tc) { e->tc->xpar = x; e->tc->w3par = w; e->tc->prefetch_pending = false; } }
+    ~ParityAfter() { if (e->tc) { e->tc->xpar = x; e->tc->w3par = w; e->tc->prefetch_pending = false; e->tc->shadows_pending = false; } }
   } parity_after{e, piped && !e->tc->no_prefetch ? (x0 ^ ((steps - (tail_no_prefetch ? 1 : 0)) & 1)) : (piped ? x0 : 0),
                  w3_flips ? (w0 ^ (steps & 1)) : w0};
   const int fl = (eps != nullptr ? 1 : 0) | ((e->tc ? e->tc->sm_share : 1) << 1) | (steps << 8) | (x0 << 20) | (w0 << 21) |
@@ -628,7 +628,9 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
         const bool tail = piped && tail_no_prefetch && i == steps - 1;
         const bool saved = e->tc->no_prefetch;
         if (tail) e->tc->no_prefetch = true;
+        e->tc->defer_shadows = i < steps - 1;        // a later step of this capture joins the refresh (tc05_join_shadows)
         const int rc = one();
+        e->tc->defer_shadows = false;
         e->tc->no_prefetch = saved;
         MDT_TRY(rc);
       }

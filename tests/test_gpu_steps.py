@@ -157,3 +157,22 @@ def test_grouped_trials_equal_trials_stepped_alone(E, mode, T):
     grp.close()
     for e in grouped + alone:
         e.close()
+
+
+@pytest.mark.parametrize("mode", ["tf32x3", "bf16"])
+def test_train_steps_with_a_separate_optimizer_kernel_equal_single_steps(E, mode, monkeypatch):
+    """Steps whose optimizer is its own kernel (what DDP groups and SGD run; forced here on one GPU with
+    MDT_NO_FUSED_ADAM=1): inside a multi-step graph the refresh of the transposed weight shadows is moved to a side
+    stream and joined before the next step's first reader.  Must stay bit-identical to single steps."""
+    monkeypatch.setenv("MDT_NO_FUSED_ADAM", "1")
+    B = 64
+    a, b = pair(E, mode, B)
+    pool = torch.rand(6, B, 784, generator=torch.Generator().manual_seed(77)).cuda()
+    n = 37
+    losses = torch.zeros(n, device="cuda")
+    a.train_steps(pool, 1, n, losses)
+    want = [float(b.train_step(pool[(1 + i) % 6], None).item()) for i in range(n)]
+    a.synchronize()
+    assert losses.cpu().tolist() == want
+    assert torch.equal(a.params, b.params) and torch.equal(a.exp_avg, b.exp_avg)
+    a.close(); b.close()
