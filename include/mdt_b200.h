@@ -250,7 +250,12 @@ int mdt_engine_launch_count(mdt_engine* e, int64_t* kernels);
  * gradient into the exchange region, and one kernel per rank waits for its peers' "ready" flags, sums the n partial
  * gradients in rank order (own from local memory, the others over NVLink), stores the sum into the bound gradient
  * buffer and applies Adam.  Errors: MDT_ERR_CUDA when a peer's region cannot be mapped (no peer access) -- the caller
- * then simply keeps the NCCL path. */
+ * then simply keeps the NCCL path.
+ * One engine per GPU at a time on this path: the exchange kernel keeps all its blocks resident while it waits for the
+ * peers, which leaves no room for another engine's GEMMs on the same GPU.  Two engines whose exchanges are in flight
+ * together (in different orders on different ranks) therefore stall each other until the bounded wait expires; the
+ * reference never does this (one trial per group at a time, ref:vae-hpo.py:200-202) -- synchronise one engine before
+ * stepping the next, or give concurrent engines MDT_EXCHANGE_NCCL. */
 int mdt_engine_exchange_handle(mdt_engine* e, void* handle64);
 int mdt_engine_set_peers(mdt_engine* e, const void* handles64, int n);
 /* *enabled: 1 once mdt_engine_set_peers succeeded; *timed_out: 1 if a bounded wait on a peer's flag ever expired (a

@@ -1,6 +1,11 @@
 """A DDP group stepped through mdt_train_steps (16-step graphs: staged-ahead batches, weight-shadow refresh on a side
 stream) against the same group stepped one mdt_train_step at a time: parameters must be bit-identical, on every rank and
-across ranks, for every exchange.  torchrun --nproc-per-node N scripts/ddp_multistep_check.py"""
+across ranks, for every exchange.  torchrun --nproc-per-node N scripts/ddp_multistep_check.py
+
+The two engines are stepped ONE AFTER THE OTHER (synchronize + barrier in between): the peer-memory exchange kernels
+spin with every block resident, so two of them in flight on the same GPUs in different orders on different ranks
+starve each other's GEMMs until the bounded wait (30 s) expires and flags the step.  The first version of this script
+did not do that, and its one 2-GPU run (round 2) reported False for tf32x3/p2p after such a stall; tf32x3/nccl: True."""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
@@ -21,6 +26,7 @@ for mode in ("tf32x3", "bf16"):
             engs.append(e)
         a, b = engs
         a.train_steps(pool, 2, 37)
+        a.synchronize(); dist.barrier(group=g)
         for i in range(37):
             b.train_step(pool[(2 + i) % 5], None, want_loss=False)
         a.synchronize(); b.synchronize()
