@@ -13,6 +13,9 @@ CUDA box) replaces those two names with factories that
   ``EngineModule`` / ``EngineAdam`` pair backed by ONE ``VAEEngine``;
 * fall through to the real torch classes for anything else.
 
+``torch.optim.SGD`` over the wrapped model's parameters becomes ``EngineSGD`` (the engine's flat SGD kernel; the
+reference itself only builds Adam).
+
 ``torch.utils.data.DataLoader`` gets the same treatment for the reference's two MNIST loaders
 (ref:vae-hpo.py:148-158): a device-resident loader that yields bit-identical batches without the host pipeline.
 
@@ -134,8 +137,11 @@ class EngineModule(nn.Module):
             eng.grads.copy_(old.grads)
             t, _ = old.state()
             eng.params_changed()
-            lr, betas, eps = getattr(self, "_adam_h", (1e-3, (0.9, 0.999), 1e-8))
-            eng.set_adam(lr, betas, eps, completed_steps=t)
+            if getattr(self, "_sgd_h", None) is not None:
+                eng.set_sgd(*self._sgd_h, completed_steps=t)
+            else:
+                lr, betas, eps = getattr(self, "_adam_h", (1e-3, (0.9, 0.999), 1e-8))
+                eng.set_adam(lr, betas, eps, completed_steps=t)
             old.close()
         self.engine = eng
         # the script's parameters become views of the flat buffers (so decode(), state_dict(), .grad keep working)
@@ -239,7 +245,7 @@ class EngineAdam:
             lr, betas, eps = cfg.lr, cfg.betas, cfg.eps
         self.defaults = dict(lr=lr, betas=betas, eps=eps, weight_decay=0, amsgrad=False)
         self.param_groups = [dict(self.defaults, params=list(owner.module.parameters()))]
-        owner._adam_h = (lr, betas, eps)
+        owner._adam_h, owner._sgd_h = (lr, betas, eps), None
         owner.engine.set_adam(lr, betas, eps, 0)
 
     def zero_grad(self, set_to_none=True):
@@ -254,6 +260,65 @@ class EngineAdam:
         eng = self.owner.engine
         return {"step": t, "exp_avg": eng.exp_avg.clone(), "exp_avg_sq": eng.exp_avg_sq.clone(),
                 "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
+
+
+class EngineSGD:
+    """Stands where ``optim.SGD(model.parameters(), lr, momentum, dampening, weight_decay, nesterov)`` would stand
+    (BASELINE north_star (c); the reference itself instantiates Adam, ref:vae-hpo.py:131).  ``step()`` is the flat SGD
+    kernel (mdt_engine_set_sgd + mdt_adam_step); the engine's exp_avg buffer holds the momentum buffer."""
+
+    def __init__(self, owner, lr, momentum, dampening, weight_decay, nesterov):
+        self.owner = owner
+        from . import hpo
+        if hpo.overridden():           # MDT_HPO_LR applies to whichever optimizer the script builds
+            lr = hpo.trial_config(hpo.group_index(owner.process_group), lr=lr).lr
+        self.defaults = dict(lr=lr, momentum=momentum, dampening=dampening, weight_decay=weight_decay, nesterov=nesterov)
+        self.param_groups = [dict(self.defaults, params=list(owner.module.parameters()))]
+        owner._sgd_h = (lr, momentum, dampening, weight_decay, nesterov)
+        owner.engine.exp_avg.zero_()   # torch creates the momentum buffer on the first step
+        owner.engine.set_sgd(lr, momentum, dampening, weight_decay, nesterov, completed_steps=0)
+
+    def zero_grad(self, set_to_none=True):
+        pass
+
+    def step(self, closure=None):
+        self.owner.engine.adam_step()      # the engine's optimizer step: SGD once set_sgd was called
+        return None
+
+    def state_dict(self):
+        t, _ = self.owner.engine.state()
+        return {"step": t, "momentum_buffer": self.owner.engine.exp_avg.clone(),
+                "param_groups": [{k: v for k, v in self.param_groups[0].items() if k != "params"}]}
+
+
+def _engine_owner(plist):
+    """The EngineModule whose ten parameters `plist` is, or None."""
+    if not plist or isinstance(plist[0], dict):
+        return None
+    owners = {id(_ENGINE_OF_PARAM.get(id(p))) for p in plist}
+    owner = _ENGINE_OF_PARAM.get(id(plist[0]))
+    return owner if owner is not None and len(owners) == 1 and len(plist) == 10 else None
+
+
+def _make_sgd_shim(orig_sgd):
+    class SGD(orig_sgd):
+        def __new__(cls, params=None, lr=1e-3, momentum=0, dampening=0, weight_decay=0, nesterov=False, **kwargs):
+            plist = list(params) if params is not None else []
+            if cls is SGD:
+                owner = _engine_owner(plist)
+                plain = (owner is not None and not kwargs and not isinstance(lr, torch.Tensor)
+                         and not (nesterov and (momentum <= 0 or dampening != 0)))     # torch raises for that one itself
+                if plain:
+                    return EngineSGD(owner, float(lr), float(momentum), float(dampening), float(weight_decay), bool(nesterov))
+            obj = super().__new__(cls)
+            obj._mdt_params = plist          # a generator argument was consumed above: hand the list to __init__
+            return obj
+
+        def __init__(self, params=None, *args, **kwargs):
+            super().__init__(self.__dict__.pop("_mdt_params", params), *args, **kwargs)
+
+    SGD.__qualname__ = SGD.__name__ = "SGD"
+    return SGD
 
 
 class DeviceLoader:
@@ -385,7 +450,8 @@ def _make_loader_shim(orig_loader):
 
 
 def install():
-    """Patch torch.nn.parallel.DistributedDataParallel and torch.optim.Adam (idempotent)."""
+    """Patch torch.nn.parallel.DistributedDataParallel, torch.optim.Adam / SGD and torch.utils.data.DataLoader
+    (idempotent)."""
     if _ORIG or not torch.cuda.is_available():
         return False
     _ORIG["ddp"] = torch.nn.parallel.DistributedDataParallel
@@ -393,6 +459,8 @@ def install():
     ddp, adam = _make_shims(_ORIG["ddp"], _ORIG["adam"])
     torch.nn.parallel.DistributedDataParallel = ddp
     torch.optim.Adam = adam
+    _ORIG["sgd"] = torch.optim.SGD
+    torch.optim.SGD = _make_sgd_shim(_ORIG["sgd"])
     _ORIG["loader"] = _tud.DataLoader
     _tud.DataLoader = _make_loader_shim(_ORIG["loader"])
     return True
@@ -403,5 +471,7 @@ def uninstall():
         return
     torch.nn.parallel.DistributedDataParallel = _ORIG.pop("ddp")
     torch.optim.Adam = _ORIG.pop("adam")
+    if "sgd" in _ORIG:
+        torch.optim.SGD = _ORIG.pop("sgd")
     if "loader" in _ORIG:
         _tud.DataLoader = _ORIG.pop("loader")
