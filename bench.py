@@ -662,6 +662,7 @@ def run_own(args):
     # ---- other group layouts (gradient exchange inside each group), BASELINE configs 4 and 5, metric #2
     layouts = {f"{world}x1": round(value, 1)}
     layouts_bf16, exchanges, allreduce, config5 = None, None, None, None
+    multistep = {}
     if world > 1 and not args.no_layouts:
         exchanges = {}
         if _has_bf16():
@@ -682,6 +683,60 @@ def run_own(args):
                     return round(world * B / (ms2 * 1e-3), 1)
                 finally:
                     e2.close()
+
+            def multistep_check(mode, xch, n=37):
+                """mdt_train_steps (multi-step graphs) against the same batches stepped one mdt_train_step at a time,
+                on this layout's groups: parameters and moments bit-identical on every rank and across the ranks of a
+                group, no expired peer wait.  The two engines are stepped ONE AFTER THE OTHER (synchronize + barrier):
+                two peer-memory engines of a group in flight together starve each other (include/mdt_b200.h)."""
+                a = new_engine(mode, group=mine, seed=1234 + rank // k, exchange=xch)
+                if xch in ("p2p", "p2p_two_shot") and not a.p2p:
+                    a.close()
+                    return None
+                b = new_engine(mode, group=mine, seed=1234 + rank // k, exchange=xch)
+                same = True
+                try:
+                    try:
+                        a.train_steps(pool, 3, n)
+                        a.synchronize()
+                    except Exception as exc:      # noqa: BLE001 -- every rank must still reach the collectives below
+                        sys.stderr.write(f"[bench] rank {rank}: multistep_check {name}/{xch} (multi-step leg): {exc}\n")
+                        same = False
+                    dist.barrier()
+                    try:
+                        for i in range(n):
+                            b.train_step(pool[(3 + i) % POOL_BATCHES], None, want_loss=False)
+                        b.synchronize()
+                        same = (same and torch.equal(a.params, b.params) and torch.equal(a.exp_avg, b.exp_avg)
+                                and torch.equal(a.exp_avg_sq, b.exp_avg_sq)
+                                and not a.exchange_status()[1] and not b.exchange_status()[1])
+                    except Exception as exc:      # noqa: BLE001
+                        sys.stderr.write(f"[bench] rank {rank}: multistep_check {name}/{xch} (single-step leg): {exc}\n")
+                        same = False
+                    got = [torch.empty_like(a.params) for _ in range(k)]
+                    dist.all_gather(got, a.params.clone(), group=mine)
+                    same = same and all(torch.equal(got[0], t) for t in got)
+                    flag = torch.tensor([1 if same else 0], device=device)
+                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+                    return "ok" if int(flag.item()) == 1 else "FAIL"
+                finally:
+                    a.close()
+                    b.close()
+
+            if not args.no_parity:
+                chk = {}
+                for xch in ("p2p", "p2p_two_shot", "nccl"):
+                    r_ = section(f"multistep_parity/{name}/{xch}", lambda: multistep_check(args.gemm_mode, xch))
+                    if r_ is not None:
+                        chk[xch] = r_
+                if any(chk.get(x) == "FAIL" for x in ("p2p", "p2p_two_shot")):
+                    # every rank sees the same (world-reduced) verdict: peer-memory groups are timed on the form the
+                    # golden replays check, one step per call
+                    os.environ["MDT_P2P_SINGLE_STEPS"] = "1"
+                    chk["note"] = "peer-memory groups timed with MDT_P2P_SINGLE_STEPS=1 from here on"
+                multistep[name] = chk
+                if rank == 0:
+                    _PARTIAL.update({"multistep_parity": multistep})
 
             per = {}
             for xch in ("p2p", "p2p_two_shot", "nccl"):
@@ -749,7 +804,7 @@ def run_own(args):
                        "one_call_per_step_ms": ms_call, "one_call_per_step_value": round(world * B / (ms_call * 1e-3), 1)},
             "clocks": clk, "e2e": e2e, "gpu_launches": int(total_launches),
             "gpu_launches_per_step": round(total_launches / (world * R * n_region), 2), "roofline": roofline,
-            "cpu_baseline": cpu_baseline, "ddp_parity": parity, "layouts": layouts, "layouts_bf16": layouts_bf16,
+            "cpu_baseline": cpu_baseline, "ddp_parity": parity, "multistep_parity": multistep or None, "layouts": layouts, "layouts_bf16": layouts_bf16,
             "exchanges": exchanges, "allreduce": allreduce, "config5": config5, "modes": modes,
             "trials_per_gpu": multi_trial, "trials_per_gpu_grouped": multi_trial_grouped, "trials_per_gpu_streams": multi_trial_streams, "torch_cuda_eager": eager, "compat_mode": compat, "unchanged_script": script_e2e,
             "kernels": kernels,

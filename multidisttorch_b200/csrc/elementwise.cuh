@@ -575,10 +575,13 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a
               omb2 = a.st->next[4], eps = a.st->next[5];
   const unsigned int t = a.st->xch_seq + 1u;          // bumped by the last block, after every block has read it
   const float gs = a.grad_scale;
+  // An exchange of this engine that already timed out is not waited for again: the steps still queued behind it (a
+  // multi-step graph holds up to 32) then fail at once instead of after another 30 s each.
+  const bool dead = a.st->xch_error != 0u;
   __shared__ int peers_ok;
-  if (threadIdx.x == 0) peers_ok = 1;
+  if (threadIdx.x == 0) peers_ok = dead ? 0 : 1;
   __syncthreads();
-  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
+  if (!dead && threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
     if (blockIdx.x == 0) {                            // this rank's gradient is complete (the kernel is stream-ordered
       __threadfence_system();                         // behind its weight-gradient GEMMs): tell peer threadIdx.x
       st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
@@ -634,7 +637,8 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allreduce_kernel(AdamArgs a
       __threadfence_system();
       for (int r = 0; r < pa.n; ++r)                  // every block of this rank has finished reading the peers' buffers
         if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
-      for (int r = 0; r < pa.n; ++r)
+      const bool gave_up = *reinterpret_cast<volatile unsigned int*>(&a.st->xch_error) != 0u;   // now or in an earlier step
+      for (int r = 0; r < pa.n && !gave_up; ++r)
         if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) flag_exchange_error(a.st);
     }
   }
@@ -650,7 +654,8 @@ __global__ void __launch_bounds__(kAdamThreads) p2p_reduce_slice_kernel(PeerArgs
   pdl_wait();
   pdl_trigger();
   const unsigned int t = st->xch_seq + 1u;            // bumped by the Adam kernel that follows
-  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
+  const bool dead = st->xch_error != 0u;              // an earlier exchange timed out: no further waits (see adam_allreduce_kernel)
+  if (!dead && threadIdx.x < pa.n && (int)threadIdx.x != pa.me) {
     if (blockIdx.x == 0) {
       __threadfence_system();
       st_release_sys(pa.flags[threadIdx.x] + pa.me, t);
@@ -690,10 +695,11 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allgather_kernel(AdamArgs a
               omb2 = a.st->next[4], eps = a.st->next[5];
   const unsigned int t = a.st->xch_seq + 1u;
   const float gs = a.grad_scale;
+  const bool dead = a.st->xch_error != 0u;            // (set by the reduce-slice kernel just before, or by an earlier step)
   __shared__ int peers_ok;
-  if (threadIdx.x == 0) peers_ok = 1;
+  if (threadIdx.x == 0) peers_ok = dead ? 0 : 1;
   __syncthreads();
-  if (threadIdx.x < pa.n && (int)threadIdx.x != pa.me)
+  if (!dead && threadIdx.x < pa.n && (int)threadIdx.x != pa.me)
     if (!wait_flag_ge(pa.flags[pa.me] + 2 * kMaxPeers + threadIdx.x, t)) { flag_exchange_error(a.st); peers_ok = 0; }
   __syncthreads();
   const bool update = peers_ok != 0 && a.st->xch_error == 0u;   // (the reduce-slice kernel may have timed out already)
@@ -740,7 +746,8 @@ __global__ void __launch_bounds__(kAdamThreads) adam_allgather_kernel(AdamArgs a
       __threadfence_system();
       for (int r = 0; r < pa.n; ++r)                  // this rank has finished reading gradients and reduced slices
         if (r != pa.me) st_release_sys(pa.flags[r] + kMaxPeers + pa.me, t);
-      for (int r = 0; r < pa.n; ++r)
+      const bool gave_up = *reinterpret_cast<volatile unsigned int*>(&a.st->xch_error) != 0u;   // now or in an earlier step
+      for (int r = 0; r < pa.n && !gave_up; ++r)
         if (r != pa.me && !wait_flag_ge(pa.flags[pa.me] + kMaxPeers + r, t)) flag_exchange_error(a.st);
     }
   }
