@@ -431,6 +431,49 @@ def section(name, fn, default=None):
         return {"error": f"{type(exc).__name__}: {str(exc)[:300]}"} if default is None else default
 
 
+def multistep_check(torch, dist, make_engine, pool, group, group_size, device, label, need_p2p=False, first=3, n=37):
+    """mdt_train_steps (multi-step graphs) against the same batches stepped one mdt_train_step at a time, on one trial
+    group: parameters and moments bit-identical on every rank and across the ranks of the group, no expired peer wait.
+    Every rank of the WORLD calls this together (each on its own group).  The two engines are stepped ONE AFTER THE
+    OTHER (synchronize + barrier): two peer-memory engines of a group in flight together starve each other
+    (include/mdt_b200.h).  A rank whose engine raises still reaches every collective, so the others do not hang.
+    Returns "ok" / "FAIL" (the same on every rank), or None when the peer-memory exchange is not available."""
+    rank = dist.get_rank()
+    a = make_engine()
+    if need_p2p and not a.p2p:
+        a.close()
+        return None
+    b = make_engine()
+    same = True
+    try:
+        try:
+            a.train_steps(pool, first, n)
+            a.synchronize()
+        except Exception as exc:      # noqa: BLE001
+            sys.stderr.write(f"[bench] rank {rank}: multistep_check {label} (multi-step leg): {exc}\n")
+            same = False
+        dist.barrier()
+        try:
+            for i in range(n):
+                b.train_step(pool[(first + i) % pool.shape[0]], None, want_loss=False)
+            b.synchronize()
+            same = (same and torch.equal(a.params, b.params) and torch.equal(a.exp_avg, b.exp_avg)
+                    and torch.equal(a.exp_avg_sq, b.exp_avg_sq)
+                    and not a.exchange_status()[1] and not b.exchange_status()[1])
+        except Exception as exc:      # noqa: BLE001
+            sys.stderr.write(f"[bench] rank {rank}: multistep_check {label} (single-step leg): {exc}\n")
+            same = False
+        got = [torch.empty_like(a.params) for _ in range(group_size)]
+        dist.all_gather(got, a.params.clone(), group=group)
+        same = same and all(torch.equal(got[0], t) for t in got)
+        flag = torch.tensor([1 if same else 0], device=device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return "ok" if int(flag.item()) == 1 else "FAIL"
+    finally:
+        a.close()
+        b.close()
+
+
 def run_own(args):
     ctx = Ctx(args)
     watchdog = start_watchdog(args.max_seconds, ctx.rank)
@@ -684,49 +727,15 @@ def run_own(args):
                 finally:
                     e2.close()
 
-            def multistep_check(mode, xch, n=37):
-                """mdt_train_steps (multi-step graphs) against the same batches stepped one mdt_train_step at a time,
-                on this layout's groups: parameters and moments bit-identical on every rank and across the ranks of a
-                group, no expired peer wait.  The two engines are stepped ONE AFTER THE OTHER (synchronize + barrier):
-                two peer-memory engines of a group in flight together starve each other (include/mdt_b200.h)."""
-                a = new_engine(mode, group=mine, seed=1234 + rank // k, exchange=xch)
-                if xch in ("p2p", "p2p_two_shot") and not a.p2p:
-                    a.close()
-                    return None
-                b = new_engine(mode, group=mine, seed=1234 + rank // k, exchange=xch)
-                same = True
-                try:
-                    try:
-                        a.train_steps(pool, 3, n)
-                        a.synchronize()
-                    except Exception as exc:      # noqa: BLE001 -- every rank must still reach the collectives below
-                        sys.stderr.write(f"[bench] rank {rank}: multistep_check {name}/{xch} (multi-step leg): {exc}\n")
-                        same = False
-                    dist.barrier()
-                    try:
-                        for i in range(n):
-                            b.train_step(pool[(3 + i) % POOL_BATCHES], None, want_loss=False)
-                        b.synchronize()
-                        same = (same and torch.equal(a.params, b.params) and torch.equal(a.exp_avg, b.exp_avg)
-                                and torch.equal(a.exp_avg_sq, b.exp_avg_sq)
-                                and not a.exchange_status()[1] and not b.exchange_status()[1])
-                    except Exception as exc:      # noqa: BLE001
-                        sys.stderr.write(f"[bench] rank {rank}: multistep_check {name}/{xch} (single-step leg): {exc}\n")
-                        same = False
-                    got = [torch.empty_like(a.params) for _ in range(k)]
-                    dist.all_gather(got, a.params.clone(), group=mine)
-                    same = same and all(torch.equal(got[0], t) for t in got)
-                    flag = torch.tensor([1 if same else 0], device=device)
-                    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-                    return "ok" if int(flag.item()) == 1 else "FAIL"
-                finally:
-                    a.close()
-                    b.close()
+            def multistep_case(mode, xch):
+                make = lambda: new_engine(mode, group=mine, seed=1234 + rank // k, exchange=xch)
+                return multistep_check(torch, dist, make, pool, mine, k, device, f"{name}/{xch}",
+                                       need_p2p=xch in ("p2p", "p2p_two_shot"))
 
             if not args.no_parity:
                 chk = {}
                 for xch in ("p2p", "p2p_two_shot", "nccl"):
-                    r_ = section(f"multistep_parity/{name}/{xch}", lambda: multistep_check(args.gemm_mode, xch))
+                    r_ = section(f"multistep_parity/{name}/{xch}", lambda: multistep_case(args.gemm_mode, xch))
                     if r_ is not None:
                         chk[xch] = r_
                 if any(chk.get(x) == "FAIL" for x in ("p2p", "p2p_two_shot")):
