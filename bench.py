@@ -474,6 +474,27 @@ def multistep_check(torch, dist, make_engine, pool, group, group_size, device, l
         b.close()
 
 
+def multistep_fallbacks(check_kinds, env):
+    """Run the multi-step checks of one layout and, where one fails, step back to the next more conservative form
+    for the engines created afterwards (every rank sees the same world-reduced verdicts, so every rank sets the same
+    switches): first the weight-shadow refresh back on the main stream (MDT_NO_DEFER_SHADOWS=1, the one change of
+    round 2 that never ran on a multi-GPU box), then -- for the peer-memory exchanges -- one step per call
+    (MDT_P2P_SINGLE_STEPS=1, the form the golden DDP replays check)."""
+    chk = check_kinds(("p2p", "p2p_two_shot", "nccl"))
+    bad = [x for x in ("p2p", "p2p_two_shot", "nccl") if chk.get(x) not in (None, "ok")]
+    if bad and env.get("MDT_NO_DEFER_SHADOWS") != "1":
+        env["MDT_NO_DEFER_SHADOWS"] = "1"
+        again = check_kinds(bad, "/no_defer")
+        chk["retry_with_MDT_NO_DEFER_SHADOWS"] = again
+        bad = [x for x in bad if again.get(x) not in (None, "ok")]
+        chk["note"] = "engines from here on are created with MDT_NO_DEFER_SHADOWS=1"
+    if any(x in ("p2p", "p2p_two_shot") for x in bad) and env.get("MDT_P2P_SINGLE_STEPS") != "1":
+        env["MDT_P2P_SINGLE_STEPS"] = "1"
+        chk["note"] = chk.get("note", "") + ("; " if chk.get("note") else "") + \
+            "peer-memory groups from here on are stepped with MDT_P2P_SINGLE_STEPS=1"
+    return chk
+
+
 def run_own(args):
     ctx = Ctx(args)
     watchdog = start_watchdog(args.max_seconds, ctx.rank)
@@ -733,16 +754,15 @@ def run_own(args):
                                        need_p2p=xch in ("p2p", "p2p_two_shot"))
 
             if not args.no_parity:
-                chk = {}
-                for xch in ("p2p", "p2p_two_shot", "nccl"):
-                    r_ = section(f"multistep_parity/{name}/{xch}", lambda: multistep_case(args.gemm_mode, xch))
-                    if r_ is not None:
-                        chk[xch] = r_
-                if any(chk.get(x) == "FAIL" for x in ("p2p", "p2p_two_shot")):
-                    # every rank sees the same (world-reduced) verdict: peer-memory groups are timed on the form the
-                    # golden replays check, one step per call
-                    os.environ["MDT_P2P_SINGLE_STEPS"] = "1"
-                    chk["note"] = "peer-memory groups timed with MDT_P2P_SINGLE_STEPS=1 from here on"
+                def check_kinds(kinds, tag):
+                    got = {}
+                    for xch in kinds:
+                        r_ = section(f"multistep_parity/{name}/{xch}{tag}", lambda: multistep_case(args.gemm_mode, xch))
+                        if r_ is not None:
+                            got[xch] = r_
+                    return got
+
+                chk = multistep_fallbacks(lambda kinds, tag="": check_kinds(kinds, tag), os.environ)
                 multistep[name] = chk
                 if rank == 0:
                     _PARTIAL.update({"multistep_parity": multistep})

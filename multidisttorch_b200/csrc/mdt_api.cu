@@ -119,6 +119,7 @@ struct mdt_engine {
   bool opt_pipeline = true, opt_graph_reduce = true, opt_graph_dbg = false;
   int opt_steps_per_graph = 16;
   bool opt_p2p_single = false;                      // MDT_P2P_SINGLE_STEPS
+  bool opt_defer_shadows = true;                    // MDT_NO_DEFER_SHADOWS=1: weight shadows refreshed on the main stream
   volatile unsigned long long* mailbox = nullptr;   // ring of 64 words at loss_pinned + 64 bytes: see publish_loss()
   volatile unsigned int* err_word = nullptr;        // pinned word the exchange kernels set when a peer never answered
   float* loss_hist = nullptr;                       // device ring of the last kLossHist per-step losses
@@ -629,7 +630,7 @@ int train_step_device(mdt_engine* e, const float* x, int B, const float* eps, in
         const bool tail = piped && tail_no_prefetch && i == steps - 1;
         const bool saved = e->tc->no_prefetch;
         if (tail) e->tc->no_prefetch = true;
-        e->tc->defer_shadows = i < steps - 1;        // a later step of this capture joins the refresh (tc05_join_shadows)
+        e->tc->defer_shadows = e->opt_defer_shadows && i < steps - 1;   // a later step of this capture joins the refresh (tc05_join_shadows)
         const int rc = one();
         e->tc->defer_shadows = false;
         e->tc->no_prefetch = saved;
@@ -733,6 +734,7 @@ int mdt_engine_create(const mdt_cfg* cfg, void* nccl_comm, int group_size, int g
   e->opt_graph_dbg = getenv("MDT_GRAPH_DBG") != nullptr;
   if (const char* v = getenv("MDT_STEPS_PER_GRAPH")) e->opt_steps_per_graph = atoi(v);
   if (const char* v = getenv("MDT_P2P_SINGLE_STEPS")) e->opt_p2p_single = atoi(v) != 0;
+  if (const char* v = getenv("MDT_NO_DEFER_SHADOWS")) e->opt_defer_shadows = atoi(v) == 0;
   e->exchange = cfg->exchange;
   if (const char* v = getenv("MDT_P2P_TWO_SHOT_FROM")) e->two_shot_from = atoi(v);
   if (const char* v = getenv("MDT_P2P_TWO_SHOT_BYTES")) e->two_shot_bytes = atoll(v);

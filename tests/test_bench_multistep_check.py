@@ -22,3 +22,45 @@ def test_multistep_check_verdicts_agree_across_ranks_and_failures_do_not_hang():
         assert r["no_peer_memory"] is None
         assert r["all_closed"] is True
     assert any("injected failure in the multi-step leg" in log for log in logs)
+
+
+def _scripted(results):
+    """check_kinds stand-in: pops the next scripted verdict table; records what was asked."""
+    asked = []
+
+    def check(kinds, tag=""):
+        asked.append((tuple(kinds), tag))
+        table = results.pop(0)
+        return {k: table[k] for k in kinds if table.get(k) is not None}
+    return check, asked
+
+
+def test_multistep_fallbacks_all_ok_sets_nothing():
+    import bench
+    env = {}
+    check, asked = _scripted([{"p2p": "ok", "p2p_two_shot": "ok", "nccl": "ok"}])
+    chk = bench.multistep_fallbacks(check, env)
+    assert chk == {"p2p": "ok", "p2p_two_shot": "ok", "nccl": "ok"} and env == {} and len(asked) == 1
+
+
+def test_multistep_fallbacks_first_step_back_is_the_shadow_refresh():
+    import bench
+    env = {}
+    check, asked = _scripted([{"p2p": "FAIL", "p2p_two_shot": "ok", "nccl": "ok"}, {"p2p": "ok"}])
+    chk = bench.multistep_fallbacks(check, env)
+    assert env == {"MDT_NO_DEFER_SHADOWS": "1"}
+    assert asked[1] == (("p2p",), "/no_defer") and chk["retry_with_MDT_NO_DEFER_SHADOWS"] == {"p2p": "ok"}
+    assert "MDT_NO_DEFER_SHADOWS=1" in chk["note"] and "SINGLE_STEPS" not in chk["note"]
+
+
+def test_multistep_fallbacks_peer_memory_ends_on_single_steps_nccl_does_not():
+    import bench
+    env = {}
+    check, _ = _scripted([{"p2p": "FAIL", "p2p_two_shot": None, "nccl": {"error": "boom"}}, {"p2p": "FAIL", "nccl": "FAIL"}])
+    chk = bench.multistep_fallbacks(check, env)
+    assert env == {"MDT_NO_DEFER_SHADOWS": "1", "MDT_P2P_SINGLE_STEPS": "1"}
+    assert "MDT_P2P_SINGLE_STEPS=1" in chk["note"]
+    # a later layout of the same run: the switches are already set, nothing is retried
+    check2, asked2 = _scripted([{"p2p": "ok", "p2p_two_shot": "ok", "nccl": "FAIL"}])
+    chk2 = bench.multistep_fallbacks(check2, env)
+    assert len(asked2) == 1 and "note" not in chk2
