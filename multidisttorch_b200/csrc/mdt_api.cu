@@ -1091,9 +1091,9 @@ int mdt_train_steps(mdt_engine* e, const mdt_batch_source* src, int batch, int64
   }
   // MDT_P2P_SINGLE_STEPS=1: groups that exchange gradients over peer memory take one mdt_train_step per batch (the
   // form every DDP fixture checks) instead of multi-step graphs.  Multi-step graphs against single steps were compared
-  // bit for bit on one GPU (fused and separate optimizer) and on 2 GPUs with the NCCL exchange; the 2-GPU peer-memory
-  // comparison of round 2 was invalid (scripts/ddp_multistep_check.py then kept two peer-memory engines of one group in
-  // flight at once -- see DESIGN.md section 5) and could not be repeated, so this switch stays as the way back.
+  // bit for bit on one GPU (fused and separate optimizer) and on 2 GPUs with the NCCL exchange; the one 2-GPU
+  // peer-memory comparison of round 2 came out negative for reasons it could not pin down, so
+  // bench.py --gpus N repeats it before timing and falls back to this switch when it fails.
   if (e->opt_p2p_single && e->gsize > 1 && e->p2p && !e->use_sgd && e->exchange != MDT_EXCHANGE_NCCL) {
     const unsigned int seq_before = e->pub_expected;
     for (int i = 0; i < n_steps; ++i) {

@@ -5,7 +5,10 @@ across ranks, for every exchange.  torchrun --nproc-per-node N scripts/ddp_multi
 The two engines are stepped ONE AFTER THE OTHER (synchronize + barrier in between): the peer-memory exchange kernels
 spin with every block resident, so two of them in flight on the same GPUs in different orders on different ranks
 starve each other's GEMMs until the bounded wait (30 s) expires and flags the step.  The first version of this script
-did not do that, and its one 2-GPU run (round 2) reported False for tf32x3/p2p after such a stall; tf32x3/nccl: True."""
+did not do that; its one 2-GPU run (round 2) reported False for tf32x3/p2p (tf32x3/nccl: True) and overran its time
+limit -- an expired wait, from that overlap or from a real fault of the multi-step peer-memory path: not known
+(DESIGN.md section 5).  bench.py --gpus N runs the same comparison before it times a layout (multistep_parity)."""
+
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch, torch.distributed as dist
